@@ -1,0 +1,647 @@
+// K2 (fused policy/value MLP forward + action sampling) and K4 (fused loss + backward).
+//
+// Replaces, for a whole [rows x n] batch per launch:
+//   Actor.act            A3C/policies.py:42-72,110-115      -> acx_policy_forward_sample_{gauss,cat}
+//   Actor.get_kl / logp  A3C/policies.py:60,69,75,106-108   -> acx_policy_logp_{gauss,cat}
+//   Critic.value         A3C/policies.py:146-150,176-177    -> acx_value_forward
+//   Actor/Critic loss + compute_gradients
+//                        A3C/policies.py:74-85,152-158      -> acx_loss_backward_{gauss,cat}
+// See acx_mlp.cuh for the tile engine.  Head math follows oracle/policies.py line by line.
+#include "acx_mlp.cuh"
+
+using namespace acxmlp;
+
+namespace {
+
+template <int H1, bool LRELU>
+__device__ inline void layer1_chunk(Smem& sm, int c1, int ob) {
+  // X1[c1*64 + r][m] = act(sum_i obs[i][m] * W1[i][k] + b1[k]) for the 64 rows of this chunk
+  const int r = threadIdx.x >> 2, q = (threadIdx.x & 3) * 16, k = c1 * CH + r;
+  const float bk = sm.b1[k];
+#pragma unroll
+  for (int m4 = 0; m4 < 4; ++m4) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < ob; ++i) {
+      const float w = sm.W1[i * H1 + k];
+      const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + q + 4 * m4]);
+      s.x = fmaf(o.x, w, s.x); s.y = fmaf(o.y, w, s.y); s.z = fmaf(o.z, w, s.z); s.w = fmaf(o.w, w, s.w);
+    }
+    float4 o;
+    o.x = act_fn<LRELU>(__fadd_rn(s.x, bk)); o.y = act_fn<LRELU>(__fadd_rn(s.y, bk));
+    o.z = act_fn<LRELU>(__fadd_rn(s.z, bk)); o.w = act_fn<LRELU>(__fadd_rn(s.w, bk));
+    *reinterpret_cast<float4*>(&sm.bufA[r * MS + q + 4 * m4]) = o;
+  }
+}
+
+template <int H1>
+__device__ inline void layer1_grad(Smem& sm, int c1, int ob, float* __restrict__ scrW1, float* __restrict__ scrb1,
+                                   bool first) {
+  const int j = threadIdx.x;
+  if (j < CH) {
+    float sb = 0.f, sw[MAX_OB];
+#pragma unroll
+    for (int i = 0; i < MAX_OB; ++i) sw[i] = 0.f;
+    for (int m4 = 0; m4 < MT / 4; ++m4) {
+      const float4 d = *reinterpret_cast<const float4*>(&sm.bufA[j * MS + 4 * m4]);
+      sb += d.x; sb += d.y; sb += d.z; sb += d.w;
+#pragma unroll
+      for (int i = 0; i < MAX_OB; ++i)
+        if (i < ob) {
+          const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + 4 * m4]);
+          sw[i] = fmaf(o.x, d.x, sw[i]); sw[i] = fmaf(o.y, d.y, sw[i]);
+          sw[i] = fmaf(o.z, d.z, sw[i]); sw[i] = fmaf(o.w, d.w, sw[i]);
+        }
+    }
+    const int k = c1 * CH + j;
+    scrb1[k] = first ? sb : scrb1[k] + sb;
+#pragma unroll
+    for (int i = 0; i < MAX_OB; ++i)
+      if (i < ob) {
+        float* p = scrW1 + i * H1 + k;
+        *p = first ? sw[i] : *p + sw[i];
+      }
+  }
+}
+
+// pre-activation of the head for sample m: pre[a] = sum_k Xh[k][m] * Wh[k][a] + bh[a]
+template <int HH>
+__device__ inline void head_pre(const Smem& sm, const float* __restrict__ Xh, int m, int nout, float (&pre)[MAX_OUT]) {
+#pragma unroll
+  for (int a = 0; a < MAX_OUT; ++a) pre[a] = 0.f;
+  for (int k = 0; k < HH; ++k) {
+    const float x = Xh[k * MS + m];
+#pragma unroll
+    for (int a = 0; a < MAX_OUT; ++a)
+      if (a < nout) pre[a] = fmaf(x, sm.Wh[k * nout + a], pre[a]);
+  }
+#pragma unroll
+  for (int a = 0; a < MAX_OUT; ++a)
+    if (a < nout) pre[a] = __fadd_rn(pre[a], sm.bh[a]);
+}
+
+template <int H1, int H3, bool LRELU, int HEAD, int MODE>
+__global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+  constexpr bool TRAIN = MODE == MODE_TRAIN;
+  constexpr int TJ3 = H3 / 16, NC1 = H1 / CH;
+  const AcxNetLayout L = A.L;
+  const int ob = L.ob, nout = L.nout, tid = threadIdx.x;
+  const float* __restrict__ P = A.params;
+
+  for (int i = tid; i < ob * H1; i += NT) sm.W1[i] = P[L.W1 + i];
+  for (int i = tid; i < H1; i += NT) sm.b1[i] = P[L.b1 + i];
+  for (int i = tid; i < H2; i += NT) sm.b2[i] = P[L.b2 + i];
+  for (int i = tid; i < H3; i += NT) sm.b3[i] = P[L.b3 + i];
+  for (int i = tid; i < H3 * nout; i += NT) sm.Wh[i] = P[L.Wh + i];
+  if (tid < nout) {
+    sm.bh[tid] = P[L.bh + tid];
+    if (HEAD == HEAD_GAUSS) sm.log_std[tid] = P[L.log_std + tid];
+  }
+
+  const int tpr = (A.n + MT - 1) / MT;
+  const int ntiles = A.rows * tpr;
+  const unsigned int mine = ((int)blockIdx.x < ntiles) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  Ring<H1, H3, TRAIN> ring;
+  ring.init(&sm, P + L.W2, P + L.W3, mine);     // __syncthreads inside: small params visible after it
+  const Coord c;
+
+  const unsigned int step0 = A.step0 + ((MODE == MODE_SAMPLE && A.step_base) ? *A.step_base : 0u);
+  const double invB = 1.0 / ((double)A.rows * (double)A.n);
+  double lsum[4] = {0.0, 0.0, 0.0, 0.0};        // per-thread loss sums (head threads)
+  float dls[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};    // d loss / d log_std (gauss train)
+  float beta = 0.f, gam = 0.f, adv_mean = 0.f, adv_inv = 1.f;
+  if (TRAIN && HEAD != HEAD_VALUE) {
+    beta = A.opt[ACX_OPT_BETA_KL]; gam = A.opt[ACX_OPT_GAMMA_ENT];
+    if (A.adv_stats) { adv_mean = A.adv_stats[0]; adv_inv = A.adv_stats[1]; }
+  }
+  float* __restrict__ scr = TRAIN ? A.scratch + (size_t)blockIdx.x * L.size : nullptr;
+  bool first = true;
+  if (TRAIN && tid < L.size - L.bh) scr[L.bh + tid] = 0.f;     // head bias / log_std slots incl. alignment padding
+
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int row = tile / tpr, n0 = (tile % tpr) * MT;
+    const int valid = min(MT, A.n - n0);
+    for (int idx = tid; idx < ob * MT; idx += NT) {
+      const int i = idx / MT, m = idx % MT;
+      sm.obs[idx] = (m < valid) ? A.obs[((size_t)row * ob + i) * A.n + n0 + m] : 0.f;
+    }
+    __syncthreads();
+
+    // ------------------------------------------------ forward: layers 1+2 (layer 1 recomputed per chunk)
+    {
+      float acc[8][4];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+#pragma unroll
+        for (int m = 0; m < 4; ++m) acc[j][m] = 0.f;
+      for (int c1 = 0; c1 < NC1; ++c1) {
+        layer1_chunk<H1, LRELU>(sm, c1, ob);
+        __syncthreads();
+        const float* slot = ring.begin();
+        f_stage<8>(slot, sm.bufA, acc, c);
+        __syncthreads();
+      }
+      f_store<8, LRELU>(sm.X2, sm.b2, acc, c);
+    }
+    __syncthreads();
+    // ------------------------------------------------ forward: layer 3
+    {
+      float acc[TJ3][4];
+#pragma unroll
+      for (int j = 0; j < TJ3; ++j)
+#pragma unroll
+        for (int m = 0; m < 4; ++m) acc[j][m] = 0.f;
+      for (int c3 = 0; c3 < 2; ++c3) {
+        const float* slot = ring.begin();
+        f_stage<TJ3>(slot, sm.X2 + c3 * CH * MS, acc, c);
+        __syncthreads();
+      }
+      f_store<TJ3, LRELU>(sm.X3, sm.b3, acc, c);
+    }
+    __syncthreads();
+
+    // ------------------------------------------------ head (one thread per sample)
+    const bool basic = (HEAD == HEAD_VALUE) && A.basic_head;
+    const float* Xh = basic ? sm.X2 : sm.X3;
+    if (tid < MT) {
+      const int m = tid;
+      const bool live = m < valid;
+      const size_t col = (size_t)n0 + m;
+      const size_t s_idx = (size_t)row * A.n + col;                 // [rows][n] arrays
+      float pre[MAX_OUT];
+      head_pre<H3>(sm, Xh, m, nout, pre);
+      float dh[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
+      if (HEAD == HEAD_VALUE) {
+        if (live) {
+          if (MODE != MODE_TRAIN) {
+            A.v_out[s_idx] = pre[0];
+          } else {
+            const float err = pre[0] - A.targets[s_idx];
+            lsum[0] += (double)err * (double)err;
+            dh[0] = (float)(2.0 * (double)err * invB);
+          }
+        }
+      } else if (HEAD == HEAD_GAUSS) {
+        if (live) {
+          float lp = 0.f, ent = 0.f, dlp = 0.f, dent = 0.f;
+          float z[MAX_OUT], sd[MAX_OUT], th[MAX_OUT], ls[MAX_OUT];
+          AcxRng4 g = {0u, 0u, 0u, 0u};
+          if (MODE == MODE_SAMPLE && A.noise == nullptr)
+            g = acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed);
+#pragma unroll
+          for (int d = 0; d < MAX_OUT; ++d)
+            if (d < nout) {
+              th[d] = tanhf(pre[d]);
+              const float mu = __fmul_rn(th[d], A.ac_scale);
+              ls[d] = fminf(fmaxf(sm.log_std[d], ACX_LOG_STD_MIN), ACX_LOG_STD_MAX);
+              sd[d] = expf(ls[d]);
+              const size_t a_idx = ((size_t)row * nout + d) * A.n + col;
+              float ac;
+              if (MODE == MODE_SAMPLE) {
+                float eps;
+                if (A.noise) eps = A.noise[a_idx];
+                else eps = (d == 0) ? acx_normal(g.x, g.y) : ((d == 1) ? acx_normal(g.z, g.w) : 0.f);
+                ac = __fadd_rn(mu, __fmul_rn(sd[d], eps));
+                A.ac_out_f[a_idx] = ac;
+              } else {
+                ac = A.ac_in_f[a_idx];
+              }
+              if (A.head_out) A.head_out[a_idx] = mu;
+              z[d] = __fdiv_rn(__fsub_rn(ac, mu), sd[d]);
+              lp += __fsub_rn(__fsub_rn(__fmul_rn(__fmul_rn(-0.5f, z[d]), z[d]), ls[d]), ACX_HALF_LOG_2PI);
+              ent += __fadd_rn(__fadd_rn(0.5f, ACX_HALF_LOG_2PI), ls[d]);
+            }
+          if (MODE != MODE_TRAIN) {
+            if (A.logp_out) A.logp_out[s_idx] = lp;
+            if (A.ent_out) A.ent_out[s_idx] = ent;
+            if (MODE == MODE_EVAL && A.logp_old) {
+              const double df = (double)A.logp_old[s_idx] - (double)lp;
+              lsum[1] += df * df;
+            }
+          } else {
+            const float advn = (A.adv[s_idx] - adv_mean) * adv_inv;
+            const float diff = A.logp_old[s_idx] - lp;
+            lsum[0] += (double)advn * (double)lp;
+            lsum[1] += (double)diff * (double)diff;
+            lsum[2] += (double)ent;
+            dlp = (float)((-(double)advn - 2.0 * (double)beta * (double)diff) * invB);
+            dent = (float)(-(double)gam * invB);
+#pragma unroll
+            for (int d = 0; d < MAX_OUT; ++d)
+              if (d < nout) {
+                const float dmu = dlp * z[d] / sd[d];
+                dh[d] = dmu * A.ac_scale * (1.0f - th[d] * th[d]);
+                const bool inside = sm.log_std[d] >= ACX_LOG_STD_MIN && sm.log_std[d] <= ACX_LOG_STD_MAX;
+                if (inside) dls[d] += dlp * (z[d] * z[d] - 1.0f) + dent;
+              }
+          }
+        }
+      } else {   // HEAD_CAT
+        if (live) {
+          float l1[MAX_OUT], logps[MAX_OUT], p[MAX_OUT];
+          float mx1 = -INFINITY, mx2 = -INFINITY;
+#pragma unroll
+          for (int a = 0; a < MAX_OUT; ++a)
+            if (a < nout) {
+              l1[a] = __fadd_rn(pre[a], 1e-8f);                 // policies.py:65
+              mx1 = fmaxf(mx1, l1[a]); mx2 = fmaxf(mx2, pre[a]);
+            }
+          float se1 = 0.f, se2 = 0.f;
+#pragma unroll
+          for (int a = 0; a < MAX_OUT; ++a)
+            if (a < nout) {
+              se1 += expf(l1[a] - mx1);
+              p[a] = expf(pre[a] - mx2);
+              se2 += p[a];
+            }
+          const float lse = mx1 + logf(se1);
+          float ent = 0.f;
+#pragma unroll
+          for (int a = 0; a < MAX_OUT; ++a)
+            if (a < nout) {
+              logps[a] = l1[a] - lse;
+              p[a] = p[a] / se2;
+              ent -= p[a] * logps[a];
+            }
+          int ac;
+          if (MODE == MODE_SAMPLE) {
+            float u;
+            if (A.noise) u = A.noise[s_idx];
+            else u = acx_u01(acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed).x);
+            // tf.multinomial: inverse CDF in double over exp(logit - max)
+            double cdf[MAX_OUT], run = 0.0;
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) { run += exp((double)pre[a] - (double)mx2); cdf[a] = run; }
+            const double thr = (double)u * run;
+            ac = 0;
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout && cdf[a] <= thr) ++ac;
+            if (ac > nout - 1) ac = nout - 1;
+            A.ac_out_i[s_idx] = ac;
+          } else {
+            ac = A.ac_in_i[s_idx];
+          }
+          float lp = 0.f;
+#pragma unroll
+          for (int a = 0; a < MAX_OUT; ++a)
+            if (a < nout && a == ac) lp = logps[a];
+          if (A.head_out) {
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) A.head_out[((size_t)row * nout + a) * A.n + col] = pre[a];
+          }
+          if (MODE != MODE_TRAIN) {
+            if (A.logp_out) A.logp_out[s_idx] = lp;
+            if (A.ent_out) A.ent_out[s_idx] = ent;
+            if (MODE == MODE_EVAL && A.logp_old) {
+              const double df = (double)A.logp_old[s_idx] - (double)lp;
+              lsum[1] += df * df;
+            }
+          } else {
+            const float advn = (A.adv[s_idx] - adv_mean) * adv_inv;
+            const float diff = A.logp_old[s_idx] - lp;
+            lsum[0] += (double)advn * (double)lp;
+            lsum[1] += (double)diff * (double)diff;
+            lsum[2] += (double)ent;
+            const float dlp = (float)((-(double)advn - 2.0 * (double)beta * (double)diff) * invB);
+            const float dent = (float)(-(double)gam * invB);
+            float dlogps[MAX_OUT], dpp[MAX_OUT], sdl = 0.f, sdp = 0.f;
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) {
+                dlogps[a] = (a == ac ? dlp : 0.f) - dent * p[a];
+                dpp[a] = -dent * logps[a];
+                sdl += dlogps[a];
+                sdp += dpp[a] * p[a];
+              }
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) dh[a] = dlogps[a] - expf(logps[a]) * sdl + p[a] * (dpp[a] - sdp);
+          }
+        }
+      }
+      if (TRAIN) {
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a)
+          if (a < nout) sm.dHead[a * MT + m] = dh[a];
+      }
+    }
+    if (!TRAIN) {
+      __syncthreads();
+      continue;
+    }
+
+    // ------------------------------------------------ backward
+    __syncthreads();
+    {   // head weights: dWh[k][a] = sum_m Xh[k][m] dHead[a][m] ; dbh[a] = sum_m dHead[a][m]
+      if (tid < H3) {
+        for (int a = 0; a < nout; ++a) {
+          float s = 0.f;
+          for (int m4 = 0; m4 < MT / 4; ++m4) {
+            const float4 x = *reinterpret_cast<const float4*>(&Xh[tid * MS + 4 * m4]);
+            const float4 d = *reinterpret_cast<const float4*>(&sm.dHead[a * MT + 4 * m4]);
+            s = fmaf(x.x, d.x, s); s = fmaf(x.y, d.y, s); s = fmaf(x.z, d.z, s); s = fmaf(x.w, d.w, s);
+          }
+          float* p = scr + L.Wh + tid * nout + a;
+          *p = first ? s : *p + s;
+        }
+      } else if (tid >= 128 && tid < 128 + nout) {
+        const int a = tid - 128;
+        float s = 0.f;
+        for (int m = 0; m < MT; ++m) s += sm.dHead[a * MT + m];
+        float* p = scr + L.bh + a;
+        *p = first ? s : *p + s;
+      }
+    }
+    __syncthreads();
+    // dPre3 = (Wh . dHead) * act'(X3), in place
+    for (int idx = tid; idx < H3 * MT; idx += NT) {
+      const int k = idx >> 6, m = idx & 63;
+      float s = 0.f;
+      for (int a = 0; a < nout; ++a) s = fmaf(sm.Wh[k * nout + a], sm.dHead[a * MT + m], s);
+      float* x = &sm.X3[k * MS + m];
+      *x = s * act_grad<LRELU>(*x);
+    }
+    __syncthreads();
+    g_stage<8, TJ3>(sm.X2, sm.X3, scr + L.W3, H3, first, c);
+    bias_grad(sm.X3, H3, scr + L.b3, first);
+    __syncthreads();
+    for (int c3 = 0; c3 < 2; ++c3) {      // dPre2 rows c3*64.. = (W3 . dPre3) * act'(X2), in place
+      const float* slot = ring.begin();
+      float acc[4][4];
+      b_stage<H3>(slot, sm.X3, acc, c);
+      b_store<LRELU>(sm.X2 + c3 * CH * MS, acc, c);
+      __syncthreads();
+    }
+    bias_grad(sm.X2, H2, scr + L.b2, first);
+    for (int c1 = 0; c1 < NC1; ++c1) {
+      layer1_chunk<H1, LRELU>(sm, c1, ob);
+      __syncthreads();
+      g_stage<4, 8>(sm.bufA, sm.X2, scr + L.W2 + (size_t)c1 * CH * H2, H2, first, c);
+      __syncthreads();
+      const float* slot = ring.begin();
+      float acc[4][4];
+      b_stage<H2>(slot, sm.X2, acc, c);
+      b_store<LRELU>(sm.bufA, acc, c);    // dPre1 chunk, in place over the recomputed X1 chunk
+      __syncthreads();
+      layer1_grad<H1>(sm, c1, ob, scr + L.W1, scr + L.b1, first);
+      __syncthreads();
+    }
+    first = false;
+  }
+
+  // ---------------------------------------------------- per-CTA scalar sums
+  if (MODE == MODE_SAMPLE) return;
+  if (MODE == MODE_EVAL && (HEAD == HEAD_VALUE || A.kl_partial == nullptr)) return;
+  __syncthreads();
+  double v[4] = {lsum[0], lsum[1], lsum[2], 0.0};
+  if (TRAIN && HEAD == HEAD_GAUSS) v[3] = 0.0;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) v[q] = acx_warp_sum_d(v[q]);
+  float dl[MAX_OUT];
+#pragma unroll
+  for (int d = 0; d < MAX_OUT; ++d) dl[d] = acx_warp_sum(dls[d]);
+  const int w = tid >> 5;
+  if ((tid & 31) == 0 && w < 2) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) sm.red[w][q] = v[q];
+#pragma unroll
+    for (int d = 0; d < MAX_OUT; ++d) sm.dHead[w * MAX_OUT + d] = dl[d];
+  }
+  __syncthreads();
+  if (tid == 0) {
+    if (TRAIN) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) A.loss_partial[(size_t)blockIdx.x * 4 + q] = sm.red[0][q] + sm.red[1][q];
+      if (HEAD == HEAD_GAUSS)
+        for (int d = 0; d < nout; ++d) scr[L.log_std + d] = sm.dHead[d] + sm.dHead[MAX_OUT + d];
+    } else {
+      A.kl_partial[blockIdx.x] = sm.red[0][1] + sm.red[1][1];
+    }
+  }
+}
+
+// grad[p] = sum over CTAs (fixed order) of scratch[cta][p]; block 0 also folds the loss sums
+__global__ void __launch_bounds__(256) acx_grad_reduce_kernel(const float* __restrict__ scratch, int ncta, int size,
+                                                              float* __restrict__ grad,
+                                                              const double* __restrict__ loss_partial,
+                                                              float* __restrict__ stats, const float* __restrict__ opt,
+                                                              int is_actor, double count) {
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < size; p += gridDim.x * blockDim.x) {
+    float s = 0.f;
+    for (int cta = 0; cta < ncta; ++cta) s += scratch[(size_t)cta * size + p];
+    grad[p] = s;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && stats != nullptr) {
+    double s0 = 0, s1 = 0, s2 = 0;
+    for (int cta = 0; cta < ncta; ++cta) {
+      s0 += loss_partial[4 * cta]; s1 += loss_partial[4 * cta + 1]; s2 += loss_partial[4 * cta + 2];
+    }
+    if (is_actor) {
+      const double rew_loss = -s0 / count, kl = s1 / count, ent = s2 / count;
+      stats[ACX_STAT_ACTOR_LOSS] = (float)(rew_loss + (double)opt[ACX_OPT_BETA_KL] * kl - (double)opt[ACX_OPT_GAMMA_ENT] * ent);
+      stats[ACX_STAT_KL_PRE] = (float)kl;
+      stats[ACX_STAT_ENT_MEAN] = (float)ent;
+      stats[ACX_STAT_REW_LOSS] = (float)rew_loss;
+    } else {
+      stats[ACX_STAT_CRITIC_LOSS] = (float)(s0 / count);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ host side
+template <int H1, int H3, bool LRELU, int HEAD, int MODE>
+int launch(const Args& a, int grid, cudaStream_t st) {
+  auto kern = acx_mlp_kernel<H1, H3, LRELU, HEAD, MODE>;
+  static bool configured[64] = {false};
+  int dev = 0;
+  ACX_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 64 && !configured[dev]) {
+    ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+    configured[dev] = true;
+  } else if (dev >= 64) {
+    ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+  }
+  kern<<<grid, NT, sizeof(Smem), st>>>(a);
+  ACX_LAUNCH_OK("acx_mlp_kernel");
+  return ACX_OK;
+}
+
+int tile_grid(int rows, int n) {
+  const long long tiles = (long long)rows * ((n + MT - 1) / MT);
+  const int sms = acx_num_sms();
+  return (int)(tiles < sms ? tiles : sms);
+}
+
+int check_common(const char* fn, const float* params, int ob_dim, int nout, int rows, int n, const float* obs) {
+  ACX_REQUIRE(params && obs, "%s: null params/obs", fn);
+  ACX_REQUIRE(acx_aligned16(params), "%s: params must be 16-byte aligned (bulk-TMA source)", fn);
+  ACX_REQUIRE(ob_dim >= 1 && ob_dim <= MAX_OB, "%s: ob_dim %d outside [1,%d]", fn, ob_dim, MAX_OB);
+  ACX_REQUIRE(nout >= 1 && nout <= MAX_OUT, "%s: output width %d outside [1,%d]", fn, nout, MAX_OUT);
+  ACX_REQUIRE(rows >= 0 && n >= 0, "%s: negative batch (rows=%d, n=%d)", fn, rows, n);
+  return ACX_OK;
+}
+
+}  // namespace
+
+extern "C" int acx_policy_forward_sample_gauss(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows,
+                                               int n, const float* obs, const float* eps, uint64_t seed,
+                                               uint64_t index0, uint32_t step0, const uint32_t* step_base, float* ac_out,
+                                               float* logp_out, float* ent_out, float* mu_out, void* stream) {
+  int rc = check_common("acx_policy_forward_sample_gauss", actor, ob_dim, ac_dim, rows, n, obs);
+  if (rc) return rc;
+  if (rows == 0 || n == 0) return ACX_OK;
+  ACX_REQUIRE(ac_out, "acx_policy_forward_sample_gauss: ac_out is null");
+  ACX_REQUIRE(eps || ac_dim <= 2, "acx_policy_forward_sample_gauss: device RNG supports ac_dim <= 2 (got %d)", ac_dim);
+  Args a; memset(&a, 0, sizeof(a));
+  a.params = actor; a.L = acx_actor_layout(ob_dim, ac_dim, 1); a.rows = rows; a.n = n; a.obs = obs;
+  a.ac_scale = ac_scale; a.noise = eps; a.seed = seed; a.index0 = index0; a.step0 = step0; a.step_base = step_base;
+  a.ac_out_f = ac_out; a.logp_out = logp_out; a.ent_out = ent_out; a.head_out = mu_out;
+  return launch<128, 64, true, HEAD_GAUSS, MODE_SAMPLE>(a, tile_grid(rows, n), (cudaStream_t)stream);
+}
+
+extern "C" int acx_policy_forward_sample_cat(const float* actor, int ob_dim, int n_act, int rows, int n,
+                                             const float* obs, const float* u, uint64_t seed, uint64_t index0,
+                                             uint32_t step0, const uint32_t* step_base, int* ac_out, float* logp_out,
+                                             float* ent_out, float* logits_out, void* stream) {
+  int rc = check_common("acx_policy_forward_sample_cat", actor, ob_dim, n_act, rows, n, obs);
+  if (rc) return rc;
+  if (rows == 0 || n == 0) return ACX_OK;
+  ACX_REQUIRE(ac_out, "acx_policy_forward_sample_cat: ac_out is null");
+  Args a; memset(&a, 0, sizeof(a));
+  a.params = actor; a.L = acx_actor_layout(ob_dim, n_act, 0); a.rows = rows; a.n = n; a.obs = obs;
+  a.noise = u; a.seed = seed; a.index0 = index0; a.step0 = step0; a.step_base = step_base;
+  a.ac_out_i = ac_out; a.logp_out = logp_out; a.ent_out = ent_out; a.head_out = logits_out;
+  return launch<128, 64, true, HEAD_CAT, MODE_SAMPLE>(a, tile_grid(rows, n), (cudaStream_t)stream);
+}
+
+extern "C" size_t acx_kl_workspace_bytes(void) { return sizeof(double) * 1024; }
+
+extern "C" int acx_policy_logp_gauss(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows, int n,
+                                     const float* obs, const float* acs, float* logp_out, float* ent_out,
+                                     float* mu_out, const float* logp_old, double* kl_partial, int* kl_blocks,
+                                     void* stream) {
+  int rc = check_common("acx_policy_logp_gauss", actor, ob_dim, ac_dim, rows, n, obs);
+  if (rc) return rc;
+  const int grid = (rows == 0 || n == 0) ? 0 : tile_grid(rows, n);
+  if (kl_blocks) *kl_blocks = grid;
+  if (grid == 0) return ACX_OK;
+  ACX_REQUIRE(acs, "acx_policy_logp_gauss: acs is null");
+  ACX_REQUIRE((logp_old == nullptr) == (kl_partial == nullptr),
+              "acx_policy_logp_gauss: logp_old and kl_partial must be given together");
+  Args a; memset(&a, 0, sizeof(a));
+  a.params = actor; a.L = acx_actor_layout(ob_dim, ac_dim, 1); a.rows = rows; a.n = n; a.obs = obs;
+  a.ac_scale = ac_scale; a.ac_in_f = acs; a.logp_out = logp_out; a.ent_out = ent_out; a.head_out = mu_out;
+  a.logp_old = logp_old; a.kl_partial = kl_partial;
+  return launch<128, 64, true, HEAD_GAUSS, MODE_EVAL>(a, grid, (cudaStream_t)stream);
+}
+
+extern "C" int acx_policy_logp_cat(const float* actor, int ob_dim, int n_act, int rows, int n, const float* obs,
+                                   const int* acs, float* logp_out, float* ent_out, float* logits_out,
+                                   const float* logp_old, double* kl_partial, int* kl_blocks, void* stream) {
+  int rc = check_common("acx_policy_logp_cat", actor, ob_dim, n_act, rows, n, obs);
+  if (rc) return rc;
+  const int grid = (rows == 0 || n == 0) ? 0 : tile_grid(rows, n);
+  if (kl_blocks) *kl_blocks = grid;
+  if (grid == 0) return ACX_OK;
+  ACX_REQUIRE(acs, "acx_policy_logp_cat: acs is null");
+  ACX_REQUIRE((logp_old == nullptr) == (kl_partial == nullptr),
+              "acx_policy_logp_cat: logp_old and kl_partial must be given together");
+  Args a; memset(&a, 0, sizeof(a));
+  a.params = actor; a.L = acx_actor_layout(ob_dim, n_act, 0); a.rows = rows; a.n = n; a.obs = obs;
+  a.ac_in_i = acs; a.logp_out = logp_out; a.ent_out = ent_out; a.head_out = logits_out;
+  a.logp_old = logp_old; a.kl_partial = kl_partial;
+  return launch<128, 64, true, HEAD_CAT, MODE_EVAL>(a, grid, (cudaStream_t)stream);
+}
+
+extern "C" int acx_value_forward(const float* critic, int ob_dim, int rows, int n, const float* obs, float* v_out,
+                                 int basic_head, void* stream) {
+  int rc = check_common("acx_value_forward", critic, ob_dim, 1, rows, n, obs);
+  if (rc) return rc;
+  if (rows == 0 || n == 0) return ACX_OK;
+  ACX_REQUIRE(v_out, "acx_value_forward: v_out is null");
+  Args a; memset(&a, 0, sizeof(a));
+  a.params = critic; a.L = acx_critic_layout(ob_dim); a.rows = rows; a.n = n; a.obs = obs;
+  a.v_out = v_out; a.basic_head = basic_head;
+  return launch<256, 128, false, HEAD_VALUE, MODE_EVAL>(a, tile_grid(rows, n), (cudaStream_t)stream);
+}
+
+extern "C" size_t acx_loss_backward_workspace_bytes(int ob_dim, int num_ac, int cont) {
+  const size_t sms = (size_t)acx_num_sms();
+  const size_t pa = (size_t)acx_actor_layout(ob_dim, num_ac, cont).size, pc = (size_t)acx_critic_layout(ob_dim).size;
+  return sms * (pa + pc) * sizeof(float) + 2 * sms * 4 * sizeof(double) + 256;
+}
+
+static int loss_backward(int cont, const float* actor, const float* critic, int ob_dim, int num_ac, float ac_scale,
+                         int rows, int n, const float* obs, const void* acs, const float* adv, const float* adv_stats,
+                         const float* logp_old, const float* targets, const float* opt, float* grad_actor,
+                         float* grad_critic, float* stats, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  const char* fn = cont ? "acx_loss_backward_gauss" : "acx_loss_backward_cat";
+  ACX_REQUIRE(actor || critic, "%s: neither actor nor critic given", fn);
+  ACX_REQUIRE(rows >= 1 && n >= 1, "%s: empty batch (rows=%d, n=%d): the mean loss is undefined", fn, rows, n);
+  ACX_REQUIRE(workspace && workspace_bytes >= acx_loss_backward_workspace_bytes(ob_dim, num_ac, cont),
+              "%s: workspace too small (%zu < %zu)", fn, workspace_bytes,
+              acx_loss_backward_workspace_bytes(ob_dim, num_ac, cont));
+  ACX_REQUIRE(acx_aligned16(workspace), "%s: workspace must be 16-byte aligned", fn);
+  const int sms = acx_num_sms();
+  const int grid = tile_grid(rows, n);
+  const AcxNetLayout La = acx_actor_layout(ob_dim, num_ac, cont), Lc = acx_critic_layout(ob_dim);
+  unsigned char* wsb = reinterpret_cast<unsigned char*>(workspace);
+  double* lossp_a = reinterpret_cast<double*>(wsb);
+  double* lossp_c = lossp_a + (size_t)sms * 4;
+  float* scr_a = reinterpret_cast<float*>(wsb + 2 * (size_t)sms * 4 * sizeof(double) + 128);
+  float* scr_c = scr_a + (size_t)sms * La.size;
+  const double count = (double)rows * (double)n;
+  if (actor) {
+    int rc = check_common(fn, actor, ob_dim, num_ac, rows, n, obs);
+    if (rc) return rc;
+    ACX_REQUIRE(acs && adv && logp_old && opt && grad_actor, "%s: null actor-side buffer", fn);
+    Args a; memset(&a, 0, sizeof(a));
+    a.params = actor; a.L = La; a.rows = rows; a.n = n; a.obs = obs; a.ac_scale = ac_scale;
+    a.ac_in_f = cont ? reinterpret_cast<const float*>(acs) : nullptr;
+    a.ac_in_i = cont ? nullptr : reinterpret_cast<const int*>(acs);
+    a.adv = adv; a.adv_stats = adv_stats; a.logp_old = logp_old; a.opt = opt;
+    a.scratch = scr_a; a.loss_partial = lossp_a;
+    rc = cont ? launch<128, 64, true, HEAD_GAUSS, MODE_TRAIN>(a, grid, st)
+              : launch<128, 64, true, HEAD_CAT, MODE_TRAIN>(a, grid, st);
+    if (rc) return rc;
+    acx_grad_reduce_kernel<<<(La.size + 255) / 256, 256, 0, st>>>(scr_a, grid, La.size, grad_actor, lossp_a, stats, opt,
+                                                                 1, count);
+    ACX_LAUNCH_OK("acx_grad_reduce_kernel(actor)");
+  }
+  if (critic) {
+    int rc = check_common(fn, critic, ob_dim, 1, rows, n, obs);
+    if (rc) return rc;
+    ACX_REQUIRE(targets && grad_critic, "%s: null critic-side buffer", fn);
+    Args a; memset(&a, 0, sizeof(a));
+    a.params = critic; a.L = Lc; a.rows = rows; a.n = n; a.obs = obs;
+    a.targets = targets; a.scratch = scr_c; a.loss_partial = lossp_c;
+    rc = launch<256, 128, false, HEAD_VALUE, MODE_TRAIN>(a, grid, st);
+    if (rc) return rc;
+    acx_grad_reduce_kernel<<<(Lc.size + 255) / 256, 256, 0, st>>>(scr_c, grid, Lc.size, grad_critic, lossp_c, stats,
+                                                                 opt, 0, count);
+    ACX_LAUNCH_OK("acx_grad_reduce_kernel(critic)");
+  }
+  return ACX_OK;
+}
+
+extern "C" int acx_loss_backward_gauss(const float* actor, const float* critic, int ob_dim, int ac_dim, float ac_scale,
+                                       int rows, int n, const float* obs, const float* acs, const float* adv,
+                                       const float* adv_stats, const float* logp_old, const float* targets,
+                                       const float* opt, float* grad_actor, float* grad_critic, float* stats,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+  return loss_backward(1, actor, critic, ob_dim, ac_dim, ac_scale, rows, n, obs, acs, adv, adv_stats, logp_old,
+                       targets, opt, grad_actor, grad_critic, stats, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int acx_loss_backward_cat(const float* actor, const float* critic, int ob_dim, int n_act, int rows, int n,
+                                     const float* obs, const int* acs, const float* adv, const float* adv_stats,
+                                     const float* logp_old, const float* targets, const float* opt, float* grad_actor,
+                                     float* grad_critic, float* stats, void* workspace, size_t workspace_bytes,
+                                     void* stream) {
+  return loss_backward(0, actor, critic, ob_dim, n_act, 0.f, rows, n, obs, acs, adv, adv_stats, logp_old, targets,
+                       opt, grad_actor, grad_critic, stats, workspace, workspace_bytes, (cudaStream_t)stream);
+}

@@ -1,0 +1,259 @@
+// K3 -- windowed discounted-return / advantage scan over the rollout horizon, with the
+// batch moments needed for advantage normalisation.
+//
+// Replaces PathAdv.__call__ (A3C/process.py:54-66 == Basic_AC/run_AC.py:63-75) and the
+// moments of A3C/process.py:247.  Buffers are time-major [T][N]; done[t][n] = 1 closes an
+// episode segment (terminal, no bootstrap); the tail segment of a column is cut by the
+// horizon and bootstraps from V[T] (the reference's max_path_length cut, process.py:63).
+//
+//   S_t   = r_t + gamma * (done_t ? 0 : S_{t+1})                    (segment suffix sum)
+//   e_t   = exclusive end of the segment that contains t
+//   t+L <  e_t :  G_t = S_t - gamma^L S_{t+L} + gamma^L V[t+L]      (window cut inside the segment)
+//   t+L >= e_t :  G_t = S_t + (terminal ? 0 : gamma^(e_t - t) V[e_t])
+//   adv_t = G_t - V[t]
+//
+// Two kernels compute the same thing:
+//   * acx_scan_cols_kernel   one thread per env column, serial in time, loads coalesced over
+//                            the env axis -- the HBM-bound path for wide batches (17 B/sample);
+//   * acx_scan_warp_kernel   one warp per column, a warp-level segmented (affine) scan over
+//                            time with shuffles -- for few, long columns (the reference's own
+//                            shape: 1 env x ~1200 steps).
+// Recurrences run in fp64 like the reference's numpy code.
+#include "acx_common.cuh"
+
+struct ScanWs {              // caller-provided workspace, see acx_returns_adv_workspace_bytes
+  unsigned int ticket;       // self-resetting "last block" counter (must be 0 before the first call)
+  unsigned int pad[3];
+  double partial[1];         // [2 * grid]
+};
+
+__device__ inline void scan_finish_moments(double s, double q, ScanWs* ws, float* stats, long long count) {
+  // block reduce (fixed order) -> partials -> last block folds them in index order: deterministic
+  __shared__ double sh[2][8];
+  __shared__ bool last;
+  s = acx_warp_sum_d(s);
+  q = acx_warp_sum_d(q);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) { sh[0][w] = s; sh[1][w] = q; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0, b = 0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { a += sh[0][i]; b += sh[1][i]; }
+    ws->partial[2 * blockIdx.x] = a;
+    ws->partial[2 * blockIdx.x + 1] = b;
+    __threadfence();
+    last = (atomicAdd(&ws->ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (last && threadIdx.x == 0) {
+    __threadfence();
+    double a = 0, b = 0;
+    for (unsigned i = 0; i < gridDim.x; ++i) {
+      a += ((volatile double*)ws->partial)[2 * i];
+      b += ((volatile double*)ws->partial)[2 * i + 1];
+    }
+    const double mean = a / (double)count;
+    double var = b / (double)count - mean * mean;
+    if (var < 0) var = 0;
+    stats[0] = (float)mean;
+    stats[1] = (float)(1.0 / (1e-8 + sqrt(var)));      // A3C/process.py:247
+    stats[2] = (float)sqrt(var);
+    ws->ticket = 0;
+  }
+}
+
+constexpr int SCAN_CHUNK = 8;
+
+__global__ void __launch_bounds__(256) acx_scan_cols_kernel(int T, int N, const float* __restrict__ rew,
+                                                            const unsigned char* __restrict__ done,
+                                                            const float* __restrict__ V, double gamma, int L,
+                                                            float* __restrict__ G, float* __restrict__ adv,
+                                                            ScanWs* ws, float* __restrict__ stats) {
+  double msum = 0, msq = 0;
+  const double gL = pow(gamma, (double)L);
+  for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+    const bool windowed = T > L;
+    // ---- reverse pass: S_t (and, when the window can cut a segment, e_t)
+    double carry = 0.0;           // S_{t+1} within the segment, 0 past its end
+    double boot = (double)V[(size_t)T * N + n];   // gamma-discounted bootstrap carried along (plain mode)
+    int e = T;
+    for (int t1 = T; t1 > 0; t1 -= SCAN_CHUNK) {
+      const int cnt = t1 < SCAN_CHUNK ? t1 : SCAN_CHUNK;
+      float r[SCAN_CHUNK], v[SCAN_CHUNK];
+      unsigned char d[SCAN_CHUNK];
+#pragma unroll
+      for (int i = 0; i < SCAN_CHUNK; ++i) {
+        if (i < cnt) {
+          const size_t off = (size_t)(t1 - 1 - i) * N + n;
+          r[i] = __ldg(rew + off); d[i] = __ldg(done + off); v[i] = __ldg(V + off);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < SCAN_CHUNK; ++i) {
+        if (i < cnt) {
+          const int t = t1 - 1 - i;
+          const size_t off = (size_t)t * N + n;
+          if (d[i]) { carry = 0.0; boot = 0.0; e = t + 1; }
+          if (!windowed) {
+            // G_t = r_t + gamma * G_{t+1}, with G_{e} = V[e] for a horizon-cut tail, 0 after a terminal
+            carry = (double)r[i] + gamma * (carry + boot);
+            boot = 0.0;
+            const float g = (float)carry, a = (float)(carry - (double)v[i]);
+            G[off] = g; adv[off] = a;
+            msum += (double)a; msq += (double)a * (double)a;
+          } else {
+            carry = (double)r[i] + gamma * carry;
+            G[off] = (float)carry;
+            reinterpret_cast<int*>(adv)[off] = e;
+          }
+        }
+      }
+    }
+    if (windowed) {
+      // ---- forward fix-up, in place: S_{t+L} is read before its own slot is rewritten
+      for (int t = 0; t < T; ++t) {
+        const size_t off = (size_t)t * N + n;
+        const int et = reinterpret_cast<const int*>(adv)[off];
+        double g = (double)G[off];
+        if (t + L < et) {
+          g += gL * ((double)V[(size_t)(t + L) * N + n] - (double)G[(size_t)(t + L) * N + n]);
+        } else {
+          const bool terminal = done[(size_t)(et - 1) * N + n] != 0;
+          if (!terminal) g += pow(gamma, (double)(et - t)) * (double)V[(size_t)et * N + n];
+        }
+        const float a = (float)(g - (double)V[off]);
+        G[off] = (float)g; adv[off] = a;
+        msum += (double)a; msq += (double)a * (double)a;
+      }
+    }
+  }
+  scan_finish_moments(msum, msq, ws, stats, (long long)T * N);
+}
+
+// affine element of the reverse recurrence x_t = b + a * x_{t+1}; `e` rides along as a min-scan
+struct Aff { double a, b; int e; };
+__device__ inline Aff aff_combine(const Aff& lo, const Aff& hi) {   // lo is earlier in time, applied last
+  Aff o; o.a = lo.a * hi.a; o.b = lo.b + lo.a * hi.b; o.e = lo.e < hi.e ? lo.e : hi.e;
+  return o;
+}
+
+__global__ void __launch_bounds__(256) acx_scan_warp_kernel(int T, int N, const float* __restrict__ rew,
+                                                            const unsigned char* __restrict__ done,
+                                                            const float* __restrict__ V, double gamma, int L,
+                                                            float* __restrict__ G, float* __restrict__ adv,
+                                                            ScanWs* ws, float* __restrict__ stats) {
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  double msum = 0, msq = 0;
+  const double gL = pow(gamma, (double)L);
+  const bool windowed = T > L;
+  for (int n = blockIdx.x * warps_per_block + (threadIdx.x >> 5); n < N; n += gridDim.x * warps_per_block) {
+    // carry from later time: value of S (or G) just after the current 32-step block, and its segment end
+    double carry = windowed ? 0.0 : (double)V[(size_t)T * N + n];
+    int carry_e = T;
+    for (int hi = T; hi > 0; hi -= 32) {
+      const int t = hi - 1 - lane;            // lane 0 holds the latest step of the block
+      Aff x; x.a = 1.0; x.b = 0.0; x.e = 0x7fffffff;
+      float v = 0.f;
+      if (t >= 0) {
+        const size_t off = (size_t)t * N + n;
+        const bool d = done[off] != 0;
+        x.a = d ? 0.0 : gamma; x.b = (double)rew[off]; x.e = d ? t + 1 : 0x7fffffff;
+        v = V[off];
+      }
+      // inclusive scan toward later time: after it, lane k holds steps t_k .. hi-1 composed
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        Aff y;
+        y.a = __shfl_up_sync(0xffffffffu, x.a, o);
+        y.b = __shfl_up_sync(0xffffffffu, x.b, o);
+        y.e = __shfl_up_sync(0xffffffffu, x.e, o);
+        if (lane >= o) x = aff_combine(x, y);
+      }
+      const double val = x.b + x.a * carry;
+      const int e = x.e < carry_e ? x.e : carry_e;
+      if (t >= 0) {
+        const size_t off = (size_t)t * N + n;
+        if (!windowed) {
+          const float a = (float)(val - (double)v);
+          G[off] = (float)val; adv[off] = a;
+          msum += (double)a; msq += (double)a * (double)a;
+        } else {
+          G[off] = (float)val;
+          reinterpret_cast<int*>(adv)[off] = e;
+        }
+      }
+      // new carry = value at the earliest step of this block (highest active lane)
+      const int src = (hi >= 32) ? 31 : hi - 1;
+      carry = __shfl_sync(0xffffffffu, val, src);
+      carry_e = __shfl_sync(0xffffffffu, e, src);
+    }
+    if (windowed) {
+      __syncwarp();
+      __threadfence_block();
+      // S_{t+L} must be read for the whole 32-step block before any slot of it is rewritten
+      for (int lo = 0; lo < T; lo += 32) {
+        const int t = lo + lane;
+        double g = 0; float a = 0; bool live = t < T;
+        if (live) {
+          const size_t off = (size_t)t * N + n;
+          const int et = reinterpret_cast<const int*>(adv)[off];
+          g = (double)G[off];
+          if (t + L < et) {
+            g += gL * ((double)V[(size_t)(t + L) * N + n] - (double)G[(size_t)(t + L) * N + n]);
+          } else {
+            const bool terminal = done[(size_t)(et - 1) * N + n] != 0;
+            if (!terminal) g += pow(gamma, (double)(et - t)) * (double)V[(size_t)et * N + n];
+          }
+          a = (float)(g - (double)V[off]);
+        }
+        __syncwarp();
+        if (live) {
+          const size_t off = (size_t)t * N + n;
+          G[off] = (float)g; adv[off] = a;
+          msum += (double)a; msq += (double)a * (double)a;
+        }
+        __syncwarp();
+        __threadfence_block();
+      }
+    }
+  }
+  scan_finish_moments(msum, msq, ws, stats, (long long)T * N);
+}
+
+static int scan_grid(int N, int mode) {
+  int g = mode == 1 ? (N + 7) / 8 : (N + 255) / 256;
+  int cap = acx_num_sms() * 8;
+  if (g > cap) g = cap;
+  return g < 1 ? 1 : g;
+}
+
+extern "C" size_t acx_returns_adv_workspace_bytes(int T, int n) {
+  (void)T; (void)n;
+  return sizeof(ScanWs) + sizeof(double) * 2 * (size_t)(148 * 8 + 64);
+}
+
+extern "C" int acx_returns_adv_scan(int T, int n, const float* rew, const unsigned char* done, const float* V,
+                                    double gamma, int look_ahead, float* G_out, float* adv_out, float* stats_out,
+                                    void* workspace, size_t workspace_bytes, int mode, void* stream) {
+  ACX_REQUIRE(T >= 0 && n >= 0, "acx_returns_adv_scan: negative size (T=%d, n=%d)", T, n);
+  ACX_REQUIRE(look_ahead >= 1, "acx_returns_adv_scan: look_ahead must be >= 1 (got %d)", look_ahead);
+  if (T == 0 || n == 0) return ACX_OK;
+  ACX_REQUIRE(rew && done && V && G_out && adv_out && stats_out && workspace, "acx_returns_adv_scan: null buffer");
+  ACX_REQUIRE(workspace_bytes >= acx_returns_adv_workspace_bytes(T, n),
+              "acx_returns_adv_scan: workspace too small (%zu < %zu)", workspace_bytes,
+              acx_returns_adv_workspace_bytes(T, n));
+  ACX_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 15u) == 0, "acx_returns_adv_scan: workspace must be 16-byte aligned");
+  if (mode == ACX_SCAN_AUTO) mode = (n < 2048 && T >= 64) ? ACX_SCAN_WARP : ACX_SCAN_COLS;
+  ACX_REQUIRE(mode == ACX_SCAN_COLS || mode == ACX_SCAN_WARP, "acx_returns_adv_scan: bad mode %d", mode);
+  cudaStream_t st = (cudaStream_t)stream;
+  ScanWs* ws = reinterpret_cast<ScanWs*>(workspace);
+  if (mode == ACX_SCAN_WARP)
+    acx_scan_warp_kernel<<<scan_grid(n, 1), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out,
+                                                         adv_out, ws, stats_out);
+  else
+    acx_scan_cols_kernel<<<scan_grid(n, 0), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out,
+                                                         adv_out, ws, stats_out);
+  ACX_LAUNCH_OK("acx_scan kernel");
+  return ACX_OK;
+}

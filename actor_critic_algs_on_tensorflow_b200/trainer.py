@@ -1,0 +1,279 @@
+"""Fused rollout + update loop on one B200 (one process per GPU), the body of the reference's
+outer ``while`` loop (``A3C/process.py:217-285``; ``Basic_AC/run_AC.py:208-284``) for N
+environments x T steps per update instead of ~6 whole episodes:
+
+    rollout      T x { acx_policy_forward_sample_*  ->  acx_env_step }     process.py:86-96
+    values       acx_value_forward on the T+1 observation rows             process.py:229
+    returns      acx_returns_adv_scan (+ batch moments)                    process.py:230,247
+    gradients    acx_loss_backward_*                                       process.py:257-258
+    [NCCL all-reduce of the flat gradient, world > 1]                      replaces ps push/pull
+    update       acx_adam_apply, acx_adam_tick                             policies.py:88-89,160-161
+    lr control   acx_policy_logp_* + acx_kl_finalize + acx_kl_lr_update    process.py:262-278
+
+Everything stays on the device; the whole iteration is captured into CUDA graphs (the RNG step
+counter lives in device memory so replays draw fresh noise).  PyTorch only provides device
+memory, streams and torch.distributed.  No CPU fallback.
+
+Multi-GPU (``world > 1``): environments are sharded by rank (index0 = rank * N keeps the Philox
+streams disjoint, mirroring seed+task of ``A3C/train.py:40``); parameters, Adam moments and the
+opt block are replicated.  ``mode='sync'`` is synchronous A2C: all-reduce(sum) of the flat
+gradient, x 1/world, clip, one identical Adam step on every rank, KL averaged over ranks.
+``mode='async'`` mirrors the reference's parameter-server semantics (per-worker clip, per-worker
+Adam moments and lr applied to shared parameters, then pull -- ``A3C/policies.py:85-98``,
+``A3C/process.py:257-260``): every rank applies its own clipped gradient with its own moments to
+the iteration-start parameters (stale by one push, as on the ps) and the parameter *deltas* are
+summed over ranks, i.e. every worker's push lands before the pull.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+ENV_IDS = {"Pendulum-v0": L.ENV_PENDULUM, "CartPole-v0": L.ENV_CARTPOLE, "Acrobot-v1": L.ENV_ACROBOT}
+
+
+def env_dims(env):
+    s, o, a, m = (ctypes.c_int() for _ in range(4))
+    L.call("acx_env_dims", env, ctypes.byref(s), ctypes.byref(o), ctypes.byref(a), ctypes.byref(m))
+    return s.value, o.value, a.value, m.value
+
+
+def glorot_flat(net, ob_dim, num_ac, cont, gen):
+    """xavier-uniform kernels, zero biases, log_std = 0 (A3C/policies.py:7,44-52) in the flat layout."""
+    lay, total = L.params_layout(net, ob_dim, num_ac, cont)
+    flat = np.zeros(total, dtype=np.float32)
+    fan = {"W1": (ob_dim, None), "W2": None, "W3": None, "Wh": None}
+    h = (128, 128, 64) if net == 0 else (256, 128, 128)
+    shapes = {"W1": (ob_dim, h[0]), "W2": (h[0], h[1]), "W3": (h[1], h[2]), "Wh": (h[2], num_ac if net == 0 else 1)}
+    for k, (fi, fo) in shapes.items():
+        lim = np.sqrt(6.0 / (fi + fo))
+        off, size = lay[k]
+        flat[off:off + size] = gen.uniform(-lim, lim, size=size)
+    del fan
+    return flat
+
+
+class A2CTrainer:
+    def __init__(self, env_id="Pendulum-v0", n_envs=65536, horizon=20, seed=12321, gamma=0.98, look_ahead=40,
+                 desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1, actor_lr=0.005, critic_lr=0.001, beta=1.0,
+                 gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
+                 critic_params=None, use_graph=True, max_episode_steps=0, process_group=None):
+        if not torch.cuda.is_available():
+            raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
+        L.load()
+        self.env = ENV_IDS[env_id] if isinstance(env_id, str) else int(env_id)
+        self.S, self.ob, self.n_act, default_max = env_dims(self.env)
+        self.cont = self.n_act == 0
+        self.num_ac = 1 if self.cont else self.n_act
+        self.ac_scale = 2.0                       # max(|low|, high) of Pendulum (A3C/process.py:186)
+        self.N, self.T = int(n_envs), int(horizon)
+        self.seed, self.rank, self.world, self.mode = int(seed), int(rank), int(world), mode
+        assert mode in ("sync", "async")
+        self.gamma, self.look_ahead = float(gamma), int(look_ahead)
+        self.max_steps = int(max_episode_steps) or default_max
+        self.dev = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
+        self.pg = process_group
+        self.use_graph = bool(use_graph)
+        d, f32 = self.dev, torch.float32
+        N, T = self.N, self.T
+
+        _, self.Pa = L.params_layout(0, self.ob, self.num_ac, self.cont)
+        _, self.Pc = L.params_layout(1, self.ob)
+        gen = np.random.default_rng(self.seed)
+        a0 = glorot_flat(0, self.ob, self.num_ac, self.cont, gen) if actor_params is None else np.asarray(actor_params)
+        c0 = glorot_flat(1, self.ob, 1, False, gen) if critic_params is None else np.asarray(critic_params)
+        assert a0.size == self.Pa and c0.size == self.Pc, "flat parameter size mismatch"
+        P = self.Pa + self.Pc
+        self.params = torch.empty(P, device=d, dtype=f32)
+        self.params[:self.Pa] = torch.from_numpy(a0.astype(np.float32)).to(d)
+        self.params[self.Pa:] = torch.from_numpy(c0.astype(np.float32)).to(d)
+        self.actor, self.critic = self.params[:self.Pa], self.params[self.Pa:]
+        self.m = torch.zeros(P, device=d, dtype=f32)
+        self.v = torch.zeros(P, device=d, dtype=f32)
+        self.grads = torch.zeros(P, device=d, dtype=f32)
+        self.old_params = torch.empty(P, device=d, dtype=f32) if mode == "async" else None
+
+        self.state = torch.empty((self.S, N), device=d, dtype=f32)
+        self.elapsed = torch.zeros(N, device=d, dtype=torch.int32)
+        self.obs_buf = torch.empty((T + 1, self.ob, N), device=d, dtype=f32)
+        self.acs = (torch.empty((T, self.num_ac, N), device=d, dtype=f32) if self.cont
+                    else torch.empty((T, N), device=d, dtype=torch.int32))
+        self.logps = torch.empty((T, N), device=d, dtype=f32)
+        self.ent = torch.empty((T, N), device=d, dtype=f32)
+        self.rew = torch.empty((T, N), device=d, dtype=f32)
+        self.done = torch.empty((T, N), device=d, dtype=torch.uint8)
+        self.V = torch.empty((T + 1, N), device=d, dtype=f32)
+        self.G = torch.empty((T, N), device=d, dtype=f32)
+        self.adv = torch.empty((T, N), device=d, dtype=f32)
+        self.stats = torch.zeros(L.STATS_SIZE, device=d, dtype=f32)
+        self.opt = torch.zeros(L.OPT_SIZE, device=d, dtype=f32)
+        self.step_ctr = torch.zeros(1, device=d, dtype=torch.int32)
+        self.ws_scan_bytes = L.load().acx_returns_adv_workspace_bytes(T, N)
+        self.ws_scan = torch.zeros(self.ws_scan_bytes, device=d, dtype=torch.uint8)
+        self.ws_bwd_bytes = L.load().acx_loss_backward_workspace_bytes(self.ob, self.num_ac, int(self.cont))
+        self.ws_bwd = torch.empty(self.ws_bwd_bytes, device=d, dtype=torch.uint8)
+        self.kl_part = torch.zeros(L.load().acx_kl_workspace_bytes() // 8, device=d, dtype=torch.float64)
+        self.kl_blocks = ctypes.c_int(0)
+        # optional caller-supplied noise (parity / end-to-end mode), static so graphs can replay on them
+        self.noise_buf = None
+        self.reset_u_buf = None
+        self.index0 = self.rank * N
+        self.iterations = 0
+        self._graphs = {}
+        self.launches_per_iteration = 0
+
+        s = L.cur_stream()
+        L.call("acx_opt_init", L.ptr(self.opt), actor_lr, critic_lr, beta, gamma_ent, clip, desired_kl, min_lr, max_lr,
+               int(bool(schedule)), s)
+        L.call("acx_env_reset", self.env, N, L.ptr(self.state), L.ptr(self.elapsed), L.ptr(self.obs_buf[0]), None,
+               self.seed, self.index0, 0xFFFFFFFF, s)
+
+    # ------------------------------------------------------------------ pieces (all enqueue on the current stream)
+    def _row(self, t, i):      # pointer to row i of a [rows, ...] tensor
+        return t.data_ptr() + i * t.stride(0) * t.element_size()
+
+    def _rollout(self, buffered_noise):
+        s, N = L.cur_stream(), self.N
+        n = 0
+        for t in range(self.T):
+            noise = None if not buffered_noise else self._row(self.noise_buf, t)
+            ru = None if not buffered_noise else self._row(self.reset_u_buf, t)
+            if self.cont:
+                L.call("acx_policy_forward_sample_gauss", L.ptr(self.actor), self.ob, self.num_ac, self.ac_scale, 1, N,
+                       self._row(self.obs_buf, t), noise, self.seed, self.index0, t, L.ptr(self.step_ctr),
+                       self._row(self.acs, t), self._row(self.logps, t), self._row(self.ent, t), None, s)
+            else:
+                L.call("acx_policy_forward_sample_cat", L.ptr(self.actor), self.ob, self.n_act, 1, N,
+                       self._row(self.obs_buf, t), noise, self.seed, self.index0, t, L.ptr(self.step_ctr),
+                       self._row(self.acs, t), self._row(self.logps, t), self._row(self.ent, t), None, s)
+            L.call("acx_env_step", self.env, N, L.ptr(self.state), L.ptr(self.elapsed), self._row(self.acs, t),
+                   self._row(self.obs_buf, t + 1), self._row(self.rew, t), self._row(self.done, t), ru, self.seed,
+                   self.index0, t, L.ptr(self.step_ctr), self.max_steps, s)
+            n += 2
+        L.call("acx_counter_add", L.ptr(self.step_ctr), self.T, s)
+        return n + 1
+
+    def _gradients(self):
+        s, N, T = L.cur_stream(), self.N, self.T
+        L.call("acx_value_forward", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V), 0, s)
+        L.call("acx_returns_adv_scan", T, N, L.ptr(self.rew), L.ptr(self.done), L.ptr(self.V), self.gamma,
+               self.look_ahead, L.ptr(self.G), L.ptr(self.adv), L.ptr(self.stats), L.ptr(self.ws_scan),
+               self.ws_scan_bytes, L.SCAN_AUTO, s)
+        ga, gc = self.grads[:self.Pa], self.grads[self.Pa:]
+        common = (L.ptr(self.obs_buf), L.ptr(self.acs), L.ptr(self.adv), L.ptr(self.stats), L.ptr(self.logps),
+                  L.ptr(self.G), L.ptr(self.opt), L.ptr(ga), L.ptr(gc), L.ptr(self.stats), L.ptr(self.ws_bwd),
+                  self.ws_bwd_bytes, s)
+        if self.cont:
+            L.call("acx_loss_backward_gauss", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.num_ac,
+                   self.ac_scale, T, N, *common)
+        else:
+            L.call("acx_loss_backward_cat", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.n_act, T, N, *common)
+        return 2 + 4
+
+    def _apply(self, grad_scale):
+        s, Pa, Pc = L.cur_stream(), self.Pa, self.Pc
+        L.call("acx_adam_apply", L.ptr(self.actor), L.ptr(self.grads[:Pa]), L.ptr(self.m[:Pa]), L.ptr(self.v[:Pa]), Pa,
+               L.ptr(self.critic), L.ptr(self.grads[Pa:]), L.ptr(self.m[Pa:]), L.ptr(self.v[Pa:]), Pc, L.ptr(self.opt),
+               grad_scale, s)
+        L.call("acx_adam_tick", L.ptr(self.opt), s)
+        return 2
+
+    def _post_kl(self):
+        s, N, T = L.cur_stream(), self.N, self.T
+        if self.cont:
+            L.call("acx_policy_logp_gauss", L.ptr(self.actor), self.ob, self.num_ac, self.ac_scale, T, N,
+                   L.ptr(self.obs_buf), L.ptr(self.acs), None, None, None, L.ptr(self.logps), L.ptr(self.kl_part),
+                   ctypes.byref(self.kl_blocks), s)
+        else:
+            L.call("acx_policy_logp_cat", L.ptr(self.actor), self.ob, self.n_act, T, N, L.ptr(self.obs_buf),
+                   L.ptr(self.acs), None, None, None, L.ptr(self.logps), L.ptr(self.kl_part),
+                   ctypes.byref(self.kl_blocks), s)
+        L.call("acx_kl_finalize", L.ptr(self.kl_part), self.kl_blocks.value, float(T) * float(N), L.ptr(self.stats), s)
+        return 2
+
+    def _lr_update(self):
+        L.call("acx_kl_lr_update", L.ptr(self.opt), L.ptr(self.stats), L.cur_stream())
+        return 1
+
+    # ------------------------------------------------------------------ segments + graphs
+    def _seg_a(self, buffered):
+        self.obs_buf[0].copy_(self.obs_buf[self.T]) if self.iterations_started else None
+        return self._rollout(buffered) + self._gradients() + 1
+
+    def _run(self, key, fn):
+        """Run fn() on the current stream, through a CUDA graph after the first (eager, warm-up) call."""
+        if not self.use_graph:
+            return fn()
+        ent = self._graphs.get(key)
+        if ent is None:
+            n = fn()                                   # eager warm-up (also sets lazily configured attributes)
+            self._graphs[key] = [n, 1, None]
+            return n
+        if ent[2] is None:
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn()
+            ent[2] = g
+        ent[2].replay()
+        return ent[0]
+
+    def _allreduce(self, t, average=False):
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.pg)
+        if average:
+            t.mul_(1.0 / self.world)
+
+    iterations_started = False
+
+    def iteration(self, noise=None, reset_u=None):
+        """One rollout + update.  ``noise``/``reset_u``: optional DEVICE tensors [T, ac, N] (normals) or
+        [T, N] (uniforms) and [T, S, N]; default is the device Philox stream."""
+        buffered = noise is not None
+        if buffered:
+            if self.noise_buf is None:
+                self.noise_buf = torch.empty_like(noise, device=self.dev)
+                self.reset_u_buf = torch.empty((self.T, self.S, self.N), device=self.dev, dtype=torch.float32)
+            self.noise_buf.copy_(noise, non_blocking=True)
+            self.reset_u_buf.copy_(reset_u, non_blocking=True)
+        tag = "buf" if buffered else "rng"
+        if not self.iterations_started:
+            # first iteration: obs_buf[0] already holds the reset observations
+            n = self._rollout(buffered) + self._gradients()
+            self.iterations_started = True
+        else:
+            n = self._run("a_" + tag, lambda: self._seg_a(buffered))
+        if self.world == 1:
+            n += self._run("b1", lambda: self._apply(1.0) + self._post_kl() + self._lr_update())
+        elif self.mode == "sync":
+            self._allreduce(self.grads)
+            n += self._run("b", lambda: self._apply(1.0 / self.world) + self._post_kl())
+            self._allreduce(self.stats[L.STAT_KL_POST:L.STAT_KL_POST + 1], average=True)
+            n += self._run("c", self._lr_update)
+        else:   # async: stale-gradient pushes onto shared parameters, then pull
+            self.old_params.copy_(self.params)
+            n += self._run("b", lambda: self._apply(1.0))
+            self.params.sub_(self.old_params)                      # this worker's delta
+            self._allreduce(self.params)                           # every worker's push lands
+            self.params.add_(self.old_params)                      # pull
+            n += self._run("c", lambda: self._post_kl() + self._lr_update())
+        self.iterations += 1
+        self.launches_per_iteration = n
+        return n
+
+    # ------------------------------------------------------------------ host-side views (synchronise)
+    def read_stats(self):
+        """Device -> host copy of the stats/opt blocks as a dict (the values the reference logs)."""
+        st = self.stats.cpu().numpy()
+        op = self.opt.cpu().numpy()
+        return dict(act_loss=float(st[L.STAT_ACTOR_LOSS]), crit_loss=float(st[L.STAT_CRITIC_LOSS]),
+                    kl_dist=float(st[L.STAT_KL_POST]), kl_pre=float(st[L.STAT_KL_PRE]),
+                    avg_ent=float(st[L.STAT_ENT_MEAN]), act_lr=float(st[L.STAT_ACTOR_LR_USED]),
+                    next_lr=float(op[L.OPT_ACTOR_LR]), beta=float(op[L.OPT_BETA_KL]),
+                    gamma_ent=float(op[L.OPT_GAMMA_ENT]), adv_mean=float(st[L.STAT_ADV_MEAN]),
+                    adv_std=float(st[L.STAT_ADV_STD]), iteration=int(op[L.OPT_ITER]), adam_t=int(op[L.OPT_ADAM_T]))
+
+    def env_steps_per_iteration(self):
+        return self.N * self.T

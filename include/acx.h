@@ -1,0 +1,199 @@
+/* libacx -- C ABI of the B200-native actor-critic hot path.
+ *
+ * The reference (renly/Actor-Critic-Algs-on-Tensorflow) has no FFI of its own: its hot
+ * path is Python calling TensorFlow 1.3 sessions and gym.  This header is the boundary a
+ * maintainer binds instead (INTEGRATION.md shows the ctypes stub); every entry point cites
+ * the reference code it replaces.  Host code above this ABI lives in
+ * actor_critic_algs_on_tensorflow_b200/ and mirrors the reference's Python interface.
+ *
+ * Conventions
+ *   - plain C types only; every pointer is a DEVICE pointer unless stated otherwise;
+ *   - nothing is allocated, freed or synchronised inside: the caller owns every buffer,
+ *     including workspaces whose size comes from the matching *_workspace_bytes();
+ *   - `stream` is a cudaStream_t passed as void*; all work is stream-ordered on it;
+ *   - return value: ACX_OK (0) or a negative ACX_ERR_*; acx_last_error() (thread-local)
+ *     gives the message;
+ *   - batches are structure-of-arrays: obs[rows][ob_dim][n], actions[rows][ac_dim][n] (float)
+ *     or [rows][n] (int32), per-sample scalars [rows][n]; rollout buffers are time-major
+ *     [T][n];
+ *   - network parameters are ONE flat fp32 buffer per network, 16-byte aligned, laid out by
+ *     acx_params_layout() (kernels [in][out] row-major as in the TF checkpoint);
+ *   - device RNG: Philox4x32-10, counter (index0 + column, step0 + row, stream id), key = seed;
+ *     `step_base` (nullable DEVICE pointer to one uint32) is added to the step, so that a
+ *     captured CUDA graph can be replayed with fresh randomness (acx_counter_add advances it).
+ */
+#ifndef ACX_H_
+#define ACX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ACX_ABI_VERSION 1
+
+#define ACX_OK 0
+#define ACX_ERR_INVALID (-1)   /* bad argument (null pointer, size, alignment) */
+#define ACX_ERR_CUDA (-2)      /* a CUDA runtime call or launch failed */
+#define ACX_ERR_UNSUPPORTED (-3)
+
+#define ACX_ENV_PENDULUM 0     /* Pendulum-v0 */
+#define ACX_ENV_CARTPOLE 1     /* CartPole-v0 */
+#define ACX_ENV_ACROBOT 2      /* Acrobot-v1 */
+
+#define ACX_SCAN_AUTO 0
+#define ACX_SCAN_COLS 1        /* one thread per env column (wide batches) */
+#define ACX_SCAN_WARP 2        /* warp-level segmented scan over time (few long columns) */
+
+/* device "opt" block: float[ACX_OPT_SIZE] -- the non-trainable variables of
+ * A3C/policies.py:77-79,151 plus the Adam bookkeeping TF keeps in slot variables */
+#define ACX_OPT_SIZE 16
+#define ACX_OPT_ACTOR_LR 0
+#define ACX_OPT_CRITIC_LR 1
+#define ACX_OPT_BETA_KL 2
+#define ACX_OPT_GAMMA_ENT 3
+#define ACX_OPT_BETA1_POW 4    /* beta1^t, updated by repeated fp32 multiplication like TF */
+#define ACX_OPT_BETA2_POW 5
+#define ACX_OPT_CLIP 6         /* elementwise actor gradient clip (0.1 A3C, 1.0 Basic_AC); <=0: off */
+#define ACX_OPT_DESIRED_KL 7
+#define ACX_OPT_MIN_LR 8
+#define ACX_OPT_MAX_LR 9
+#define ACX_OPT_ITER 10        /* local iteration counter i (float, exact below 2^24) */
+#define ACX_OPT_SCHEDULE 11    /* != 0: apply the beta/gamma LinearSchedule on device */
+#define ACX_OPT_ADAM_T 12
+
+/* device "stats" block: float[ACX_STATS_SIZE] */
+#define ACX_STATS_SIZE 16
+#define ACX_STAT_ADV_MEAN 0
+#define ACX_STAT_ADV_INV_STD 1
+#define ACX_STAT_ADV_STD 2
+#define ACX_STAT_ACTOR_LOSS 3
+#define ACX_STAT_CRITIC_LOSS 4
+#define ACX_STAT_KL_PRE 5
+#define ACX_STAT_ENT_MEAN 6
+#define ACX_STAT_KL_POST 7
+#define ACX_STAT_REW_LOSS 8
+#define ACX_STAT_ACTOR_LR_USED 9
+
+int acx_abi_version(void);
+const char* acx_last_error(void);
+
+/* Flat parameter layout.  net: 0 = actor (A3C/policies.py:44-52,63), 1 = critic (:146-150).
+ * offsets[9] = {W1,b1,W2,b2,W3,b3,Whead,bhead,log_std(-1 if none)}, sizes[9] likewise (element
+ * counts); returns the padded total (floats) or a negative error.  Every tensor starts on a
+ * 4-float boundary.  HOST pointers. */
+int acx_params_layout(int net, int ob_dim, int num_ac, int cont, int* offsets, int* sizes);
+
+/* ---------------------------------------------------------------- K1: env step
+ * Replaces env.reset() / env.step(ac) -- A3C/process.py:79,91 (gym classic_control) -- for n
+ * envs.  state[S][n], elapsed[n] int32 are updated in place; obs_out[ob][n], rew_out[n],
+ * done_out[n] (uint8) are written.  Where done (termination or TimeLimit: elapsed >=
+ * max_steps, max_steps <= 0 -> gym's default) the env is reset at once and obs_out is the
+ * new episode's first observation.  reset_u[S][n] uniforms in [0,1) or NULL (Philox). */
+int acx_env_dims(int env, int* state_dim, int* obs_dim, int* n_actions, int* max_episode_steps);
+int acx_env_reset(int env, int n, float* state, int* elapsed, float* obs_out, const float* reset_u,
+                  uint64_t seed, uint64_t index0, uint32_t step, void* stream);
+int acx_env_step(int env, int n, float* state, int* elapsed, const void* action, float* obs_out,
+                 float* rew_out, unsigned char* done_out, const float* reset_u, uint64_t seed,
+                 uint64_t index0, uint32_t step, const uint32_t* step_base, int max_steps, void* stream);
+int acx_env_step_pendulum(int n, float* state, int* elapsed, const float* action, float* obs_out,
+                          float* rew_out, unsigned char* done_out, const float* reset_u, uint64_t seed,
+                          uint64_t index0, uint32_t step, const uint32_t* step_base, int max_steps,
+                          void* stream);
+int acx_env_step_cartpole(int n, float* state, int* elapsed, const int* action, float* obs_out,
+                          float* rew_out, unsigned char* done_out, const float* reset_u, uint64_t seed,
+                          uint64_t index0, uint32_t step, const uint32_t* step_base, int max_steps,
+                          void* stream);
+int acx_env_step_acrobot(int n, float* state, int* elapsed, const int* action, float* obs_out,
+                         float* rew_out, unsigned char* done_out, const float* reset_u, uint64_t seed,
+                         uint64_t index0, uint32_t step, const uint32_t* step_base, int max_steps,
+                          void* stream);
+
+/* ---------------------------------------------------------------- K2: policy / value forward
+ * Actor.act, Gaussian head -- A3C/policies.py:44-58,110-115.  eps[rows][ac_dim][n] standard
+ * normals or NULL (Philox; ac_dim <= 2).  Outputs: ac_out[rows][ac_dim][n], logp_out,
+ * ent_out, mu_out (the last three nullable). */
+int acx_policy_forward_sample_gauss(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows, int n,
+                                    const float* obs, const float* eps, uint64_t seed, uint64_t index0,
+                                    uint32_t step0, const uint32_t* step_base, float* ac_out, float* logp_out, float* ent_out,
+                                    float* mu_out, void* stream);
+/* Actor.act, categorical head -- A3C/policies.py:63-67.  u[rows][n] uniforms in [0,1) or NULL.
+ * tf.multinomial is restated as an inverse CDF in double (parity unpinned). */
+int acx_policy_forward_sample_cat(const float* actor, int ob_dim, int n_act, int rows, int n, const float* obs,
+                                  const float* u, uint64_t seed, uint64_t index0, uint32_t step0,
+                                  const uint32_t* step_base, int* ac_out,
+                                  float* logp_out, float* ent_out, float* logits_out, void* stream);
+/* log-prob of stored actions under the current weights (A3C/policies.py:60,69) and, when
+ * logp_old is given, the per-block partial sums of (logp_old - logp)^2 for Actor.get_kl
+ * (A3C/policies.py:75,106-108): kl_partial[*kl_blocks] doubles (acx_kl_workspace_bytes()). */
+size_t acx_kl_workspace_bytes(void);
+int acx_policy_logp_gauss(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows, int n,
+                          const float* obs, const float* acs, float* logp_out, float* ent_out, float* mu_out,
+                          const float* logp_old, double* kl_partial, int* kl_blocks /*host*/, void* stream);
+int acx_policy_logp_cat(const float* actor, int ob_dim, int n_act, int rows, int n, const float* obs,
+                        const int* acs, float* logp_out, float* ent_out, float* logits_out,
+                        const float* logp_old, double* kl_partial, int* kl_blocks /*host*/, void* stream);
+/* Critic.value -- A3C/policies.py:146-150,176-177; basic_head != 0 reproduces
+ * Basic_AC/policies.py:134-135 (value head reads the second layer). */
+int acx_value_forward(const float* critic, int ob_dim, int rows, int n, const float* obs, float* v_out,
+                      int basic_head, void* stream);
+
+/* ---------------------------------------------------------------- K3: returns / advantages
+ * PathAdv.__call__ -- A3C/process.py:54-66 -- over time-major [T][n] buffers with done masks
+ * (each column may hold several episode segments; the tail is cut by the horizon and
+ * bootstraps from V[T]); plus the batch moments of A3C/process.py:247:
+ * stats_out[0] = mean(adv), [1] = 1/(1e-8 + std(adv)), [2] = std(adv) (population).
+ * V is [T+1][n].  workspace: 16-byte aligned, first 16 bytes zero before the first call. */
+size_t acx_returns_adv_workspace_bytes(int T, int n);
+int acx_returns_adv_scan(int T, int n, const float* rew, const unsigned char* done, const float* V,
+                         double gamma, int look_ahead, float* G_out, float* adv_out, float* stats_out,
+                         void* workspace, size_t workspace_bytes, int mode, void* stream);
+
+/* ---------------------------------------------------------------- K4: loss + backward
+ * Actor loss  -mean(adv*lp) + beta*mean((lp_old-lp)^2) - gamma*mean(entropy) and its gradient
+ * (A3C/policies.py:74-84, unclipped here: the clip of :85 is applied in acx_adam_apply after
+ * the cross-rank reduction) and critic loss mean((v-target)^2) with gradient (:152-158), in
+ * one call.  adv is raw; adv_stats (device {mean, 1/(1e-8+std)}, e.g. K3's stats_out) applies
+ * the normalisation of A3C/process.py:247 on the fly (NULL: use adv as given).  beta/gamma are
+ * read from the device opt block.  Either network may be NULL to skip it.  Writes
+ * grad_actor / grad_critic (flat, same layout as the parameters) and stats[ACX_STAT_*]. */
+size_t acx_loss_backward_workspace_bytes(int ob_dim, int num_ac, int cont);
+int acx_loss_backward_gauss(const float* actor, const float* critic, int ob_dim, int ac_dim, float ac_scale,
+                            int rows, int n, const float* obs, const float* acs, const float* adv,
+                            const float* adv_stats, const float* logp_old, const float* targets,
+                            const float* opt, float* grad_actor, float* grad_critic, float* stats,
+                            void* workspace, size_t workspace_bytes, void* stream);
+int acx_loss_backward_cat(const float* actor, const float* critic, int ob_dim, int n_act, int rows, int n,
+                          const float* obs, const int* acs, const float* adv, const float* adv_stats,
+                          const float* logp_old, const float* targets, const float* opt, float* grad_actor,
+                          float* grad_critic, float* stats, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* ---------------------------------------------------------------- K5: optimiser + lr control
+ * acx_opt_init fills a device opt block (HOST values in, one small kernel). */
+int acx_opt_init(float* opt, float actor_lr, float critic_lr, float beta_kl, float gamma_ent, float clip,
+                 float desired_kl, float min_lr, float max_lr, int schedule_on, void* stream);
+/* tf.train.AdamOptimizer.apply_gradients (A3C/policies.py:82,88-89,155,160-161), TF ApplyAdam
+ * arithmetic, for both networks in one launch.  grad *= grad_scale first (1/world after an
+ * all-reduce sum), actor grads are then clipped to +-opt[CLIP] (policies.py:85).  Reads the
+ * beta powers from opt; acx_adam_tick advances them (and the step count) afterwards. */
+int acx_adam_apply(float* actor, const float* grad_actor, float* m_actor, float* v_actor, int n_actor,
+                   float* critic, const float* grad_critic, float* m_critic, float* v_critic, int n_critic,
+                   const float* opt, float grad_scale, void* stream);
+int acx_adam_tick(float* opt, void* stream);
+/* *counter += inc (one uint32 on device): advances the RNG step base inside a captured graph. */
+int acx_counter_add(uint32_t* counter, uint32_t inc, void* stream);
+/* Actor.get_kl tail + the lr rule of A3C/process.py:262-270 + the LinearSchedule updates of
+ * :271-278, all on device: acx_kl_finalize folds kl_partial into stats[ACX_STAT_KL_POST]
+ * (mean over count); acx_kl_lr_update applies lr*1.5 / lr/1.5 with the clamp, the schedules
+ * (when opt[SCHEDULE] != 0) and increments opt[ITER].  Split so that a cross-rank average of
+ * stats[KL_POST] can sit between them. */
+int acx_kl_finalize(const double* kl_partial, int kl_blocks, double count, float* stats, void* stream);
+int acx_kl_lr_update(float* opt, float* stats, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACX_H_ */

@@ -1,0 +1,54 @@
+"""Shared helpers for the GPU parity tests (test infrastructure)."""
+import os
+
+import numpy as np
+import torch
+
+from oracle import policies as P
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def demo_weights():
+    """Flat actor/critic buffers (oracle layout) from the reference's shipped checkpoint fixture."""
+    from actor_critic_algs_on_tensorflow_b200.tf_bundle import read_bundle
+    t = read_bundle(os.path.join(GOLDEN, "model-Pendulum_a3c"))
+    al, cl = P.actor_layout(3, 1, True), P.critic_layout(3)
+    a = {"W1": t["global_actor/first_layer/kernel"], "b1": t["global_actor/first_layer/bias"],
+         "W2": t["global_actor/second_layer/kernel"], "b2": t["global_actor/second_layer/bias"],
+         "W3": t["global_actor/third_layer/kernel"], "b3": t["global_actor/third_layer/bias"],
+         "Wh": t["global_actor/mu_layer/kernel"], "bh": t["global_actor/mu_layer/bias"],
+         "log_std": t["global_actor/log_std"]}
+    c = {"W1": t["global_critic/first_layer/kernel"], "b1": t["global_critic/first_layer/bias"],
+         "W2": t["global_critic/second_layer/kernel"], "b2": t["global_critic/second_layer/bias"],
+         "W3": t["global_critic/third_layer/kernel"], "b3": t["global_critic/third_layer/bias"],
+         "Wh": t["global_critic/value/kernel"], "bh": t["global_critic/value/bias"]}
+    c["Wv"], c["bv"] = c.pop("Wh"), c.pop("bh")
+    return P.pack(a, al), P.pack(c, cl)
+
+
+def random_weights(ob_dim, num_ac, cont, seed, bias_scale=0.1):
+    rng = np.random.default_rng(seed)
+    al, cl = P.actor_layout(ob_dim, num_ac, cont), P.critic_layout(ob_dim)
+    a, c = P.glorot_init(al, rng), P.glorot_init(cl, rng)
+    # non-zero biases / log_std so that every gradient path is exercised
+    for lay, flat in ((al, a), (cl, c)):
+        for k, o, s in P.items(lay):
+            if len(s) == 1:
+                flat[o:o + s[0]] = rng.normal(size=s) * bias_scale
+    return a, c
+
+
+def soa(x):
+    """[B, d] -> [d, B] contiguous float32 (one 'row' of the [rows][d][n] batch layout)."""
+    return np.ascontiguousarray(np.asarray(x, dtype=np.float32).T)
+
+
+def dev_t(x, dev, dtype=None):
+    t = torch.as_tensor(np.ascontiguousarray(x), device=dev)
+    return t if dtype is None else t.to(dtype)
+
+
+def rel_err(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
