@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""Benchmark of the actor-critic hot path (BASELINE.json metric: env-steps/sec, rollout+update).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = one rollout + update iteration over the synthetic workload of BASELINE.json configs[2]:
+Pendulum-v0 A2C, 65,536 envs x 20-step horizon PER GPU (weak scaling; at N > 1 the flat gradient
+is all-reduced over NCCL).  Prints ONE JSON line on rank 0 (contract in the task statement).
+
+  value     device-resident throughput: env state, weights and RNG live in HBM; CUDA-event time per
+            step, L2 flushed between timed steps, max over ranks.
+  e2e       same metric through the public trainer API with HOST buffers: every step copies that
+            step's action noise and reset uniforms from pinned host memory (H2D) and reads the stats
+            block and the updated parameters back (D2H), all inside the timed region.
+  roofline  for the dominant kernel (fused loss+backward of the critic MLP) plus a per-kernel table
+            (`kernels`): algorithmic FLOPs or bytes per launch / CUDA-event duration of that kernel
+            timed alone in this run.
+  cpu_baseline / --impl reference
+            the numpy restatement of the reference's math (oracle/a2c.py; TF 1.3 + gym cannot be
+            installed here -- BASELINE.md) on the host cores, on a bounded sample of the workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+ENV_ID, N_ENVS, HORIZON, SEED = "Pendulum-v0", 65536, 20, 12321
+WORKLOAD = "Pendulum-v0 A2C, 65536 envs x 20-step horizon per GPU, fused rollout+update (BASELINE.json configs[2])"
+FLOP_ACTOR_FWD, FLOP_CRITIC_FWD = 50048.0, 100096.0       # per sample, 2 FLOP/MAC
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12         # FFMA peak at max boost clock (computed)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), float(d.get("bf16_tflops", 1590.0)), "measured"
+    return 6650.0, 1590.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.15)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 7 and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) >= 7 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_baseline(steps=2, n_envs=2048, warmup=1):
+    """Oracle A2C iteration (numpy, all host threads through BLAS) on a bounded sample."""
+    from oracle import a2c, envs as E
+    S = a2c.A2CState(E.PENDULUM, n_envs, seed=SEED)
+    for _ in range(warmup):
+        a2c.iteration(S, T=HORIZON)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        a2c.iteration(S, T=HORIZON)
+    dt = time.perf_counter() - t0
+    return n_envs * HORIZON * steps / dt, dt / steps, "%d envs x %d steps x %d iterations of the same workload" % (
+        n_envs, HORIZON, steps)
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    cores = os.cpu_count()
+    v, sec, sample = cpu_baseline(steps=max(1, args.steps), n_envs=2048, warmup=min(args.warmup, 1))
+    line = {"impl": "reference", "metric": "env-steps/sec (rollout+update)", "value": v, "unit": "env-steps/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": sample},
+            "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "numpy restatement of the reference's math (oracle/a2c.py): TF 1.3 and gym are not installable "
+                    "here (BASELINE.md section 2); an upper bound on the real reference, which runs batch-1 sess.run"}
+    print(json.dumps(line), flush=True)
+
+
+def time_kernel(fn, flush, reps=5):
+    import torch
+    fn()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(reps):
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    return tot / reps * 1e-3
+
+
+def kernel_table(tr, flush, hbm_peak):
+    """Per-kernel achieved FLOP/s or GB/s, each kernel timed alone on the trainer's own buffers."""
+    from actor_critic_algs_on_tensorflow_b200 import _lib as L
+    N, T, B = tr.N, tr.T, tr.N * tr.T
+    s = L.cur_stream()
+    Pa = tr.Pa
+    ga, gc = tr.grads[:Pa], tr.grads[Pa:]
+    common = (L.ptr(tr.obs_buf), L.ptr(tr.acs), L.ptr(tr.adv), L.ptr(tr.stats), L.ptr(tr.logps), L.ptr(tr.G),
+              L.ptr(tr.opt), L.ptr(ga), L.ptr(gc), L.ptr(tr.stats), L.ptr(tr.ws_bwd), tr.ws_bwd_bytes, s)
+    ks = {}
+
+    def bwd(actor, critic):
+        return lambda: L.call("acx_loss_backward_gauss", actor, critic, tr.ob, tr.num_ac, tr.ac_scale, T, N, *common)
+    ks["loss_backward_critic (K4)"] = (bwd(None, L.ptr(tr.critic)), 3 * FLOP_CRITIC_FWD * B, None)
+    ks["loss_backward_actor (K4)"] = (bwd(L.ptr(tr.actor), None), 3 * FLOP_ACTOR_FWD * B, None)
+    ks["value_forward (K2)"] = (lambda: L.call("acx_value_forward", L.ptr(tr.critic), tr.ob, T + 1, N,
+                                               L.ptr(tr.obs_buf), L.ptr(tr.V), 0, s), FLOP_CRITIC_FWD * (T + 1) * N, None)
+    ks["policy_forward_sample (K2)"] = (lambda: L.call(
+        "acx_policy_forward_sample_gauss", L.ptr(tr.actor), tr.ob, tr.num_ac, tr.ac_scale, 1, N, L.ptr(tr.obs_buf), None,
+        tr.seed, 0, 0, None, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent), None, s), FLOP_ACTOR_FWD * N, None)
+    ks["policy_logp_kl (K2/K5)"] = (lambda: L.call(
+        "acx_policy_logp_gauss", L.ptr(tr.actor), tr.ob, tr.num_ac, tr.ac_scale, T, N, L.ptr(tr.obs_buf), L.ptr(tr.acs),
+        None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part), __import__("ctypes").byref(tr.kl_blocks), s),
+        FLOP_ACTOR_FWD * B, None)
+    import torch
+    st2, el2 = tr.state.clone(), tr.elapsed.clone()
+    ks["env_step pendulum (K1)"] = (lambda: L.call(
+        "acx_env_step", tr.env, N, L.ptr(st2), L.ptr(el2), L.ptr(tr.acs), L.ptr(tr.obs_buf[1]), L.ptr(tr.rew),
+        L.ptr(tr.done), None, tr.seed, 0, 0, None, tr.max_steps, s), None, 45.0 * N)
+    G2, A2 = torch.empty_like(tr.G), torch.empty_like(tr.adv)
+    ks["returns_adv_scan (K3)"] = (lambda: L.call(
+        "acx_returns_adv_scan", T, N, L.ptr(tr.rew), L.ptr(tr.done), L.ptr(tr.V), tr.gamma, tr.look_ahead, L.ptr(G2),
+        L.ptr(A2), L.ptr(tr.stats), L.ptr(tr.ws_scan), tr.ws_scan_bytes, 0, s), None, 17.0 * B + 4.0 * N)
+    m2, v2, p2 = tr.m.clone(), tr.v.clone(), tr.params.clone()
+    ks["adam_apply (K5)"] = (lambda: L.call(
+        "acx_adam_apply", L.ptr(p2[:Pa]), L.ptr(ga), L.ptr(m2[:Pa]), L.ptr(v2[:Pa]), Pa, L.ptr(p2[Pa:]), L.ptr(gc),
+        L.ptr(m2[Pa:]), L.ptr(v2[Pa:]), tr.Pc, L.ptr(tr.opt), 1.0, s), None, 28.0 * (tr.Pa + tr.Pc))
+    out = {}
+    for name, (fn, flops, nbytes) in ks.items():
+        sec = time_kernel(fn, flush)
+        if flops is not None:
+            ach = flops / sec / 1e12
+            out[name] = {"bound": "fp32", "ms": sec * 1e3, "achieved": ach, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
+                         "frac": ach / FP32_PEAK_TFLOPS}
+        else:
+            ach = nbytes / sec / 1e9
+            out[name] = {"bound": "hbm", "ms": sec * 1e3, "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": ach / hbm_peak, "algorithmic_bytes": nbytes}
+    return out
+
+
+def run_ours(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+    from actor_critic_algs_on_tensorflow_b200.trainer import A2CTrainer
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    hbm_peak, bf16_peak, peaks_src = measured_peaks()
+    tr = A2CTrainer(ENV_ID, n_envs=N_ENVS, horizon=HORIZON, seed=SEED, rank=rank, world=world, mode=args.mode)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
+
+    def flush():
+        flush_buf.fill_(1)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):          # >= 3 warm-up steps (also builds the CUDA graphs)
+        tr.iteration()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    evs = []
+    barrier()
+    for _ in range(args.steps):
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        launches = tr.iteration()
+        b.record()
+        evs.append((a, b))
+    barrier()
+    sampler.stop_flag = True
+    sec = sum(a.elapsed_time(b) for a, b in evs) * 1e-3
+    t = torch.tensor([sec], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    sec = float(t.item())
+    steps_per_it = N_ENVS * HORIZON
+    value = world * steps_per_it * args.steps / sec
+    stats = tr.read_stats()
+
+    # ---- end to end through the public API with host buffers
+    eps_h = torch.randn((HORIZON, 1, N_ENVS), dtype=torch.float32).pin_memory()
+    ru_h = torch.rand((HORIZON, tr.S, N_ENVS), dtype=torch.float32).pin_memory()
+    stats_h = torch.empty(32, dtype=torch.float32).pin_memory()
+    params_h = torch.empty(tr.Pa + tr.Pc, dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        tr.iteration(noise=eps_h, reset_u=ru_h)                    # H2D inside
+        stats_h[:16].copy_(tr.stats, non_blocking=True)            # D2H: losses / KL / lr ...
+        stats_h[16:].copy_(tr.opt, non_blocking=True)
+        params_h.copy_(tr.params, non_blocking=True)               # ... and the updated weights
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    e_evs = []
+    for _ in range(args.steps):
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        e2e_step()
+        b.record()
+        e_evs.append((a, b))
+    barrier()
+    e_sec = sum(a.elapsed_time(b) for a, b in e_evs) * 1e-3
+    t = torch.tensor([e_sec], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e_sec = float(t.item())
+    h2d = eps_h.numel() * 4 + ru_h.numel() * 4
+    d2h = stats_h.numel() * 4 + params_h.numel() * 4
+
+    if rank == 0:
+        kernels = kernel_table(tr, flush, hbm_peak)
+        dom = kernels["loss_backward_critic (K4)"]
+        step_ms = sec / args.steps * 1e3
+        roof = {"kernel": "acx_mlp_kernel<critic, train> (fused loss+backward, K4)", "bound": "fp32",
+                "achieved": dom["achieved"], "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": dom["frac"],
+                "peak_source": "computed FFMA peak 148 SM x 128 lanes x 2 x 1.965 GHz; the kernel is fp32 FFMA, not a "
+                               "tensor-core kernel (bf16 tensor peak %s: %.0f TFLOP/s)" % (peaks_src, bf16_peak),
+                "share_of_step": dom["ms"] / step_ms, "traffic": None,
+                "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
+        total_flops = (FLOP_ACTOR_FWD * (1 + 3 + 1) + FLOP_CRITIC_FWD * (3 + (HORIZON + 1) / HORIZON)) * steps_per_it
+        cb_v, cb_sec, cb_sample = (cpu_baseline() if world == 1 else (None, None, None))
+        line = {"metric": "env-steps/sec (rollout+update)", "value": value, "unit": "env-steps/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": step_ms, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "envs_per_gpu": N_ENVS, "horizon": HORIZON, "mode": args.mode,
+                           "l2": "flushed (256 MiB write) between timed steps", "weights": "glorot-uniform, seed 12321",
+                           "rng": "device Philox4x32-10", "cuda_graphs": True,
+                           "parallelism": "dp%d (envs sharded by rank, NCCL all-reduce of the flat gradient)" % world},
+                "e2e": {"value": world * steps_per_it * args.steps / e_sec, "unit": "env-steps/s",
+                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e_sec / args.steps * 1e3},
+                "gpu_launches": int(launches) * args.steps,
+                "clocks": sampler.summary(),
+                "roofline": roof, "kernels": kernels,
+                "step_tflops": total_flops / (sec / args.steps) / 1e12,
+                "train_stats": stats}
+        if cb_v is not None:
+            line["cpu_baseline"] = {"value": cb_v, "unit": "env-steps/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": cb_sample, "sec_per_iteration": cb_sec}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--mode", choices=["sync", "async"], default="sync")
+    args = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 and world == 1 and args.impl == "ours":
+        # convenience: re-launch ourselves under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    if args.impl == "reference":
+        run_reference(args, rank)
+    else:
+        run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()
