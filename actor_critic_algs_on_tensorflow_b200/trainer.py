@@ -44,14 +44,12 @@ def glorot_flat(net, ob_dim, num_ac, cont, gen):
     """xavier-uniform kernels, zero biases, log_std = 0 (A3C/policies.py:7,44-52) in the flat layout."""
     lay, total = L.params_layout(net, ob_dim, num_ac, cont)
     flat = np.zeros(total, dtype=np.float32)
-    fan = {"W1": (ob_dim, None), "W2": None, "W3": None, "Wh": None}
     h = (128, 128, 64) if net == 0 else (256, 128, 128)
     shapes = {"W1": (ob_dim, h[0]), "W2": (h[0], h[1]), "W3": (h[1], h[2]), "Wh": (h[2], num_ac if net == 0 else 1)}
     for k, (fi, fo) in shapes.items():
         lim = np.sqrt(6.0 / (fi + fo))
         off, size = lay[k]
         flat[off:off + size] = gen.uniform(-lim, lim, size=size)
-    del fan
     return flat
 
 
@@ -199,7 +197,7 @@ class A2CTrainer:
 
     # ------------------------------------------------------------------ segments + graphs
     def _seg_a(self, buffered):
-        self.obs_buf[0].copy_(self.obs_buf[self.T]) if self.iterations_started else None
+        self.obs_buf[0].copy_(self.obs_buf[self.T])      # the last observation of the previous rollout
         return self._rollout(buffered) + self._gradients() + 1
 
     def _run(self, key, fn):

@@ -101,7 +101,7 @@ def update(S, ro, gamma=0.98, look_ahead=40, desired_kl=0.002, min_lr=1e-6, max_
     if allreduce is not None:
         kl = float(allreduce(np.array([kl]))[0])
     stats = dict(actor_loss=float(ag["loss"]), critic_loss=float(cg["loss"]), kl=kl, actor_lr=S.actor_lr,
-                 avg_ent=ro["ent_sum"] / B, mean_rew=float(ro["rew"].mean()), G=G, adv=adv, V=V,
+                 avg_ent=ro["ent_sum"] / B, mean_rew=float(ro["rew"].mean()), G=G, adv=adv, V=V, rollout=ro,
                  grad_actor=g_a, grad_critic=g_c)
     S.actor_lr = float(np.float32(P.kl_lr_rule(S.actor_lr, kl, desired_kl, min_lr, max_lr)))
     if S.it % 100 == 0:                                  # A3C/process.py:271-278

@@ -48,11 +48,16 @@ def backward_gpu(lib, dev, cont, actor, critic, ob, num_ac, obs_rows, acs_rows, 
     return ga.cpu().numpy(), gc.cpu().numpy(), stats.cpu().numpy()
 
 
-def check_grads(got, want, lay, tol):
+def check_grads(got, want, lay, tol, want32=None):
+    """Per tensor: max-abs-diff / max-abs < tol.  The mean gradient of a large batch with random-sign
+    advantages is a heavily cancelling sum (|result| ~ |terms| / sqrt(B)); the numpy fp32 restatement of the
+    reference's own math then sits up to ~1e-3 from the fp64 value.  Where that happens (want32 given) the
+    bar is "no less accurate than twice the fp32 restatement", never looser than that."""
     for k, o, s in P.items(lay):
         sz = int(np.prod(s))
         g, w = got[o:o + sz], want[o:o + sz]
-        assert rel_err(g, w) < tol, "%s: rel err %.3g" % (k, rel_err(g, w))
+        bar = tol if want32 is None else max(tol, 2.0 * rel_err(want32[o:o + sz], w))
+        assert rel_err(g, w) < bar, "%s: rel err %.3g (bar %.3g)" % (k, rel_err(g, w), bar)
     used = np.zeros(lay["_size"], bool)
     for k, o, s in P.items(lay):
         used[o:o + int(np.prod(s))] = True
@@ -80,8 +85,11 @@ def test_gauss_loss_backward_matches_oracle(lib, dev, rows, n, weights):
     wa = P.actor_loss_grads(actor, lay, obs.reshape(B, 3), acs.reshape(B, 1), adv.reshape(B), lp_old.reshape(B), beta,
                             gam, True, 2.0, clip=None, dtype=np.float64)
     wc = P.critic_loss_grads(critic, clay, obs.reshape(B, 3), targets.reshape(B), dtype=np.float64)
-    check_grads(ga, wa["grad_raw"], lay, 2 * TOL)
-    check_grads(gc, wc["grad"], clay, 2 * TOL)
+    wa32 = P.actor_loss_grads(actor, lay, obs.reshape(B, 3), acs.reshape(B, 1), adv.reshape(B), lp_old.reshape(B), beta,
+                              gam, True, 2.0, clip=None, dtype=np.float32)
+    wc32 = P.critic_loss_grads(critic, clay, obs.reshape(B, 3), targets.reshape(B), dtype=np.float32)
+    check_grads(ga, wa["grad_raw"], lay, 2 * TOL, wa32["grad_raw"])
+    check_grads(gc, wc["grad"], clay, 2 * TOL, wc32["grad"])
     np.testing.assert_allclose(stats[3], wa["loss"], rtol=2 * TOL, atol=1e-6)
     np.testing.assert_allclose(stats[4], wc["loss"], rtol=2 * TOL)
     np.testing.assert_allclose(stats[5], wa["kl"], rtol=2 * TOL)
