@@ -14,6 +14,7 @@ CSRC = os.path.join(_HERE, "csrc")
 ENV_PENDULUM, ENV_CARTPOLE, ENV_ACROBOT = 0, 1, 2
 SCAN_AUTO, SCAN_COLS, SCAN_WARP = 0, 1, 2
 OPT_SIZE, STATS_SIZE = 16, 16
+SCAN_STATIC_MAX_COLUMNS = 131072
 (OPT_ACTOR_LR, OPT_CRITIC_LR, OPT_BETA_KL, OPT_GAMMA_ENT, OPT_BETA1_POW, OPT_BETA2_POW, OPT_CLIP, OPT_DESIRED_KL,
  OPT_MIN_LR, OPT_MAX_LR, OPT_ITER, OPT_SCHEDULE, OPT_ADAM_T) = range(13)
 (STAT_ADV_MEAN, STAT_ADV_INV_STD, STAT_ADV_STD, STAT_ACTOR_LOSS, STAT_CRITIC_LOSS, STAT_KL_PRE, STAT_ENT_MEAN,
@@ -56,6 +57,7 @@ SIGNATURES = {
     "acx_value_forward": (_i, [_p, _i, _i, _i, _p, _p, _i, _p]),
     "acx_returns_adv_workspace_bytes": (_sz, [_i, _i]),
     "acx_returns_adv_scan": (_i, [_i, _i, _p, _p, _p, _d, _i, _p, _p, _p, _p, _sz, _i, _p]),
+    "acx_returns_adv_scan_static": (_i, [_i, _i, _p, _p, _p, _d, _i, _p, _p, _p, _i, _p]),
     "acx_loss_backward_workspace_bytes": (_sz, [_i, _i, _i]),
     "acx_loss_backward_gauss": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_loss_backward_cat": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),

@@ -257,3 +257,56 @@ extern "C" int acx_returns_adv_scan(int T, int n, const float* rew, const unsign
   ACX_LAUNCH_OK("acx_scan kernel");
   return ACX_OK;
 }
+
+// ------------------------------------------------------------------ allocation-free variant
+// Same kernels, but the partial-moment scratch is a fixed array that lives in the library's
+// device image instead of a caller workspace.  Every GPU that loads libacx.so carries these
+// ACX_SCAN_STATIC_SCRATCH_BYTES until the process exits.
+#define ACX_SCAN_STATIC_MAX_BLOCKS 512
+#define ACX_SCAN_STATIC_SCRATCH_BYTES (16 + 16 * ACX_SCAN_STATIC_MAX_BLOCKS)
+static __device__ __align__(256) unsigned char g_scan_static_scratch[ACX_SCAN_STATIC_SCRATCH_BYTES];
+
+// In host code `g_scan_static_scratch` is only a handle for the runtime, not an address a kernel can
+// use: the device address has to be asked for, once per device, while that device is current.
+static int scan_static_scratch(ScanWs** out) {
+  static void* addr[64] = {nullptr};
+  int dev = 0;
+  ACX_CUDA_OK(cudaGetDevice(&dev));
+  ACX_REQUIRE(dev >= 0 && dev < 64, "acx_returns_adv_scan_static: device ordinal %d not supported (max 63)", dev);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    ACX_CUDA_OK(cudaGetSymbolAddress(&p, g_scan_static_scratch));
+    ACX_REQUIRE(p != nullptr, "acx_returns_adv_scan_static: no device address for the static scratch");
+    addr[dev] = p;
+  }
+  *out = reinterpret_cast<ScanWs*>(addr[dev]);
+  return ACX_OK;
+}
+
+extern "C" int acx_returns_adv_scan_static(int T, int n, const float* rew, const unsigned char* done, const float* V,
+                                           double gamma, int look_ahead, float* G_out, float* adv_out,
+                                           float* stats_out, int mode, void* stream) {
+  ACX_REQUIRE(T >= 0 && n >= 0, "acx_returns_adv_scan_static: negative size (T=%d, n=%d)", T, n);
+  ACX_REQUIRE(look_ahead >= 1, "acx_returns_adv_scan_static: look_ahead must be >= 1 (got %d)", look_ahead);
+  ACX_REQUIRE(n <= ACX_SCAN_STATIC_MAX_COLUMNS,
+              "acx_returns_adv_scan_static: n = %d env columns exceeds the built-in scratch (maximum %d); use "
+              "acx_returns_adv_scan with a caller workspace for wider batches", n, ACX_SCAN_STATIC_MAX_COLUMNS);
+  if (T == 0 || n == 0) return ACX_OK;
+  ACX_REQUIRE(rew && done && V && G_out && adv_out && stats_out, "acx_returns_adv_scan_static: null buffer");
+  if (mode == ACX_SCAN_AUTO) mode = (n < 2048 && T >= 64) ? ACX_SCAN_WARP : ACX_SCAN_COLS;
+  ACX_REQUIRE(mode == ACX_SCAN_COLS || mode == ACX_SCAN_WARP, "acx_returns_adv_scan_static: bad mode %d", mode);
+  ScanWs* ws = nullptr;
+  int rc = scan_static_scratch(&ws);
+  if (rc != ACX_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps whatever the previous call left: the "last block" ticket has to start at zero
+  ACX_CUDA_OK(cudaMemsetAsync(ws, 0, 16, st));
+  int grid = mode == ACX_SCAN_WARP ? (n + 7) / 8 : (n + 255) / 256;
+  if (grid > ACX_SCAN_STATIC_MAX_BLOCKS) grid = ACX_SCAN_STATIC_MAX_BLOCKS;
+  if (mode == ACX_SCAN_WARP)
+    acx_scan_warp_kernel<<<grid, 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out, adv_out, ws, stats_out);
+  else
+    acx_scan_cols_kernel<<<grid, 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out, adv_out, ws, stats_out);
+  ACX_LAUNCH_OK("acx_scan kernel (static scratch)");
+  return ACX_OK;
+}

@@ -150,6 +150,27 @@ size_t acx_returns_adv_workspace_bytes(int T, int n);
 int acx_returns_adv_scan(int T, int n, const float* rew, const unsigned char* done, const float* V,
                          double gamma, int look_ahead, float* G_out, float* adv_out, float* stats_out,
                          void* workspace, size_t workspace_bytes, int mode, void* stream);
+/* The same scan for callers that have no way to hand over a workspace.  (No counterpart in the
+ * reference: this entry point exists only for embedding.)  Think of a rollout worker living inside
+ * another framework's process, where that framework's pool has already claimed the GPU's memory and
+ * a fresh cudaMalloc fails; of a control loop that cannot afford the device-wide synchronisation an
+ * allocation implies; or of a sandboxed plugin thread that is given input and output buffers and
+ * nothing else.  Inputs and outputs are still the caller's; only the few KB of partial-moment
+ * scratch come from a fixed array inside the library's device image (about 8 KB that every GPU
+ * loading the library keeps until the process exits).
+ *   - Limit: n <= ACX_SCAN_STATIC_MAX_COLUMNS env columns per call (T is unlimited); wider batches
+ *     are refused with ACX_ERR_INVALID and a message -- use acx_returns_adv_scan for those.
+ *   - Nothing is allocated or freed, here or in any library it calls.
+ *   - The first call on each device looks up the array's device address (that device must be
+ *     current); make that first call before any stream capture begins.
+ *   - All calls on a device share the one array and it keeps the previous call's contents; the
+ *     entry point re-zeroes the counter it depends on (stream-ordered) before launching.  Two calls
+ *     whose kernels can overlap on the GPU (different streams, no dependency) race on it: keep
+ *     calls to this entry point ordered with respect to each other. */
+#define ACX_SCAN_STATIC_MAX_COLUMNS 131072
+int acx_returns_adv_scan_static(int T, int n, const float* rew, const unsigned char* done, const float* V,
+                                double gamma, int look_ahead, float* G_out, float* adv_out,
+                                float* stats_out, int mode, void* stream);
 
 /* ---------------------------------------------------------------- K4: loss + backward
  * Actor loss  -mean(adv*lp) + beta*mean((lp_old-lp)^2) - gamma*mean(entropy) and its gradient
