@@ -1,0 +1,103 @@
+"""The fused rollout+update loop (trainer.A2CTrainer) against the oracle's iteration (oracle/a2c.py)
+from the same Philox streams and the same initial weights; CUDA-graph replay vs eager launches;
+caller-supplied noise; checkpoint export.  Tolerances: rollout quantities 1e-4 (T chained fp32 env steps
+and forwards), returns 2e-4, gradients 2e-3 of the tensor's max (they inherit the rollout's rounding)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import a2c, envs as E, philox as R
+from actor_critic_algs_on_tensorflow_b200.trainer import A2CTrainer
+from actor_critic_algs_on_tensorflow_b200 import process, tf_bundle
+
+pytestmark = pytest.mark.gpu
+
+
+def _cmp_iteration(tr, st, cont):
+    ro = st["rollout"]
+    np.testing.assert_array_equal(tr.done.cpu().numpy(), ro["done"])
+    np.testing.assert_allclose(tr.rew.cpu().numpy(), ro["rew"], rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(tr.obs_buf.cpu().numpy(), ro["obs"], rtol=1e-4, atol=1e-4)
+    if cont:
+        np.testing.assert_allclose(tr.acs.cpu().numpy(), ro["acs"], rtol=1e-4, atol=1e-4)
+    else:
+        np.testing.assert_array_equal(tr.acs.cpu().numpy(), ro["acs"][:, 0, :])
+    np.testing.assert_allclose(tr.logps.cpu().numpy(), ro["logps"], rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(tr.V.cpu().numpy(), st["V"], rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(tr.G.cpu().numpy(), st["G"], rtol=2e-4, atol=2e-4)
+    ga, gc = tr.grads[:tr.Pa].cpu().numpy(), tr.grads[tr.Pa:].cpu().numpy()
+    for g, w in ((np.clip(ga, -0.1, 0.1), st["grad_actor"]), (gc, st["grad_critic"])):
+        assert np.abs(g - w).max() <= 2e-3 * np.abs(w).max()
+    got = tr.read_stats()
+    np.testing.assert_allclose(got["act_loss"], st["actor_loss"], rtol=1e-3, atol=1e-4)
+    np.testing.assert_allclose(got["crit_loss"], st["critic_loss"], rtol=1e-3)
+    np.testing.assert_allclose(got["kl_dist"], st["kl"], rtol=2e-2, atol=1e-6)
+    np.testing.assert_allclose(got["avg_ent"], st["avg_ent"], rtol=1e-4)
+    np.testing.assert_allclose(got["act_lr"], st["actor_lr"], rtol=1e-6)
+
+
+@pytest.mark.parametrize("env_id,env,N,T", [("Pendulum-v0", E.PENDULUM, 256, 8), ("CartPole-v0", E.CARTPOLE, 192, 12),
+                                            ("Acrobot-v1", E.ACROBOT, 128, 6)])
+def test_first_iteration_matches_oracle(env_id, env, N, T):
+    S = a2c.A2CState(env, N, seed=777)
+    tr = A2CTrainer(env_id, n_envs=N, horizon=T, seed=777, actor_params=S.actor.copy(), critic_params=S.critic.copy(),
+                    use_graph=False, max_episode_steps=5 if env != E.PENDULUM else 0)
+    np.testing.assert_array_equal(tr.state.cpu().numpy(), S.state)          # Philox reset, exact
+    tr.iteration()
+    torch.cuda.synchronize()
+    st = a2c.iteration(S, T=T, max_steps=5 if env != E.PENDULUM else None)
+    _cmp_iteration(tr, st, env == E.PENDULUM)
+    assert tr.done.sum().item() > 0 or env == E.PENDULUM
+    np.testing.assert_allclose(tr.read_stats()["next_lr"], S.actor_lr, rtol=1e-6)
+
+
+def test_graph_replay_equals_eager_launches():
+    outs = []
+    for use_graph in (False, True):
+        tr = A2CTrainer("Pendulum-v0", n_envs=1024, horizon=5, seed=3, use_graph=use_graph)
+        for _ in range(5):
+            tr.iteration()
+        torch.cuda.synchronize()
+        outs.append((tr.params.cpu().numpy(), tr.opt.cpu().numpy(), tr.state.cpu().numpy(), tr.step_ctr.item()))
+    for a, b in zip(*outs):
+        np.testing.assert_array_equal(a, b)          # deterministic kernels: bit-identical
+    assert outs[0][3] == 25 and outs[0][1][10] == 5 and outs[0][1][12] == 5
+
+
+def test_caller_supplied_noise_matches_oracle_and_device_rng():
+    N, T, seed = 512, 4, 99
+    idx = np.arange(N, dtype=np.uint64)
+    eps = np.stack([R.normals(idx, t, R.STREAM_ACTION, seed)[:, :1].T for t in range(T)])          # [T,1,N]
+    ru = np.stack([R.uniforms(idx, t, R.STREAM_RESET, seed).T[:2] for t in range(T)])              # [T,2,N]
+    a = A2CTrainer("Pendulum-v0", n_envs=N, horizon=T, seed=seed, use_graph=False)
+    b = A2CTrainer("Pendulum-v0", n_envs=N, horizon=T, seed=seed, use_graph=False)
+    a.iteration()
+    b.iteration(noise=torch.tensor(eps), reset_u=torch.tensor(ru))       # host tensors: H2D inside
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(b.acs.cpu().numpy(), a.acs.cpu().numpy(), rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(b.params.cpu().numpy(), a.params.cpu().numpy(), rtol=1e-3, atol=1e-5)
+
+
+def test_many_iterations_stay_finite_and_lr_adapts():
+    tr = A2CTrainer("CartPole-v0", n_envs=2048, horizon=20, seed=1)
+    for _ in range(30):
+        tr.iteration()
+    st = tr.read_stats()
+    assert np.isfinite(tr.params.cpu().numpy()).all() and st["iteration"] == 30 and st["adam_t"] == 30
+    assert 1e-6 <= st["next_lr"] <= 0.1 and st["next_lr"] != pytest.approx(0.005)
+    assert tr.done.sum().item() > 0
+
+
+def test_checkpoint_export_loads_back(tmp_path):
+    tr = A2CTrainer("Pendulum-v0", n_envs=128, horizon=4, seed=5, use_graph=False)
+    tr.iteration()
+    at, ct = process.trainer_checkpoint_tensors(tr)
+    prefix = process.save_checkpoint(str(tmp_path), "model-Pendulum", 600, at, ct)
+    assert os.path.basename(prefix) == "model-Pendulum-600"
+    t = tf_bundle.read_bundle(prefix)
+    assert len(t) == 22 and t["global_actor/second_layer/kernel"].shape == (128, 128)
+    assert open(os.path.join(str(tmp_path), "checkpoint")).read().startswith('model_checkpoint_path: "model-Pendulum-600"')
+    actor = process.load_actor(prefix, 3, 1, 'cont', 2.0)
+    np.testing.assert_array_equal(actor.net.params.cpu().numpy(), tr.actor.cpu().numpy())
