@@ -45,32 +45,49 @@ def measured_peaks():
     return 6650.0, 1590.0, "fallback"
 
 
-class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons streamed (-lms 100) during the timed region."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.rows, self.proc, self.thread = index, [], None, None
 
-    def run(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([x.strip() for x in out.strip().split(",")])
-            except Exception:
-                pass
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+
+        def pump():
+            for line in self.proc.stdout:
+                self.rows.append((time.perf_counter(), [x.strip() for x in line.strip().split(",")]))
+        self.thread = threading.Thread(target=pump, daemon=True)
+        self.thread.start()
+        time.sleep(0.35)            # let the first samples arrive before the timed region starts
+
+    def stop(self):
+        if self.proc is not None:
             time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
 
-    def summary(self):
-        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 7 and r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if len(r) >= 7 and r[1].isdigit()]
+    def summary(self, t0=None, t1=None):
+        rows = [r for t, r in self.rows if (t0 is None or t >= t0 - 0.1) and (t1 is None or t <= t1 + 0.1)] or \
+               [r for _, r in self.rows]
+        sm = sorted(int(r[0]) for r in rows if len(r) >= 7 and r[0].isdigit())
+        mx = [int(r[1]) for r in rows if len(r) >= 7 and r[1].isdigit()]
+        pw = [float(r[2]) for r in rows if len(r) >= 7 and r[2].replace(".", "", 1).isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower() == "active" for r in self.rows)]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower() == "active" for r in rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
 def cpu_baseline(steps=2, n_envs=2048, warmup=1):
@@ -157,6 +174,21 @@ def kernel_table(tr, flush, hbm_peak):
     ks["adam_apply (K5)"] = (lambda: L.call(
         "acx_adam_apply", L.ptr(p2[:Pa]), L.ptr(ga), L.ptr(m2[:Pa]), L.ptr(v2[:Pa]), Pa, L.ptr(p2[Pa:]), L.ptr(gc),
         L.ptr(m2[Pa:]), L.ptr(v2[Pa:]), tr.Pc, L.ptr(tr.opt), 1.0, s), None, 28.0 * (tr.Pa + tr.Pc))
+    # the HBM-bound kernels move only 3-22 MB at 65,536 envs (launch-latency bound): also time them at the
+    # 1,048,576-env size of BASELINE configs[4] (env kernels) / a 1M-column scan
+    NB = 1 << 20
+    from actor_critic_algs_on_tensorflow_b200.envs import VecEnv
+    for env_name, nb in (("Pendulum-v0", 45.0), ("CartPole-v0", 65.0), ("Acrobot-v1", 73.0)):
+        ve = VecEnv(env_name, NB, seed=1)
+        ve.reset()
+        act = (torch.zeros(NB, device="cuda") if ve.n_actions == 0 else torch.ones(NB, device="cuda", dtype=torch.int32))
+        ks["env_step %s, 1M envs (K1)" % env_name] = ((lambda ve=ve, act=act: ve.step(act)), None, nb * NB)
+    rB, dB = torch.randn((T, NB), device="cuda"), torch.zeros((T, NB), device="cuda", dtype=torch.uint8)
+    vB, gB, aB = torch.randn((T + 1, NB), device="cuda"), torch.empty((T, NB), device="cuda"), torch.empty((T, NB), device="cuda")
+    wsB = torch.zeros(L.load().acx_returns_adv_workspace_bytes(T, NB), device="cuda", dtype=torch.uint8)
+    ks["returns_adv_scan, 1M columns (K3)"] = (lambda: L.call(
+        "acx_returns_adv_scan", T, NB, L.ptr(rB), L.ptr(dB), L.ptr(vB), tr.gamma, tr.look_ahead, L.ptr(gB), L.ptr(aB),
+        L.ptr(tr.stats), L.ptr(wsB), wsB.numel(), 0, s), None, 17.0 * T * NB + 4.0 * NB)
     out = {}
     for name, (fn, flops, nbytes) in ks.items():
         sec = time_kernel(fn, flush)
@@ -180,7 +212,8 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     hbm_peak, bf16_peak, peaks_src = measured_peaks()
-    tr = A2CTrainer(ENV_ID, n_envs=N_ENVS, horizon=HORIZON, seed=SEED, rank=rank, world=world, mode=args.mode)
+    tr = A2CTrainer(ENV_ID, n_envs=N_ENVS, horizon=HORIZON, seed=SEED, rank=rank, world=world, mode=args.mode,
+                    use_graph=not args.no_graph)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
 
     def flush():
@@ -200,6 +233,7 @@ def run_ours(args, rank, local_rank, world):
         sampler.start()
     evs = []
     barrier()
+    t_begin = time.perf_counter()
     for _ in range(args.steps):
         flush()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -208,7 +242,9 @@ def run_ours(args, rank, local_rank, world):
         b.record()
         evs.append((a, b))
     barrier()
-    sampler.stop_flag = True
+    t_end = time.perf_counter()
+    if rank == 0:
+        sampler.stop()
     sec = sum(a.elapsed_time(b) for a, b in evs) * 1e-3
     t = torch.tensor([sec], device="cuda", dtype=torch.float64)
     if world > 1:
@@ -266,12 +302,12 @@ def run_ours(args, rank, local_rank, world):
                 "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "envs_per_gpu": N_ENVS, "horizon": HORIZON, "mode": args.mode,
                            "l2": "flushed (256 MiB write) between timed steps", "weights": "glorot-uniform, seed 12321",
-                           "rng": "device Philox4x32-10", "cuda_graphs": True,
+                           "rng": "device Philox4x32-10", "cuda_graphs": not args.no_graph,
                            "parallelism": "dp%d (envs sharded by rank, NCCL all-reduce of the flat gradient)" % world},
                 "e2e": {"value": world * steps_per_it * args.steps / e_sec, "unit": "env-steps/s",
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e_sec / args.steps * 1e3},
                 "gpu_launches": int(launches) * args.steps,
-                "clocks": sampler.summary(),
+                "clocks": sampler.summary(t_begin, t_end),
                 "roofline": roof, "kernels": kernels,
                 "step_tflops": total_flops / (sec / args.steps) / 1e12,
                 "train_stats": stats}
@@ -287,10 +323,11 @@ def run_ours(args, rank, local_rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--mode", choices=["sync", "async"], default="sync")
+    ap.add_argument("--no_graph", action="store_true", help="launch kernels eagerly (for ncu launch lists)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
