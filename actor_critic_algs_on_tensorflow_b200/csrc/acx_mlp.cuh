@@ -4,8 +4,8 @@
 // memory as [feature][sample] (row stride 68 floats, == 4 mod 32, so that both "rows across
 // lanes" and "4 consecutive samples per lane" 16-byte accesses are bank-conflict free).
 // Weight matrices are streamed from L2 in 64-row chunks through a 3-slot shared-memory ring
-// by the TMA engine (cp.async.bulk + mbarrier complete_tx; SASS UBLKCP), prefetched two
-// stages ahead, so neither the 99 KB actor nor the 197.5 KB critic has to fit next to the
+// by the TMA engine (cp.async.bulk + mbarrier complete_tx; SASS UBLKCP; eight 4 KB copies per
+// chunk -- 8-row groups, each followed by 16 bytes of padding), prefetched two stages ahead, so neither the 99 KB actor nor the 197.5 KB critic has to fit next to the
 // activations (SURVEY.md 0.4 / 7 hard part 2).  All math is fp32 FFMA; every output neuron is
 // a sequential k-ascending FMA chain, bias added last (tf.layers.dense = matmul + bias_add).
 //
@@ -23,8 +23,7 @@ constexpr int MT = 64;              // samples per tile
 constexpr int MS = 68;              // activation row stride (floats)
 constexpr int NT = 256;             // threads per CTA
 constexpr int CH = 64;              // weight rows per ring chunk
-constexpr int WS_MAX = 132;         // slot row stride for J = 128 (J + 4)
-constexpr int SLOT_FLOATS = CH * WS_MAX;
+constexpr int SLOT_FLOATS = CH * 128 + 32;   // 8 groups of (8 rows x J floats + 4 floats of padding), J <= 128
 constexpr int NSLOT = 3;
 constexpr int H2 = 128;
 constexpr int MAX_OB = 8;
@@ -119,10 +118,11 @@ template <int H1, int H3, bool TRAIN> struct Ring {
     unsigned long long* bar = &sm->bar[q];
     if (lane == 0) acx_mbar_expect_tx(reinterpret_cast<uint64_t*>(bar), (uint32_t)(CH * J * 4));
     __syncwarp();
+    // eight 8-row groups, one bulk copy each (4 KB for J = 128); a group is followed by 4 floats of padding
     float* dst = sm->slot[q];
-#pragma unroll
-    for (int r = lane; r < CH; r += 32)
-      acx_bulk_g2s(dst + r * (J + 4), src + (size_t)r * J, (uint32_t)(J * 4), reinterpret_cast<uint64_t*>(bar));
+    if (lane < CH / 8)
+      acx_bulk_g2s(dst + lane * (8 * J + 4), src + (size_t)lane * 8 * J, (uint32_t)(8 * J * 4),
+                   reinterpret_cast<uint64_t*>(bar));
   }
   __device__ inline void init(Smem* s, const float* w2, const float* w3, unsigned int ntiles) {
     sm = s; W2 = w2; W3 = w3; g = 0; total = ntiles * P;
@@ -148,30 +148,39 @@ template <int H1, int H3, bool TRAIN> struct Ring {
 struct Coord {
   int a;    // 0..15 : (warp&3)*4 + (lane&3)   -> j-quad (F), k row (B, G)
   int b;    // 0..15 : (warp>>2)*8 + (lane>>2) -> m-quad (F, B), j row (G)
+  int lj, wj;   // (lane&3), (warp&3)
   __device__ inline Coord() {
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-    a = (w & 3) * 4 + (l & 3);
+    lj = l & 3; wj = w & 3;
+    a = wj * 4 + lj;
     b = (w >> 2) * 8 + (l >> 2);
   }
+  // B stage: row of the 64-row weight chunk owned by accumulator i (0..3).  The four lanes that differ in
+  // lj read rows of four different 8-row groups, i.e. 16-byte chunks 4 banks apart: conflict free.
+  __device__ inline int brow(int i) const { return 8 * (lj + 4 * (i & 1)) + 2 * wj + (i >> 1); }
 };
+
+// offset (floats) of row r of a 64-row chunk with J columns inside a ring slot
+template <int J> __device__ inline int slot_row(int r) { return (r >> 3) * (8 * J + 4) + (r & 7) * J; }
 
 // F: acc[jj][mm] += sum_{k<64} W[k][j(jj)] * X[k][4b+mm];  j(jj) = 4a + (jj&3) + 64*(jj>>2)
 template <int TJ>
 __device__ inline void f_stage(const float* __restrict__ slot, const float* __restrict__ X, float (&acc)[TJ][4],
                                const Coord& c) {
-  constexpr int WS = 16 * TJ + 4;
+  constexpr int J = 16 * TJ;
   const float* wp = slot + 4 * c.a;
   const float* xp = X + 4 * c.b;
 #pragma unroll 8
   for (int k = 0; k < CH; ++k) {
     const float4 x = *reinterpret_cast<const float4*>(xp + k * MS);
+    const float* wk = wp + slot_row<J>(k);
     float w[TJ];
     {
-      const float4 t = *reinterpret_cast<const float4*>(wp + k * WS);
+      const float4 t = *reinterpret_cast<const float4*>(wk);
       w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w;
     }
     if (TJ == 8) {
-      const float4 t = *reinterpret_cast<const float4*>(wp + k * WS + 64);
+      const float4 t = *reinterpret_cast<const float4*>(wk + 64);
       w[TJ - 4] = t.x; w[TJ - 3] = t.y; w[TJ - 2] = t.z; w[TJ - 1] = t.w;
     }
 #pragma unroll
@@ -202,12 +211,13 @@ __device__ inline void f_store(float* __restrict__ OUT, const float* __restrict_
   }
 }
 
-// B: out[i][mm] = sum_{j<J} W[a+16i][j] * D[j][4b+mm]   (rows a+16i of the 64-row chunk)
+// B: out[i][mm] = sum_{j<J} W[brow(i)][j] * D[j][4b+mm]   (rows brow(i) of the 64-row chunk)
 template <int J>
 __device__ inline void b_stage(const float* __restrict__ slot, const float* __restrict__ D, float (&acc)[4][4],
                                const Coord& c) {
-  constexpr int WS = J + 4;
-  const float* wp = slot + c.a * WS;
+  const float* wp[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) wp[i] = slot + slot_row<J>(c.brow(i));
   const float* dp = D + 4 * c.b;
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -219,7 +229,7 @@ __device__ inline void b_stage(const float* __restrict__ slot, const float* __re
 #pragma unroll
     for (int jj = 0; jj < 4; ++jj) d[jj] = *reinterpret_cast<const float4*>(dp + (4 * j4 + jj) * MS);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) w[i] = *reinterpret_cast<const float4*>(wp + 16 * i * WS + 4 * j4);
+    for (int i = 0; i < 4; ++i) w[i] = *reinterpret_cast<const float4*>(wp[i] + 4 * j4);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const float wv[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
@@ -233,12 +243,12 @@ __device__ inline void b_stage(const float* __restrict__ slot, const float* __re
     }
   }
 }
-// B epilogue, in place: Y[row0 + a+16i][m] = acc * act'(Y[..][m])
+// B epilogue, in place: Y[row0 + brow(i)][m] = acc * act'(Y[..][m])
 template <bool LRELU>
 __device__ inline void b_store(float* __restrict__ Y, float (&acc)[4][4], const Coord& c) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    float4* p = reinterpret_cast<float4*>(Y + (c.a + 16 * i) * MS + 4 * c.b);
+    float4* p = reinterpret_cast<float4*>(Y + c.brow(i) * MS + 4 * c.b);
     const float4 y = *p;
     float4 o;
     o.x = acc[i][0] * act_grad<LRELU>(y.x);
