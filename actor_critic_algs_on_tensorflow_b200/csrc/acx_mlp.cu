@@ -14,12 +14,12 @@ using namespace acxmlp;
 namespace {
 
 template <int H1, bool LRELU>
-__device__ inline void layer1_chunk(Smem& sm, int c1, int ob) {
-  // X1[c1*64 + r][m] = act(sum_i obs[i][m] * W1[i][k] + b1[k]) for the 64 rows of this chunk
-  const int r = threadIdx.x >> 2, q = (threadIdx.x & 3) * 16, k = c1 * CH + r;
+__device__ inline void layer1_block(Smem& sm, int h, int ob, float* __restrict__ dst) {
+  // dst[r][m] = X1[128h + r][m] = act(sum_i obs[i][m] * W1[i][k] + b1[k]), r < 128, m < 128
+  const int r = threadIdx.x >> 1, q = (threadIdx.x & 1) * 64, k = h * 128 + r;
   const float bk = sm.b1[k];
-#pragma unroll
-  for (int m4 = 0; m4 < 4; ++m4) {
+#pragma unroll 4
+  for (int m4 = 0; m4 < 16; ++m4) {
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int i = 0; i < ob; ++i) {
       const float w = sm.W1[i * H1 + k];
@@ -29,20 +29,22 @@ __device__ inline void layer1_chunk(Smem& sm, int c1, int ob) {
     float4 o;
     o.x = act_fn<LRELU>(__fadd_rn(s.x, bk)); o.y = act_fn<LRELU>(__fadd_rn(s.y, bk));
     o.z = act_fn<LRELU>(__fadd_rn(s.z, bk)); o.w = act_fn<LRELU>(__fadd_rn(s.w, bk));
-    *reinterpret_cast<float4*>(&sm.bufA[r * MS + q + 4 * m4]) = o;
+    *reinterpret_cast<float4*>(dst + r * MS + q + 4 * m4) = o;
   }
 }
 
+// dW1[i][128h + j] (+)= sum_m obs[i][m] * D[j][m], db1 likewise, from a 128-row block D of dPre1
 template <int H1>
-__device__ inline void layer1_grad(Smem& sm, int c1, int ob, float* __restrict__ scrW1, float* __restrict__ scrb1,
-                                   bool first) {
+__device__ inline void layer1_grad(Smem& sm, int h, int ob, const float* __restrict__ D, float* __restrict__ scrW1,
+                                   float* __restrict__ scrb1, bool first) {
   const int j = threadIdx.x;
-  if (j < CH) {
+  if (j < 128) {
     float sb = 0.f, sw[MAX_OB];
 #pragma unroll
     for (int i = 0; i < MAX_OB; ++i) sw[i] = 0.f;
+#pragma unroll 4
     for (int m4 = 0; m4 < MT / 4; ++m4) {
-      const float4 d = *reinterpret_cast<const float4*>(&sm.bufA[j * MS + 4 * m4]);
+      const float4 d = *reinterpret_cast<const float4*>(D + j * MS + 4 * m4);
       sb += d.x; sb += d.y; sb += d.z; sb += d.w;
 #pragma unroll
       for (int i = 0; i < MAX_OB; ++i)
@@ -52,7 +54,7 @@ __device__ inline void layer1_grad(Smem& sm, int c1, int ob, float* __restrict__
           sw[i] = fmaf(o.z, d.z, sw[i]); sw[i] = fmaf(o.w, d.w, sw[i]);
         }
     }
-    const int k = c1 * CH + j;
+    const int k = h * 128 + j;
     scrb1[k] = first ? sb : scrb1[k] + sb;
 #pragma unroll
     for (int i = 0; i < MAX_OB; ++i)
@@ -84,7 +86,7 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
   constexpr bool TRAIN = MODE == MODE_TRAIN;
-  constexpr int TJ3 = H3 / 16, NC1 = H1 / CH;
+  constexpr int TJ3 = H3 / 16, NB = H1 / 128;
   const AcxNetLayout L = A.L;
   const int ob = L.ob, nout = L.nout, tid = threadIdx.x;
   const float* __restrict__ P = A.params;
@@ -103,7 +105,7 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
   const int ntiles = A.rows * tpr;
   const unsigned int mine = ((int)blockIdx.x < ntiles) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   Ring<H1, H3, TRAIN> ring;
-  ring.init(&sm, P + L.W2, P + L.W3, mine);     // __syncthreads inside: small params visible after it
+  ring.init(&sm, P + L.W2, P + L.W3, A.wT, mine);     // __syncthreads inside: small params visible after it
   const Coord c;
 
   const unsigned int step0 = A.step0 + ((MODE == MODE_SAMPLE && A.step_base) ? *A.step_base : 0u);
@@ -128,31 +130,27 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
     }
     __syncthreads();
 
-    // ------------------------------------------------ forward: layers 1+2 (layer 1 recomputed per chunk)
+    // ------------------------------------------------ forward: layers 1+2 (layer 1 recomputed per 128-row block)
     {
-      float acc[8][4];
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-#pragma unroll
-        for (int m = 0; m < 4; ++m) acc[j][m] = 0.f;
-      for (int c1 = 0; c1 < NC1; ++c1) {
-        layer1_chunk<H1, LRELU>(sm, c1, ob);
+      float acc[8][8];
+      f_zero<8>(acc);
+      for (int h = 0; h < NB; ++h) {
+        layer1_block<H1, LRELU>(sm, h, ob, sm.X3);
         __syncthreads();
-        const float* slot = ring.begin();
-        f_stage<8>(slot, sm.bufA, acc, c);
-        __syncthreads();
+        for (int cc = 0; cc < 4; ++cc) {
+          const float* slot = ring.begin();
+          f_stage<8>(slot, sm.X3 + cc * CH * MS, acc, c);
+          __syncthreads();
+        }
       }
       f_store<8, LRELU>(sm.X2, sm.b2, acc, c);
     }
     __syncthreads();
     // ------------------------------------------------ forward: layer 3
     {
-      float acc[TJ3][4];
-#pragma unroll
-      for (int j = 0; j < TJ3; ++j)
-#pragma unroll
-        for (int m = 0; m < 4; ++m) acc[j][m] = 0.f;
-      for (int c3 = 0; c3 < 2; ++c3) {
+      float acc[TJ3][8];
+      f_zero<TJ3>(acc);
+      for (int c3 = 0; c3 < 4; ++c3) {
         const float* slot = ring.begin();
         f_stage<TJ3>(slot, sm.X2 + c3 * CH * MS, acc, c);
         __syncthreads();
@@ -359,7 +357,7 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
     __syncthreads();
     // dPre3 = (Wh . dHead) * act'(X3), in place
     for (int idx = tid; idx < H3 * MT; idx += NT) {
-      const int k = idx >> 6, m = idx & 63;
+      const int k = idx >> 7, m = idx & 127;
       float s = 0.f;
       for (int a = 0; a < nout; ++a) s = fmaf(sm.Wh[k * nout + a], sm.dHead[a * MT + m], s);
       float* x = &sm.X3[k * MS + m];
@@ -369,25 +367,32 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
     g_stage<8, TJ3>(sm.X2, sm.X3, scr + L.W3, H3, first, c);
     bias_grad(sm.X3, H3, scr + L.b3, first);
     __syncthreads();
-    for (int c3 = 0; c3 < 2; ++c3) {      // dPre2 rows c3*64.. = (W3 . dPre3) * act'(X2), in place
-      const float* slot = ring.begin();
-      float acc[4][4];
-      b_stage<H3>(slot, sm.X3, acc, c);
-      b_store<LRELU>(sm.X2 + c3 * CH * MS, acc, c);
-      __syncthreads();
+    {   // dPre2 = (W3 . dPre3) * act'(X2), in place: F-type over the transposed copy W3T[j][k]
+      float acc[8][8];
+      f_zero<8>(acc);
+      for (int c3 = 0; c3 < H3 / CH; ++c3) {
+        const float* slot = ring.begin();
+        f_stage<8>(slot, sm.X3 + c3 * CH * MS, acc, c);
+        __syncthreads();
+      }
+      fb_store<LRELU>(sm.X2, acc, c);
     }
+    __syncthreads();
     bias_grad(sm.X2, H2, scr + L.b2, first);
-    for (int c1 = 0; c1 < NC1; ++c1) {
-      layer1_chunk<H1, LRELU>(sm, c1, ob);
+    for (int h = 0; h < NB; ++h) {
+      layer1_block<H1, LRELU>(sm, h, ob, sm.X3);        // X1 rows 128h.. (dPre3 is dead by now)
       __syncthreads();
-      g_stage<4, 8>(sm.bufA, sm.X2, scr + L.W2 + (size_t)c1 * CH * H2, H2, first, c);
+      g_stage<8, 8>(sm.X3, sm.X2, scr + L.W2 + (size_t)h * 128 * H2, H2, first, c);
+      float acc[8][8];
+      f_zero<8>(acc);
+      for (int cc = 0; cc < 4; ++cc) {                  // dX1 block = W2T_h . dPre2
+        const float* slot = ring.begin();
+        f_stage<8>(slot, sm.X2 + cc * CH * MS, acc, c);
+        __syncthreads();                                // (also: every g_stage read of X3 is done before fb_store)
+      }
+      fb_store<LRELU>(sm.X3, acc, c);                   // dPre1 block, in place over the recomputed X1 block
       __syncthreads();
-      const float* slot = ring.begin();
-      float acc[4][4];
-      b_stage<H2>(slot, sm.X2, acc, c);
-      b_store<LRELU>(sm.bufA, acc, c);    // dPre1 chunk, in place over the recomputed X1 chunk
-      __syncthreads();
-      layer1_grad<H1>(sm, c1, ob, scr + L.W1, scr + L.b1, first);
+      layer1_grad<H1>(sm, h, ob, sm.X3, scr + L.W1, scr + L.b1, first);
       __syncthreads();
     }
     first = false;
@@ -405,7 +410,7 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
 #pragma unroll
   for (int d = 0; d < MAX_OUT; ++d) dl[d] = acx_warp_sum(dls[d]);
   const int w = tid >> 5;
-  if ((tid & 31) == 0 && w < 2) {
+  if ((tid & 31) == 0 && w < 4) {      // the head threads are warps 0..3
 #pragma unroll
     for (int q = 0; q < 4; ++q) sm.red[w][q] = v[q];
 #pragma unroll
@@ -415,11 +420,26 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
   if (tid == 0) {
     if (TRAIN) {
 #pragma unroll
-      for (int q = 0; q < 4; ++q) A.loss_partial[(size_t)blockIdx.x * 4 + q] = sm.red[0][q] + sm.red[1][q];
+      for (int q = 0; q < 4; ++q) A.loss_partial[(size_t)blockIdx.x * 4 + q] = (sm.red[0][q] + sm.red[1][q]) + (sm.red[2][q] + sm.red[3][q]);
       if (HEAD == HEAD_GAUSS)
-        for (int d = 0; d < nout; ++d) scr[L.log_std + d] = sm.dHead[d] + sm.dHead[MAX_OUT + d];
+        for (int d = 0; d < nout; ++d) scr[L.log_std + d] = (sm.dHead[d] + sm.dHead[MAX_OUT + d]) + (sm.dHead[2 * MAX_OUT + d] + sm.dHead[3 * MAX_OUT + d]);
     } else {
-      A.kl_partial[blockIdx.x] = sm.red[0][1] + sm.red[1][1];
+      A.kl_partial[blockIdx.x] = (sm.red[0][1] + sm.red[1][1]) + (sm.red[2][1] + sm.red[3][1]);
+    }
+  }
+}
+
+// wT = [ W3T[j][k] = W3[k][j]  (H3 x 128) | W2T[h][j][kk] = W2[128h + kk][j]  (H1/128 x 128 x 128) ]
+__global__ void __launch_bounds__(256) acx_transpose_weights_kernel(const float* __restrict__ P, AcxNetLayout L,
+                                                                    float* __restrict__ wT) {
+  const int n3 = L.H3 * 128, n2 = L.H1 * 128;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n3 + n2; i += gridDim.x * blockDim.x) {
+    if (i < n3) {
+      const int j = i >> 7, k = i & 127;
+      wT[i] = P[L.W3 + k * L.H3 + j];
+    } else {
+      const int r = i - n3, h = r / (128 * 128), j = (r >> 7) & 127, kk = r & 127;
+      wT[i] = P[L.W2 + (h * 128 + kk) * 128 + j];
     }
   }
 }
@@ -572,7 +592,8 @@ extern "C" int acx_value_forward(const float* critic, int ob_dim, int rows, int 
 extern "C" size_t acx_loss_backward_workspace_bytes(int ob_dim, int num_ac, int cont) {
   const size_t sms = (size_t)acx_num_sms();
   const size_t pa = (size_t)acx_actor_layout(ob_dim, num_ac, cont).size, pc = (size_t)acx_critic_layout(ob_dim).size;
-  return sms * (pa + pc) * sizeof(float) + 2 * sms * 4 * sizeof(double) + 256;
+  const size_t wt = (size_t)(ACX_A_H3 + ACX_A_H1 + ACX_C_H3 + ACX_C_H1) * 128;      // transposed weight copies
+  return sms * (pa + pc) * sizeof(float) + 2 * sms * 4 * sizeof(double) + wt * sizeof(float) + 512;
 }
 
 static int loss_backward(int cont, const float* actor, const float* critic, int ob_dim, int num_ac, float ac_scale,
@@ -592,7 +613,9 @@ static int loss_backward(int cont, const float* actor, const float* critic, int 
   unsigned char* wsb = reinterpret_cast<unsigned char*>(workspace);
   double* lossp_a = reinterpret_cast<double*>(wsb);
   double* lossp_c = lossp_a + (size_t)sms * 4;
-  float* scr_a = reinterpret_cast<float*>(wsb + 2 * (size_t)sms * 4 * sizeof(double) + 128);
+  float* wT_a = reinterpret_cast<float*>(wsb + 2 * (size_t)sms * 4 * sizeof(double) + 128);
+  float* wT_c = wT_a + (size_t)(ACX_A_H3 + ACX_A_H1) * 128;
+  float* scr_a = wT_c + (size_t)(ACX_C_H3 + ACX_C_H1) * 128;
   float* scr_c = scr_a + (size_t)sms * La.size;
   const double count = (double)rows * (double)n;
   if (actor) {
@@ -604,7 +627,9 @@ static int loss_backward(int cont, const float* actor, const float* critic, int 
     a.ac_in_f = cont ? reinterpret_cast<const float*>(acs) : nullptr;
     a.ac_in_i = cont ? nullptr : reinterpret_cast<const int*>(acs);
     a.adv = adv; a.adv_stats = adv_stats; a.logp_old = logp_old; a.opt = opt;
-    a.scratch = scr_a; a.loss_partial = lossp_a;
+    a.scratch = scr_a; a.loss_partial = lossp_a; a.wT = wT_a;
+    acx_transpose_weights_kernel<<<48, 256, 0, st>>>(actor, La, wT_a);
+    ACX_LAUNCH_OK("acx_transpose_weights_kernel(actor)");
     rc = cont ? launch<128, 64, true, HEAD_GAUSS, MODE_TRAIN>(a, grid, st)
               : launch<128, 64, true, HEAD_CAT, MODE_TRAIN>(a, grid, st);
     if (rc) return rc;
@@ -618,7 +643,9 @@ static int loss_backward(int cont, const float* actor, const float* critic, int 
     ACX_REQUIRE(targets && grad_critic, "%s: null critic-side buffer", fn);
     Args a; memset(&a, 0, sizeof(a));
     a.params = critic; a.L = Lc; a.rows = rows; a.n = n; a.obs = obs;
-    a.targets = targets; a.scratch = scr_c; a.loss_partial = lossp_c;
+    a.targets = targets; a.scratch = scr_c; a.loss_partial = lossp_c; a.wT = wT_c;
+    acx_transpose_weights_kernel<<<96, 256, 0, st>>>(critic, Lc, wT_c);
+    ACX_LAUNCH_OK("acx_transpose_weights_kernel(critic)");
     rc = launch<256, 128, false, HEAD_VALUE, MODE_TRAIN>(a, grid, st);
     if (rc) return rc;
     acx_grad_reduce_kernel<<<(Lc.size + 255) / 256, 256, 0, st>>>(scr_c, grid, Lc.size, grad_critic, lossp_c, stats,
