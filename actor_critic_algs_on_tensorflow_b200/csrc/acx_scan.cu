@@ -130,6 +130,56 @@ __global__ void __launch_bounds__(256) acx_scan_cols_kernel(int T, int N, const 
   scan_finish_moments(msum, msq, ws, stats, (long long)T * N);
 }
 
+// Plain (T <= L) column scan, four adjacent env columns per thread: every row access of a warp is one
+// 512-byte burst (float4 rew / V / G / adv, uchar4 done).  Same arithmetic as acx_scan_cols_kernel.
+__global__ void __launch_bounds__(256) acx_scan_cols4_kernel(int T, int N, const float* __restrict__ rew,
+                                                             const unsigned char* __restrict__ done,
+                                                             const float* __restrict__ V, double gamma,
+                                                             float* __restrict__ G, float* __restrict__ adv,
+                                                             ScanWs* ws, float* __restrict__ stats) {
+  double msum = 0, msq = 0;
+  const int N4 = N >> 2;
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < N4; q += gridDim.x * blockDim.x) {
+    const int n = q << 2;
+    const float4 vT = __ldg(reinterpret_cast<const float4*>(V + (size_t)T * N + n));
+    double carry[4] = {0.0, 0.0, 0.0, 0.0};
+    double boot[4] = {(double)vT.x, (double)vT.y, (double)vT.z, (double)vT.w};
+    for (int t1 = T; t1 > 0; t1 -= 4) {
+      const int cnt = t1 < 4 ? t1 : 4;
+      float4 r[4], v[4];
+      uchar4 d[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (i < cnt) {
+          const size_t off = (size_t)(t1 - 1 - i) * N + n;
+          r[i] = __ldg(reinterpret_cast<const float4*>(rew + off));
+          v[i] = __ldg(reinterpret_cast<const float4*>(V + off));
+          d[i] = __ldg(reinterpret_cast<const uchar4*>(done + off));
+        }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (i < cnt) {
+          const size_t off = (size_t)(t1 - 1 - i) * N + n;
+          const float rr[4] = {r[i].x, r[i].y, r[i].z, r[i].w}, vv[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+          const unsigned char dd[4] = {d[i].x, d[i].y, d[i].z, d[i].w};
+          float g[4], a[4];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            if (dd[c]) { carry[c] = 0.0; boot[c] = 0.0; }
+            carry[c] = (double)rr[c] + gamma * (carry[c] + boot[c]);
+            boot[c] = 0.0;
+            g[c] = (float)carry[c];
+            a[c] = (float)(carry[c] - (double)vv[c]);
+            msum += (double)a[c]; msq += (double)a[c] * (double)a[c];
+          }
+          *reinterpret_cast<float4*>(G + off) = make_float4(g[0], g[1], g[2], g[3]);
+          *reinterpret_cast<float4*>(adv + off) = make_float4(a[0], a[1], a[2], a[3]);
+        }
+    }
+  }
+  scan_finish_moments(msum, msq, ws, stats, (long long)T * N);
+}
+
 // affine element of the reverse recurrence x_t = b + a * x_{t+1}; `e` rides along as a min-scan
 struct Aff { double a, b; int e; };
 __device__ inline Aff aff_combine(const Aff& lo, const Aff& hi) {   // lo is earlier in time, applied last
@@ -251,6 +301,10 @@ extern "C" int acx_returns_adv_scan(int T, int n, const float* rew, const unsign
   if (mode == ACX_SCAN_WARP)
     acx_scan_warp_kernel<<<scan_grid(n, 1), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out,
                                                          adv_out, ws, stats_out);
+  else if (T <= look_ahead && (n & 3) == 0 && acx_aligned16(rew) && acx_aligned16(V) && acx_aligned16(G_out) &&
+           acx_aligned16(adv_out) && (reinterpret_cast<uintptr_t>(done) & 3u) == 0)
+    acx_scan_cols4_kernel<<<scan_grid(n / 4, 0), 256, 0, st>>>(T, n, rew, done, V, gamma, G_out, adv_out, ws,
+                                                              stats_out);
   else
     acx_scan_cols_kernel<<<scan_grid(n, 0), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out,
                                                          adv_out, ws, stats_out);

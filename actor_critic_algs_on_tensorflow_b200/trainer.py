@@ -57,7 +57,7 @@ class A2CTrainer:
     def __init__(self, env_id="Pendulum-v0", n_envs=65536, horizon=20, seed=12321, gamma=0.98, look_ahead=40,
                  desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1, actor_lr=0.005, critic_lr=0.001, beta=1.0,
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
-                 critic_params=None, use_graph=True, max_episode_steps=0, process_group=None):
+                 critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=False):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
@@ -74,6 +74,10 @@ class A2CTrainer:
         self.dev = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         self.pg = process_group
         self.use_graph = bool(use_graph)
+        # True: forward passes (rollout sampling, values, post-update log-prob/KL) on tcgen05 with 3xTF32 operand
+        # splits -- verified to the same tolerance, but measured slower than the FFMA engine in round 1
+        # (profiles/r01_tc_forward.md), hence off by default; False keeps every GEMM on the FFMA engine
+        self.tc = bool(tensor_cores)
         d, f32 = self.dev, torch.float32
         N, T = self.N, self.T
 
@@ -114,6 +118,8 @@ class A2CTrainer:
         self.ws_bwd = torch.empty(self.ws_bwd_bytes, device=d, dtype=torch.uint8)
         self.kl_part = torch.zeros(L.load().acx_kl_workspace_bytes() // 8, device=d, dtype=torch.float64)
         self.kl_blocks = ctypes.c_int(0)
+        self.packed_a = torch.zeros(L.load().acx_tc_packed_floats(0, self.ob, self.num_ac, int(self.cont)), device=d)
+        self.packed_c = torch.zeros(L.load().acx_tc_packed_floats(1, self.ob, 1, 0), device=d)
         # optional caller-supplied noise (parity / end-to-end mode), static so graphs can replay on them
         self.noise_buf = None
         self.reset_u_buf = None
@@ -127,10 +133,20 @@ class A2CTrainer:
                int(bool(schedule)), s)
         L.call("acx_env_reset", self.env, N, L.ptr(self.state), L.ptr(self.elapsed), L.ptr(self.obs_buf[0]), None,
                self.seed, self.index0, 0xFFFFFFFF, s)
+        self._pack()
 
     # ------------------------------------------------------------------ pieces (all enqueue on the current stream)
     def _row(self, t, i):      # pointer to row i of a [rows, ...] tensor
         return t.data_ptr() + i * t.stride(0) * t.element_size()
+
+    def _pack(self):
+        """Refresh the tensor-core operand copies of the hidden-layer kernels (after every parameter change)."""
+        if not self.tc:
+            return 0
+        s = L.cur_stream()
+        L.call("acx_tc_pack_weights", 0, L.ptr(self.actor), self.ob, self.num_ac, int(self.cont), L.ptr(self.packed_a), s)
+        L.call("acx_tc_pack_weights", 1, L.ptr(self.critic), self.ob, 1, 0, L.ptr(self.packed_c), s)
+        return 2
 
     def _rollout(self, buffered_noise):
         s, N = L.cur_stream(), self.N
@@ -138,14 +154,19 @@ class A2CTrainer:
         for t in range(self.T):
             noise = None if not buffered_noise else self._row(self.noise_buf, t)
             ru = None if not buffered_noise else self._row(self.reset_u_buf, t)
-            if self.cont:
+            tail = (self._row(self.obs_buf, t), noise, self.seed, self.index0, t, L.ptr(self.step_ctr),
+                    self._row(self.acs, t), self._row(self.logps, t), self._row(self.ent, t), None, s)
+            if self.cont and self.tc:
+                L.call("acx_policy_forward_sample_gauss_tc", L.ptr(self.actor), L.ptr(self.packed_a), self.ob,
+                       self.num_ac, self.ac_scale, 1, N, *tail)
+            elif self.cont:
                 L.call("acx_policy_forward_sample_gauss", L.ptr(self.actor), self.ob, self.num_ac, self.ac_scale, 1, N,
-                       self._row(self.obs_buf, t), noise, self.seed, self.index0, t, L.ptr(self.step_ctr),
-                       self._row(self.acs, t), self._row(self.logps, t), self._row(self.ent, t), None, s)
+                       *tail)
+            elif self.tc:
+                L.call("acx_policy_forward_sample_cat_tc", L.ptr(self.actor), L.ptr(self.packed_a), self.ob, self.n_act,
+                       1, N, *tail)
             else:
-                L.call("acx_policy_forward_sample_cat", L.ptr(self.actor), self.ob, self.n_act, 1, N,
-                       self._row(self.obs_buf, t), noise, self.seed, self.index0, t, L.ptr(self.step_ctr),
-                       self._row(self.acs, t), self._row(self.logps, t), self._row(self.ent, t), None, s)
+                L.call("acx_policy_forward_sample_cat", L.ptr(self.actor), self.ob, self.n_act, 1, N, *tail)
             L.call("acx_env_step", self.env, N, L.ptr(self.state), L.ptr(self.elapsed), self._row(self.acs, t),
                    self._row(self.obs_buf, t + 1), self._row(self.rew, t), self._row(self.done, t), ru, self.seed,
                    self.index0, t, L.ptr(self.step_ctr), self.max_steps, s)
@@ -155,7 +176,11 @@ class A2CTrainer:
 
     def _gradients(self):
         s, N, T = L.cur_stream(), self.N, self.T
-        L.call("acx_value_forward", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V), 0, s)
+        if self.tc:
+            L.call("acx_value_forward_tc", L.ptr(self.critic), L.ptr(self.packed_c), self.ob, T + 1, N,
+                   L.ptr(self.obs_buf), L.ptr(self.V), 0, s)
+        else:
+            L.call("acx_value_forward", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V), 0, s)
         L.call("acx_returns_adv_scan", T, N, L.ptr(self.rew), L.ptr(self.done), L.ptr(self.V), self.gamma,
                self.look_ahead, L.ptr(self.G), L.ptr(self.adv), L.ptr(self.stats), L.ptr(self.ws_scan),
                self.ws_scan_bytes, L.SCAN_AUTO, s)
@@ -168,7 +193,7 @@ class A2CTrainer:
                    self.ac_scale, T, N, *common)
         else:
             L.call("acx_loss_backward_cat", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.n_act, T, N, *common)
-        return 2 + 4
+        return 2 + 6      # value, scan, 2 x (transpose, mlp train, grad reduce)
 
     def _apply(self, grad_scale):
         s, Pa, Pc = L.cur_stream(), self.Pa, self.Pc
@@ -176,18 +201,21 @@ class A2CTrainer:
                L.ptr(self.critic), L.ptr(self.grads[Pa:]), L.ptr(self.m[Pa:]), L.ptr(self.v[Pa:]), Pc, L.ptr(self.opt),
                grad_scale, s)
         L.call("acx_adam_tick", L.ptr(self.opt), s)
-        return 2
+        return 2 + (self._pack() if self.world == 1 or self.mode == "sync" else 0)
 
     def _post_kl(self):
         s, N, T = L.cur_stream(), self.N, self.T
-        if self.cont:
-            L.call("acx_policy_logp_gauss", L.ptr(self.actor), self.ob, self.num_ac, self.ac_scale, T, N,
-                   L.ptr(self.obs_buf), L.ptr(self.acs), None, None, None, L.ptr(self.logps), L.ptr(self.kl_part),
-                   ctypes.byref(self.kl_blocks), s)
+        tail = (T, N, L.ptr(self.obs_buf), L.ptr(self.acs), None, None, None, L.ptr(self.logps), L.ptr(self.kl_part),
+                ctypes.byref(self.kl_blocks), s)
+        if self.cont and self.tc:
+            L.call("acx_policy_logp_gauss_tc", L.ptr(self.actor), L.ptr(self.packed_a), self.ob, self.num_ac,
+                   self.ac_scale, *tail)
+        elif self.cont:
+            L.call("acx_policy_logp_gauss", L.ptr(self.actor), self.ob, self.num_ac, self.ac_scale, *tail)
+        elif self.tc:
+            L.call("acx_policy_logp_cat_tc", L.ptr(self.actor), L.ptr(self.packed_a), self.ob, self.n_act, *tail)
         else:
-            L.call("acx_policy_logp_cat", L.ptr(self.actor), self.ob, self.n_act, T, N, L.ptr(self.obs_buf),
-                   L.ptr(self.acs), None, None, None, L.ptr(self.logps), L.ptr(self.kl_part),
-                   ctypes.byref(self.kl_blocks), s)
+            L.call("acx_policy_logp_cat", L.ptr(self.actor), self.ob, self.n_act, *tail)
         L.call("acx_kl_finalize", L.ptr(self.kl_part), self.kl_blocks.value, float(T) * float(N), L.ptr(self.stats), s)
         return 2
 
@@ -256,7 +284,7 @@ class A2CTrainer:
             self.params.sub_(self.old_params)                      # this worker's delta
             self._allreduce(self.params)                           # every worker's push lands
             self.params.add_(self.old_params)                      # pull
-            n += self._run("c", lambda: self._post_kl() + self._lr_update())
+            n += self._run("c", lambda: self._pack() + self._post_kl() + self._lr_update())
         self.iterations += 1
         self.launches_per_iteration = n
         return n

@@ -161,6 +161,18 @@ def kernel_table(tr, flush, hbm_peak):
         "acx_policy_logp_gauss", L.ptr(tr.actor), tr.ob, tr.num_ac, tr.ac_scale, T, N, L.ptr(tr.obs_buf), L.ptr(tr.acs),
         None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part), __import__("ctypes").byref(tr.kl_blocks), s),
         FLOP_ACTOR_FWD * B, None)
+    TC_PEAK = None      # set by the caller through kernel_table.tc_peak
+    ks["value_forward_tc (K2, tcgen05 3xTF32)"] = (lambda: L.call(
+        "acx_value_forward_tc", L.ptr(tr.critic), L.ptr(tr.packed_c), tr.ob, T + 1, N, L.ptr(tr.obs_buf), L.ptr(tr.V), 0, s),
+        FLOP_CRITIC_FWD * (T + 1) * N, "tc")
+    ks["policy_forward_sample_tc (K2, tcgen05 3xTF32)"] = (lambda: L.call(
+        "acx_policy_forward_sample_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, 1, N,
+        L.ptr(tr.obs_buf), None, tr.seed, 0, 0, None, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent), None, s),
+        FLOP_ACTOR_FWD * N, "tc")
+    ks["policy_logp_kl_tc (K2/K5, tcgen05 3xTF32)"] = (lambda: L.call(
+        "acx_policy_logp_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, T, N,
+        L.ptr(tr.obs_buf), L.ptr(tr.acs), None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part),
+        __import__("ctypes").byref(tr.kl_blocks), s), FLOP_ACTOR_FWD * B, "tc")
     import torch
     st2, el2 = tr.state.clone(), tr.elapsed.clone()
     ks["env_step pendulum (K1)"] = (lambda: L.call(
@@ -178,11 +190,12 @@ def kernel_table(tr, flush, hbm_peak):
     # 1,048,576-env size of BASELINE configs[4] (env kernels) / a 1M-column scan
     NB = 1 << 20
     from actor_critic_algs_on_tensorflow_b200.envs import VecEnv
-    for env_name, nb in (("Pendulum-v0", 45.0), ("CartPole-v0", 65.0), ("Acrobot-v1", 73.0)):
-        ve = VecEnv(env_name, NB, seed=1)
+    for env_name, nb, nenv in (("Pendulum-v0", 45.0, NB), ("CartPole-v0", 65.0, NB), ("Acrobot-v1", 73.0, NB),
+                               ("Pendulum-v0", 45.0, 8 * NB), ("CartPole-v0", 65.0, 8 * NB)):
+        ve = VecEnv(env_name, nenv, seed=1)
         ve.reset()
-        act = (torch.zeros(NB, device="cuda") if ve.n_actions == 0 else torch.ones(NB, device="cuda", dtype=torch.int32))
-        ks["env_step %s, 1M envs (K1)" % env_name] = ((lambda ve=ve, act=act: ve.step(act)), None, nb * NB)
+        act = (torch.zeros(nenv, device="cuda") if ve.n_actions == 0 else torch.ones(nenv, device="cuda", dtype=torch.int32))
+        ks["env_step %s, %dM envs (K1)" % (env_name, nenv >> 20)] = ((lambda ve=ve, act=act: ve.step(act)), None, nb * nenv)
     rB, dB = torch.randn((T, NB), device="cuda"), torch.zeros((T, NB), device="cuda", dtype=torch.uint8)
     vB, gB, aB = torch.randn((T + 1, NB), device="cuda"), torch.empty((T, NB), device="cuda"), torch.empty((T, NB), device="cuda")
     wsB = torch.zeros(L.load().acx_returns_adv_workspace_bytes(T, NB), device="cuda", dtype=torch.uint8)
@@ -192,7 +205,14 @@ def kernel_table(tr, flush, hbm_peak):
     out = {}
     for name, (fn, flops, nbytes) in ks.items():
         sec = time_kernel(fn, flush)
-        if flops is not None:
+        if nbytes == "tc":
+            # algorithmic FLOPs (one product per MAC) against TF32 dense peak / 3: every product costs three MMAs
+            ach = flops / sec / 1e12
+            peak = kernel_table.bf16_peak / 2.0 / 3.0
+            out[name] = {"bound": "tensor", "ms": sec * 1e3, "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+                         "frac": ach / peak, "peak_note": "measured bf16 peak / 2 (tf32) / 3 (3xTF32 split)",
+                         "frac_of_fp32_ffma_peak": ach / FP32_PEAK_TFLOPS}
+        elif flops is not None:
             ach = flops / sec / 1e12
             out[name] = {"bound": "fp32", "ms": sec * 1e3, "achieved": ach, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
                          "frac": ach / FP32_PEAK_TFLOPS}
@@ -213,7 +233,7 @@ def run_ours(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     hbm_peak, bf16_peak, peaks_src = measured_peaks()
     tr = A2CTrainer(ENV_ID, n_envs=N_ENVS, horizon=HORIZON, seed=SEED, rank=rank, world=world, mode=args.mode,
-                    use_graph=not args.no_graph)
+                    use_graph=not args.no_graph, tensor_cores=args.tc)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
 
     def flush():
@@ -286,6 +306,7 @@ def run_ours(args, rank, local_rank, world):
     d2h = stats_h.numel() * 4 + params_h.numel() * 4
 
     if rank == 0:
+        kernel_table.bf16_peak = bf16_peak
         kernels = kernel_table(tr, flush, hbm_peak)
         dom = kernels["loss_backward_critic (K4)"]
         step_ms = sec / args.steps * 1e3
@@ -303,6 +324,7 @@ def run_ours(args, rank, local_rank, world):
                 "config": {"workload": WORKLOAD, "envs_per_gpu": N_ENVS, "horizon": HORIZON, "mode": args.mode,
                            "l2": "flushed (256 MiB write) between timed steps", "weights": "glorot-uniform, seed 12321",
                            "rng": "device Philox4x32-10", "cuda_graphs": not args.no_graph,
+                           "forward_engine": "tcgen05 3xTF32" if tr.tc else "fp32 FFMA", "backward_engine": "fp32 FFMA",
                            "parallelism": "dp%d (envs sharded by rank, NCCL all-reduce of the flat gradient)" % world},
                 "e2e": {"value": world * steps_per_it * args.steps / e_sec, "unit": "env-steps/s",
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e_sec / args.steps * 1e3},
@@ -328,6 +350,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--mode", choices=["sync", "async"], default="sync")
     ap.add_argument("--no_graph", action="store_true", help="launch kernels eagerly (for ncu launch lists)")
+    ap.add_argument("--tc", action="store_true", help="forward passes on the tcgen05 3xTF32 engine (slower in round 1)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))

@@ -38,12 +38,13 @@ def _cmp_iteration(tr, st, cont):
     np.testing.assert_allclose(got["act_lr"], st["actor_lr"], rtol=1e-6)
 
 
+@pytest.mark.parametrize("tensor_cores", [False, True])
 @pytest.mark.parametrize("env_id,env,N,T", [("Pendulum-v0", E.PENDULUM, 256, 8), ("CartPole-v0", E.CARTPOLE, 192, 12),
                                             ("Acrobot-v1", E.ACROBOT, 128, 6)])
-def test_first_iteration_matches_oracle(env_id, env, N, T):
+def test_first_iteration_matches_oracle(env_id, env, N, T, tensor_cores):
     S = a2c.A2CState(env, N, seed=777)
     tr = A2CTrainer(env_id, n_envs=N, horizon=T, seed=777, actor_params=S.actor.copy(), critic_params=S.critic.copy(),
-                    use_graph=False, max_episode_steps=5 if env != E.PENDULUM else 0)
+                    use_graph=False, max_episode_steps=5 if env != E.PENDULUM else 0, tensor_cores=tensor_cores)
     np.testing.assert_array_equal(tr.state.cpu().numpy(), S.state)          # Philox reset, exact
     tr.iteration()
     torch.cuda.synchronize()
