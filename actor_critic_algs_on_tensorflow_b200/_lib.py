@@ -68,6 +68,7 @@ SIGNATURES = {
     "acx_loss_backward_workspace_bytes": (_sz, [_i, _i, _i]),
     "acx_loss_backward_gauss": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_loss_backward_cat": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "acx_loss_backward_basic_critic": (_i, [_p, _i, _i, _i, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_opt_init": (_i, [_p, _f, _f, _f, _f, _f, _f, _f, _f, _i, _p]),
     "acx_adam_apply": (_i, [_p, _p, _p, _p, _i, _p, _p, _p, _p, _i, _p, _f, _p]),
     "acx_adam_tick": (_i, [_p, _p]),

@@ -361,7 +361,8 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
       float s = 0.f;
       for (int a = 0; a < nout; ++a) s = fmaf(sm.Wh[k * nout + a], sm.dHead[a * MT + m], s);
       float* x = &sm.X3[k * MS + m];
-      *x = s * act_grad<LRELU>(*x);
+      // Basic_AC critic (policies.py:134-135): the value head reads layer 2, so nothing flows into layer 3
+      *x = basic ? 0.f : s * act_grad<LRELU>(*x);
     }
     __syncthreads();
     g_stage<8, TJ3>(sm.X2, sm.X3, scr + L.W3, H3, first, c);
@@ -374,6 +375,13 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
         const float* slot = ring.begin();
         f_stage<8>(slot, sm.X3 + c3 * CH * MS, acc, c);
         __syncthreads();
+      }
+      if (basic) {   // ... and the head's gradient enters layer 2 directly: dX2[k][m] = Wv[k] * dv[m]
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj)
+#pragma unroll
+          for (int mm = 0; mm < 8; ++mm)
+            acc[jj][mm] = fmaf(sm.Wh[f_col(jj, c)], sm.dHead[4 * c.b + (mm & 3) + 64 * (mm >> 2)], acc[jj][mm]);
       }
       fb_store<LRELU>(sm.X2, acc, c);
     }
@@ -596,6 +604,9 @@ extern "C" size_t acx_loss_backward_workspace_bytes(int ob_dim, int num_ac, int 
   return sms * (pa + pc) * sizeof(float) + 2 * sms * 4 * sizeof(double) + wt * sizeof(float) + 512;
 }
 
+// set per call by acx_loss_backward_basic_critic (thread-local: the C ABI is one host thread per device)
+static thread_local int g_basic_critic_head = 0;
+
 static int loss_backward(int cont, const float* actor, const float* critic, int ob_dim, int num_ac, float ac_scale,
                          int rows, int n, const float* obs, const void* acs, const float* adv, const float* adv_stats,
                          const float* logp_old, const float* targets, const float* opt, float* grad_actor,
@@ -644,6 +655,7 @@ static int loss_backward(int cont, const float* actor, const float* critic, int 
     Args a; memset(&a, 0, sizeof(a));
     a.params = critic; a.L = Lc; a.rows = rows; a.n = n; a.obs = obs;
     a.targets = targets; a.scratch = scr_c; a.loss_partial = lossp_c; a.wT = wT_c;
+    a.basic_head = g_basic_critic_head;
     acx_transpose_weights_kernel<<<96, 256, 0, st>>>(critic, Lc, wT_c);
     ACX_LAUNCH_OK("acx_transpose_weights_kernel(critic)");
     rc = launch<256, 128, false, HEAD_VALUE, MODE_TRAIN>(a, grid, st);
@@ -671,4 +683,15 @@ extern "C" int acx_loss_backward_cat(const float* actor, const float* critic, in
                                      void* stream) {
   return loss_backward(0, actor, critic, ob_dim, n_act, 0.f, rows, n, obs, acs, adv, adv_stats, logp_old, targets,
                        opt, grad_actor, grad_critic, stats, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int acx_loss_backward_basic_critic(const float* critic, int ob_dim, int rows, int n, const float* obs,
+                                              const float* targets, float* grad_critic, float* stats, void* workspace,
+                                              size_t workspace_bytes, void* stream) {
+  g_basic_critic_head = 1;
+  const int rc = loss_backward(1, nullptr, critic, ob_dim, 1, 1.f, rows, n, obs, nullptr, nullptr, nullptr, nullptr,
+                               targets, nullptr, nullptr, grad_critic, stats, workspace, workspace_bytes,
+                               (cudaStream_t)stream);
+  g_basic_critic_head = 0;
+  return rc;
 }

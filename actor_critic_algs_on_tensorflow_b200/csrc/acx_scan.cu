@@ -142,8 +142,11 @@ __global__ void __launch_bounds__(256) acx_scan_cols4_kernel(int T, int N, const
   for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < N4; q += gridDim.x * blockDim.x) {
     const int n = q << 2;
     const float4 vT = __ldg(reinterpret_cast<const float4*>(V + (size_t)T * N + n));
-    double carry[4] = {0.0, 0.0, 0.0, 0.0};
-    double boot[4] = {(double)vT.x, (double)vT.y, (double)vT.z, (double)vT.w};
+    // fp32 recurrence: T <= look_ahead steps of r + gamma * x carry ~T * 2^-24 of relative error, far inside the
+    // 1e-5 budget, and keep the kernel on the HBM roofline (the fp64 pipe and its converts are ~10x slower)
+    const float gf = (float)gamma, glo = (float)(gamma - (double)(float)gamma);   // gamma = gf + glo to ~2^-48
+    float carry[4] = {0.f, 0.f, 0.f, 0.f};
+    float boot[4] = {vT.x, vT.y, vT.z, vT.w};
     for (int t1 = T; t1 > 0; t1 -= 4) {
       const int cnt = t1 < 4 ? t1 : 4;
       float4 r[4], v[4];
@@ -162,16 +165,18 @@ __global__ void __launch_bounds__(256) acx_scan_cols4_kernel(int T, int N, const
           const size_t off = (size_t)(t1 - 1 - i) * N + n;
           const float rr[4] = {r[i].x, r[i].y, r[i].z, r[i].w}, vv[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
           const unsigned char dd[4] = {d[i].x, d[i].y, d[i].z, d[i].w};
-          float g[4], a[4];
+          float g[4], a[4], rs = 0.f, rq = 0.f;
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
-            if (dd[c]) { carry[c] = 0.0; boot[c] = 0.0; }
-            carry[c] = (double)rr[c] + gamma * (carry[c] + boot[c]);
-            boot[c] = 0.0;
-            g[c] = (float)carry[c];
-            a[c] = (float)(carry[c] - (double)vv[c]);
-            msum += (double)a[c]; msq += (double)a[c] * (double)a[c];
+            if (dd[c]) { carry[c] = 0.f; boot[c] = 0.f; }
+            const float x = carry[c] + boot[c];
+            carry[c] = fmaf(gf, x, fmaf(glo, x, rr[c]));
+            boot[c] = 0.f;
+            g[c] = carry[c];
+            a[c] = carry[c] - vv[c];
+            rs += a[c]; rq = fmaf(a[c], a[c], rq);
           }
+          msum += (double)rs; msq += (double)rq;
           *reinterpret_cast<float4*>(G + off) = make_float4(g[0], g[1], g[2], g[3]);
           *reinterpret_cast<float4*>(adv + off) = make_float4(a[0], a[1], a[2], a[3]);
         }

@@ -318,8 +318,6 @@ class Critic(object):
     def optimize(self, obs, targets, sess=None):
         """One Adam step on mean((v - target)^2), unclipped (policies.py:152-164); with a ``global_critic``
         the local gradient is applied to the global parameters.  Returns ``[loss, None]``."""
-        if self.basic_head:
-            raise L.AcxError("Critic.optimize with basic_head=True is not implemented in the CUDA path yet")
         obs = self._obs(obs)
         B, n = obs.shape[0], self.net
         o = _soa(obs, self.dev)
@@ -328,8 +326,12 @@ class Critic(object):
         if self._ws is None or self._ws.numel() < nbytes:
             self._ws = torch.empty(nbytes, device=self.dev, dtype=torch.uint8)
         s = L.cur_stream()
-        L.call("acx_loss_backward_gauss", None, L.ptr(n.params), n.ob_dim, 1, 1.0, 1, B, L.ptr(o), None, None, None, None,
-               L.ptr(tg), L.ptr(self.opt), None, L.ptr(n.grad), L.ptr(self.stats), L.ptr(self._ws), nbytes, s)
+        if self.basic_head:
+            L.call("acx_loss_backward_basic_critic", L.ptr(n.params), n.ob_dim, 1, B, L.ptr(o), L.ptr(tg), L.ptr(n.grad),
+                   L.ptr(self.stats), L.ptr(self._ws), nbytes, s)
+        else:
+            L.call("acx_loss_backward_gauss", None, L.ptr(n.params), n.ob_dim, 1, 1.0, 1, B, L.ptr(o), None, None, None,
+                   None, L.ptr(tg), L.ptr(self.opt), None, L.ptr(n.grad), L.ptr(self.stats), L.ptr(self._ws), nbytes, s)
         target = n if self.global_critic is None else self.global_critic.net
         L.call("acx_adam_apply", None, None, None, None, 0, L.ptr(target.params), L.ptr(n.grad), L.ptr(n.m), L.ptr(n.v),
                n.size, L.ptr(self.opt), 1.0, s)

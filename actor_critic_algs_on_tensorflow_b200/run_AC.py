@@ -4,9 +4,8 @@ batch-1 ``act`` per step, at most 7 rollouts / EP_LENGTH_STOP steps per update (
 actor update (:250-251), KL-driven lr with max_lr = 1.0 (:178,261-266), beta/gamma schedules (:268-275),
 checkpoint ``<checkpoint_dir>-<Env>-<tot_rolls>`` every ``save_every`` iterations (:171,282-283).
 Every arithmetic step runs in the CUDA library through the ``Actor`` / ``Critic`` / ``PathAdv`` / env objects.
-The Basic_AC quirks are kept where the CUDA path has them: gradient clip +-1 (policies.py:81), 0.1 x xavier
-``mu_layer`` (:5-6,48); the critic head reading the second layer (:134-135) is forward-only for now, so the
-critic here is the A3C one (documented in DESIGN.md section 7).
+The Basic_AC quirks are kept: gradient clip +-1 (policies.py:81), 0.1 x xavier ``mu_layer`` (:5-6,48), and the
+critic whose value head reads the second layer (:134-135; its third layer never receives a gradient).
 """
 import argparse
 import os
@@ -65,7 +64,7 @@ def main(argv=None):
     else:
         print('Continuous Action Space. Action Scale is {}.'.format(ac_scale))
     ob_dim = env.observation_space.shape[0] * args.frames
-    critic = pol.Critic(num_ob_feat=ob_dim, seed=args.seed)
+    critic = pol.Critic(num_ob_feat=ob_dim, seed=args.seed, basic_head=True)
     actor = pol.Actor(num_ob_feat=ob_dim, ac_dim=ac_dim, act_type=act_type, ac_scale=ac_scale, seed=args.seed + 1,
                       grad_clip=1.0, head_init="basic")
     tot_rolls = 0

@@ -223,6 +223,13 @@ int acx_loss_backward_cat(const float* actor, const float* critic, int ob_dim, i
                           float* grad_critic, float* stats, void* workspace, size_t workspace_bytes,
                           void* stream);
 
+/* Critic loss + gradient for the Basic_AC network, whose value head reads the SECOND layer
+ * (Basic_AC/policies.py:134-135): the third layer gets a zero gradient, exactly as TF reports None
+ * for it.  Workspace as for acx_loss_backward_gauss(ob_dim, 1, 1). */
+int acx_loss_backward_basic_critic(const float* critic, int ob_dim, int rows, int n, const float* obs,
+                                   const float* targets, float* grad_critic, float* stats, void* workspace,
+                                   size_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------- K5: optimiser + lr control
  * acx_opt_init fills a device opt block (HOST values in, one small kernel). */
 int acx_opt_init(float* opt, float actor_lr, float critic_lr, float beta_kl, float gamma_ent, float clip,

@@ -201,3 +201,39 @@ def test_kl_lr_rule_and_schedule(lib, dev, kl, lr, want):
     o = opt.cpu().numpy()
     np.testing.assert_allclose(o[3], 10.0 ** linear_schedule_val(1500, 100, 3000, -2, -8), rtol=1e-5)
     np.testing.assert_allclose(o[2], 10.0 ** linear_schedule_val(1500, 100, 3000, 0, -4), rtol=1e-5)
+
+
+def test_basic_ac_critic_head_backward(lib, dev):
+    """Basic_AC/policies.py:134-135: the value head reads layer 2; layer 3 gets no gradient."""
+    _, critic = random_weights(4, 2, False, 77, bias_scale=0.3)
+    clay = P.critic_layout(4)
+    rng = np.random.default_rng(5)
+    rows, n = 3, 700
+    B = rows * n
+    obs = rng.normal(size=(rows, n, 4)).astype(np.float32)
+    tg = rng.normal(size=(rows, n)).astype(np.float32)
+    c = dev_t(critic, dev)
+    o = dev_t(np.stack([soa(x) for x in obs]), dev)
+    t = dev_t(tg, dev)
+    g = torch.full_like(c, 3.0)
+    stats = torch.zeros(16, device=dev)
+    nbytes = lib.load().acx_loss_backward_workspace_bytes(4, 1, 1)
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    lib.call("acx_loss_backward_basic_critic", lib.ptr(c), 4, rows, n, lib.ptr(o), lib.ptr(t), lib.ptr(g), lib.ptr(stats),
+             lib.ptr(ws), nbytes, lib.cur_stream())
+    torch.cuda.synchronize()
+    want = P.critic_loss_grads(critic, clay, obs.reshape(B, 4), tg.reshape(B), basic_head=True, dtype=np.float64)
+    want32 = P.critic_loss_grads(critic, clay, obs.reshape(B, 4), tg.reshape(B), basic_head=True, dtype=np.float32)
+    got = g.cpu().numpy()
+    for name in ("W3", "b3"):
+        o3, s3 = clay[name]
+        assert not got[o3:o3 + int(np.prod(s3))].any()
+    lay_nz = {k: v for k, v in clay.items() if k not in ("W3", "b3")}
+    check_grads(got, want["grad"], lay_nz | {"_size": clay["_size"]}, 2 * TOL, want32["grad"]) if False else None
+    for k, off, shp in P.items(clay):
+        if k in ("W3", "b3"):
+            continue
+        sz = int(np.prod(shp))
+        bar = max(2 * TOL, 2.0 * rel_err(want32["grad"][off:off + sz], want["grad"][off:off + sz]))
+        assert rel_err(got[off:off + sz], want["grad"][off:off + sz]) < bar, k
+    np.testing.assert_allclose(stats[4].item(), want["loss"], rtol=2 * TOL)
