@@ -81,7 +81,7 @@ __device__ inline void head_pre(const Smem& sm, const float* __restrict__ Xh, in
     if (a < nout) pre[a] = __fadd_rn(pre[a], sm.bh[a]);
 }
 
-template <int H1, int H3, bool LRELU, int HEAD, int MODE>
+template <int H1, int H3, bool LRELU, int HEAD, int MODE, bool REUSE = false>
 __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
   const int tpr = (A.n + MT - 1) / MT;
   const int ntiles = A.rows * tpr;
   const unsigned int mine = ((int)blockIdx.x < ntiles) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  Ring<H1, H3, TRAIN> ring;
+  Ring<H1, H3, TRAIN, REUSE> ring;
   ring.init(&sm, P + L.W2, P + L.W3, A.wT, mine);     // __syncthreads inside: small params visible after it
   const Coord c;
 
@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
   }
   float* __restrict__ scr = TRAIN ? A.scratch + (size_t)blockIdx.x * L.size : nullptr;
   bool first = true;
+  unsigned int act_phase = 0;
   if (TRAIN && tid < L.size - L.bh) scr[L.bh + tid] = 0.f;     // head bias / log_std slots incl. alignment padding
 
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -130,6 +131,26 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
     }
     __syncthreads();
 
+    const bool vec_ok = (A.n & 3) == 0;          // tile rows start on 16-byte boundaries of the cache
+    if (REUSE) {
+      // ---------------------------------------------- layers 2 and 3 come from the activation cache
+      const float* g2 = A.x2_in + ((size_t)row * H2) * A.n + n0;
+      const float* g3 = A.x3_in + ((size_t)row * H3) * A.n + n0;
+      if (vec_ok && valid == MT) {
+        // full tile: every row is 512 contiguous, 16-byte aligned bytes -> one bulk-TMA copy per row, all in flight
+        uint64_t* bar = reinterpret_cast<uint64_t*>(&sm.bar_act);
+        if (tid == 0) acx_mbar_expect_tx(bar, (uint32_t)((H2 + H3) * MT * 4));
+        __syncthreads();      // the expect_tx is registered before any copy can complete; X2/X3 are idle by now
+        if (tid < H2) acx_bulk_g2s(sm.X2 + tid * MS, g2 + (size_t)tid * A.n, MT * 4, bar);
+        else if (tid - H2 < H3) acx_bulk_g2s(sm.X3 + (tid - H2) * MS, g3 + (size_t)(tid - H2) * A.n, MT * 4, bar);
+        acx_mbar_wait(bar, act_phase & 1u);
+        ++act_phase;
+      } else {
+        load_tile(sm.X2, g2, (size_t)A.n, H2, valid, vec_ok);
+        load_tile(sm.X3, g3, (size_t)A.n, H3, valid, vec_ok);
+      }
+      __syncthreads();
+    } else {
     // ------------------------------------------------ forward: layers 1+2 (layer 1 recomputed per 128-row block)
     {
       float acc[8][8];
@@ -143,7 +164,8 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
           __syncthreads();
         }
       }
-      f_store<8, LRELU>(sm.X2, sm.b2, acc, c);
+      f_store<8, LRELU>(sm.X2, sm.b2, acc, c, A.x2_out ? A.x2_out + ((size_t)row * H2) * A.n + n0 : nullptr,
+                        (size_t)A.n, valid, vec_ok);
     }
     __syncthreads();
     // ------------------------------------------------ forward: layer 3
@@ -155,9 +177,11 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
         f_stage<TJ3>(slot, sm.X2 + c3 * CH * MS, acc, c);
         __syncthreads();
       }
-      f_store<TJ3, LRELU>(sm.X3, sm.b3, acc, c);
+      f_store<TJ3, LRELU>(sm.X3, sm.b3, acc, c, A.x3_out ? A.x3_out + ((size_t)row * H3) * A.n + n0 : nullptr,
+                          (size_t)A.n, valid, vec_ok);
     }
     __syncthreads();
+    }
 
     // ------------------------------------------------ head (one thread per sample)
     const bool basic = (HEAD == HEAD_VALUE) && A.basic_head;
@@ -481,9 +505,9 @@ __global__ void __launch_bounds__(256) acx_grad_reduce_kernel(const float* __res
 }
 
 // ------------------------------------------------------------------ host side
-template <int H1, int H3, bool LRELU, int HEAD, int MODE>
+template <int H1, int H3, bool LRELU, int HEAD, int MODE, bool REUSE = false>
 int launch(const Args& a, int grid, cudaStream_t st) {
-  auto kern = acx_mlp_kernel<H1, H3, LRELU, HEAD, MODE>;
+  auto kern = acx_mlp_kernel<H1, H3, LRELU, HEAD, MODE, REUSE>;
   static bool configured[64] = {false};
   int dev = 0;
   ACX_CUDA_OK(cudaGetDevice(&dev));
@@ -515,10 +539,10 @@ int check_common(const char* fn, const float* params, int ob_dim, int nout, int 
 
 }  // namespace
 
-extern "C" int acx_policy_forward_sample_gauss(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows,
-                                               int n, const float* obs, const float* eps, uint64_t seed,
-                                               uint64_t index0, uint32_t step0, const uint32_t* step_base, float* ac_out,
-                                               float* logp_out, float* ent_out, float* mu_out, void* stream) {
+static int sample_gauss(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows, int n, const float* obs,
+                        const float* eps, uint64_t seed, uint64_t index0, uint32_t step0, const uint32_t* step_base,
+                        float* ac_out, float* logp_out, float* ent_out, float* mu_out, float* x2_out, float* x3_out,
+                        void* stream) {
   int rc = check_common("acx_policy_forward_sample_gauss", actor, ob_dim, ac_dim, rows, n, obs);
   if (rc) return rc;
   if (rows == 0 || n == 0) return ACX_OK;
@@ -528,13 +552,32 @@ extern "C" int acx_policy_forward_sample_gauss(const float* actor, int ob_dim, i
   a.params = actor; a.L = acx_actor_layout(ob_dim, ac_dim, 1); a.rows = rows; a.n = n; a.obs = obs;
   a.ac_scale = ac_scale; a.noise = eps; a.seed = seed; a.index0 = index0; a.step0 = step0; a.step_base = step_base;
   a.ac_out_f = ac_out; a.logp_out = logp_out; a.ent_out = ent_out; a.head_out = mu_out;
+  a.x2_out = x2_out; a.x3_out = x3_out;
   return launch<128, 64, true, HEAD_GAUSS, MODE_SAMPLE>(a, tile_grid(rows, n), (cudaStream_t)stream);
 }
 
-extern "C" int acx_policy_forward_sample_cat(const float* actor, int ob_dim, int n_act, int rows, int n,
-                                             const float* obs, const float* u, uint64_t seed, uint64_t index0,
-                                             uint32_t step0, const uint32_t* step_base, int* ac_out, float* logp_out,
-                                             float* ent_out, float* logits_out, void* stream) {
+extern "C" int acx_policy_forward_sample_gauss(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows,
+                                               int n, const float* obs, const float* eps, uint64_t seed,
+                                               uint64_t index0, uint32_t step0, const uint32_t* step_base, float* ac_out,
+                                               float* logp_out, float* ent_out, float* mu_out, void* stream) {
+  return sample_gauss(actor, ob_dim, ac_dim, ac_scale, rows, n, obs, eps, seed, index0, step0, step_base, ac_out,
+                      logp_out, ent_out, mu_out, nullptr, nullptr, stream);
+}
+
+extern "C" int acx_policy_forward_sample_gauss_cached(const float* actor, int ob_dim, int ac_dim, float ac_scale,
+                                                      int rows, int n, const float* obs, const float* eps,
+                                                      uint64_t seed, uint64_t index0, uint32_t step0,
+                                                      const uint32_t* step_base, float* ac_out, float* logp_out,
+                                                      float* ent_out, float* mu_out, float* x2_out, float* x3_out,
+                                                      void* stream) {
+  ACX_REQUIRE(x2_out && x3_out, "acx_policy_forward_sample_gauss_cached: null activation cache");
+  return sample_gauss(actor, ob_dim, ac_dim, ac_scale, rows, n, obs, eps, seed, index0, step0, step_base, ac_out,
+                      logp_out, ent_out, mu_out, x2_out, x3_out, stream);
+}
+
+static int sample_cat(const float* actor, int ob_dim, int n_act, int rows, int n, const float* obs, const float* u,
+                      uint64_t seed, uint64_t index0, uint32_t step0, const uint32_t* step_base, int* ac_out,
+                      float* logp_out, float* ent_out, float* logits_out, float* x2_out, float* x3_out, void* stream) {
   int rc = check_common("acx_policy_forward_sample_cat", actor, ob_dim, n_act, rows, n, obs);
   if (rc) return rc;
   if (rows == 0 || n == 0) return ACX_OK;
@@ -543,7 +586,26 @@ extern "C" int acx_policy_forward_sample_cat(const float* actor, int ob_dim, int
   a.params = actor; a.L = acx_actor_layout(ob_dim, n_act, 0); a.rows = rows; a.n = n; a.obs = obs;
   a.noise = u; a.seed = seed; a.index0 = index0; a.step0 = step0; a.step_base = step_base;
   a.ac_out_i = ac_out; a.logp_out = logp_out; a.ent_out = ent_out; a.head_out = logits_out;
+  a.x2_out = x2_out; a.x3_out = x3_out;
   return launch<128, 64, true, HEAD_CAT, MODE_SAMPLE>(a, tile_grid(rows, n), (cudaStream_t)stream);
+}
+
+extern "C" int acx_policy_forward_sample_cat(const float* actor, int ob_dim, int n_act, int rows, int n,
+                                             const float* obs, const float* u, uint64_t seed, uint64_t index0,
+                                             uint32_t step0, const uint32_t* step_base, int* ac_out, float* logp_out,
+                                             float* ent_out, float* logits_out, void* stream) {
+  return sample_cat(actor, ob_dim, n_act, rows, n, obs, u, seed, index0, step0, step_base, ac_out, logp_out, ent_out,
+                    logits_out, nullptr, nullptr, stream);
+}
+
+extern "C" int acx_policy_forward_sample_cat_cached(const float* actor, int ob_dim, int n_act, int rows, int n,
+                                                    const float* obs, const float* u, uint64_t seed, uint64_t index0,
+                                                    uint32_t step0, const uint32_t* step_base, int* ac_out,
+                                                    float* logp_out, float* ent_out, float* logits_out, float* x2_out,
+                                                    float* x3_out, void* stream) {
+  ACX_REQUIRE(x2_out && x3_out, "acx_policy_forward_sample_cat_cached: null activation cache");
+  return sample_cat(actor, ob_dim, n_act, rows, n, obs, u, seed, index0, step0, step_base, ac_out, logp_out, ent_out,
+                    logits_out, x2_out, x3_out, stream);
 }
 
 extern "C" size_t acx_kl_workspace_bytes(void) { return sizeof(double) * 1024; }
@@ -585,16 +647,27 @@ extern "C" int acx_policy_logp_cat(const float* actor, int ob_dim, int n_act, in
   return launch<128, 64, true, HEAD_CAT, MODE_EVAL>(a, grid, (cudaStream_t)stream);
 }
 
-extern "C" int acx_value_forward(const float* critic, int ob_dim, int rows, int n, const float* obs, float* v_out,
-                                 int basic_head, void* stream) {
+static int value_forward(const float* critic, int ob_dim, int rows, int n, const float* obs, float* v_out,
+                         int basic_head, float* x2_out, float* x3_out, void* stream) {
   int rc = check_common("acx_value_forward", critic, ob_dim, 1, rows, n, obs);
   if (rc) return rc;
   if (rows == 0 || n == 0) return ACX_OK;
   ACX_REQUIRE(v_out, "acx_value_forward: v_out is null");
   Args a; memset(&a, 0, sizeof(a));
   a.params = critic; a.L = acx_critic_layout(ob_dim); a.rows = rows; a.n = n; a.obs = obs;
-  a.v_out = v_out; a.basic_head = basic_head;
+  a.v_out = v_out; a.basic_head = basic_head; a.x2_out = x2_out; a.x3_out = x3_out;
   return launch<256, 128, false, HEAD_VALUE, MODE_EVAL>(a, tile_grid(rows, n), (cudaStream_t)stream);
+}
+
+extern "C" int acx_value_forward(const float* critic, int ob_dim, int rows, int n, const float* obs, float* v_out,
+                                 int basic_head, void* stream) {
+  return value_forward(critic, ob_dim, rows, n, obs, v_out, basic_head, nullptr, nullptr, stream);
+}
+
+extern "C" int acx_value_forward_cached(const float* critic, int ob_dim, int rows, int n, const float* obs,
+                                        float* v_out, int basic_head, float* x2_out, float* x3_out, void* stream) {
+  ACX_REQUIRE(x2_out && x3_out, "acx_value_forward_cached: null activation cache");
+  return value_forward(critic, ob_dim, rows, n, obs, v_out, basic_head, x2_out, x3_out, stream);
 }
 
 extern "C" size_t acx_loss_backward_workspace_bytes(int ob_dim, int num_ac, int cont) {
@@ -606,6 +679,8 @@ extern "C" size_t acx_loss_backward_workspace_bytes(int ob_dim, int num_ac, int 
 
 // set per call by acx_loss_backward_basic_critic (thread-local: the C ABI is one host thread per device)
 static thread_local int g_basic_critic_head = 0;
+// activation caches of the current call (acx_loss_backward_*_cached); null = recompute layers 2 and 3
+static thread_local const float* g_cache[4] = {nullptr, nullptr, nullptr, nullptr};   // actor x2, x3, critic x2, x3
 
 static int loss_backward(int cont, const float* actor, const float* critic, int ob_dim, int num_ac, float ac_scale,
                          int rows, int n, const float* obs, const void* acs, const float* adv, const float* adv_stats,
@@ -641,8 +716,13 @@ static int loss_backward(int cont, const float* actor, const float* critic, int 
     a.scratch = scr_a; a.loss_partial = lossp_a; a.wT = wT_a;
     acx_transpose_weights_kernel<<<48, 256, 0, st>>>(actor, La, wT_a);
     ACX_LAUNCH_OK("acx_transpose_weights_kernel(actor)");
-    rc = cont ? launch<128, 64, true, HEAD_GAUSS, MODE_TRAIN>(a, grid, st)
-              : launch<128, 64, true, HEAD_CAT, MODE_TRAIN>(a, grid, st);
+    a.x2_in = g_cache[0]; a.x3_in = g_cache[1];
+    if (a.x2_in && a.x3_in)
+      rc = cont ? launch<128, 64, true, HEAD_GAUSS, MODE_TRAIN, true>(a, grid, st)
+                : launch<128, 64, true, HEAD_CAT, MODE_TRAIN, true>(a, grid, st);
+    else
+      rc = cont ? launch<128, 64, true, HEAD_GAUSS, MODE_TRAIN>(a, grid, st)
+                : launch<128, 64, true, HEAD_CAT, MODE_TRAIN>(a, grid, st);
     if (rc) return rc;
     acx_grad_reduce_kernel<<<(La.size + 255) / 256, 256, 0, st>>>(scr_a, grid, La.size, grad_actor, lossp_a, stats, opt,
                                                                  1, count);
@@ -658,7 +738,9 @@ static int loss_backward(int cont, const float* actor, const float* critic, int 
     a.basic_head = g_basic_critic_head;
     acx_transpose_weights_kernel<<<96, 256, 0, st>>>(critic, Lc, wT_c);
     ACX_LAUNCH_OK("acx_transpose_weights_kernel(critic)");
-    rc = launch<256, 128, false, HEAD_VALUE, MODE_TRAIN>(a, grid, st);
+    a.x2_in = g_cache[2]; a.x3_in = g_cache[3];
+    rc = (a.x2_in && a.x3_in) ? launch<256, 128, false, HEAD_VALUE, MODE_TRAIN, true>(a, grid, st)
+                              : launch<256, 128, false, HEAD_VALUE, MODE_TRAIN>(a, grid, st);
     if (rc) return rc;
     acx_grad_reduce_kernel<<<(Lc.size + 255) / 256, 256, 0, st>>>(scr_c, grid, Lc.size, grad_critic, lossp_c, stats,
                                                                  opt, 0, count);
@@ -693,5 +775,39 @@ extern "C" int acx_loss_backward_basic_critic(const float* critic, int ob_dim, i
                                targets, nullptr, nullptr, grad_critic, stats, workspace, workspace_bytes,
                                (cudaStream_t)stream);
   g_basic_critic_head = 0;
+  return rc;
+}
+
+// Same as acx_loss_backward_{gauss,cat}, but layers 2 and 3 of each network are read from the activation cache the
+// *_cached forward entry points filled (x2[rows][128][n], x3[rows][H3][n]) instead of being recomputed.  Only valid
+// while the parameters are the ones those forwards ran with -- which is the reference's schedule: one update per
+// batch, computed on the weights that produced it (A3C/process.py:221-258).
+extern "C" int acx_loss_backward_gauss_cached(const float* actor, const float* critic, int ob_dim, int ac_dim,
+                                              float ac_scale, int rows, int n, const float* obs, const float* acs,
+                                              const float* adv, const float* adv_stats, const float* logp_old,
+                                              const float* targets, const float* opt, float* grad_actor,
+                                              float* grad_critic, float* stats, const float* actor_x2,
+                                              const float* actor_x3, const float* critic_x2, const float* critic_x3,
+                                              void* workspace, size_t workspace_bytes, void* stream) {
+  g_cache[0] = actor_x2; g_cache[1] = actor_x3; g_cache[2] = critic_x2; g_cache[3] = critic_x3;
+  const int rc = loss_backward(1, actor, critic, ob_dim, ac_dim, ac_scale, rows, n, obs, acs, adv, adv_stats, logp_old,
+                               targets, opt, grad_actor, grad_critic, stats, workspace, workspace_bytes,
+                               (cudaStream_t)stream);
+  g_cache[0] = g_cache[1] = g_cache[2] = g_cache[3] = nullptr;
+  return rc;
+}
+
+extern "C" int acx_loss_backward_cat_cached(const float* actor, const float* critic, int ob_dim, int n_act, int rows,
+                                            int n, const float* obs, const int* acs, const float* adv,
+                                            const float* adv_stats, const float* logp_old, const float* targets,
+                                            const float* opt, float* grad_actor, float* grad_critic, float* stats,
+                                            const float* actor_x2, const float* actor_x3, const float* critic_x2,
+                                            const float* critic_x3, void* workspace, size_t workspace_bytes,
+                                            void* stream) {
+  g_cache[0] = actor_x2; g_cache[1] = actor_x3; g_cache[2] = critic_x2; g_cache[3] = critic_x3;
+  const int rc = loss_backward(0, actor, critic, ob_dim, n_act, 0.f, rows, n, obs, acs, adv, adv_stats, logp_old,
+                               targets, opt, grad_actor, grad_critic, stats, workspace, workspace_bytes,
+                               (cudaStream_t)stream);
+  g_cache[0] = g_cache[1] = g_cache[2] = g_cache[3] = nullptr;
   return rc;
 }

@@ -69,6 +69,12 @@ struct Args {
   float* scratch;            // per-CTA gradient partials [grid][L.size]
   double* loss_partial;      // per-CTA loss sums [grid][4]
   const float* wT;           // transposed weights: W3T [H3][128] then W2T [H1/128][128][128]
+  // activation cache (SoA like obs): x2[rows][128][n], x3[rows][H3][n].  Forward kernels may write it, the
+  // training kernel may read it instead of recomputing layers 2 and 3 (valid while the weights are unchanged).
+  float* x2_out;
+  float* x3_out;
+  const float* x2_in;
+  const float* x3_in;
 };
 
 struct Smem {
@@ -86,6 +92,7 @@ struct Smem {
   float dHead[MAX_OUT * MT];
   double red[8][4];
   unsigned long long bar[NSLOT];
+  unsigned long long bar_act;      // arrival of a cached activation tile (bulk-TMA row copies)
 };
 
 template <bool LRELU> __device__ inline float act_fn(float x) {
@@ -99,9 +106,9 @@ template <bool LRELU> __device__ inline float act_grad(float y) {   // from the 
 // ---------------------------------------------------------------- weight ring
 // Stage order per tile: W2 (4 chunks per 128-row block of layer 1), W3 (4 chunks); training adds
 // W3T (H3/32 chunks) and W2T (4 chunks per block).
-template <int H1, int H3, bool TRAIN> struct Ring {
+template <int H1, int H3, bool TRAIN, bool REUSE = false> struct Ring {
   static constexpr int NB = H1 / 128;
-  static constexpr int NF = 4 * NB + 4;
+  static constexpr int NF = REUSE ? 0 : 4 * NB + 4;       // forward stages (none when activations come from the cache)
   static constexpr int P = TRAIN ? NF + H3 / CH + 4 * NB : NF;
   const float* W2;
   const float* W3;
@@ -113,10 +120,12 @@ template <int H1, int H3, bool TRAIN> struct Ring {
 
   __device__ inline void desc(unsigned int s, const float*& src, unsigned int& bytes) const {
     s %= P;
-    if (s < 4 * NB) { src = W2 + (size_t)s * CH * H2; bytes = CH * H2 * 4; return; }
-    s -= 4 * NB;
-    if (s < 4) { src = W3 + (size_t)s * CH * H3; bytes = CH * H3 * 4; return; }
-    s -= 4;
+    if (!REUSE) {
+      if (s < 4 * NB) { src = W2 + (size_t)s * CH * H2; bytes = CH * H2 * 4; return; }
+      s -= 4 * NB;
+      if (s < 4) { src = W3 + (size_t)s * CH * H3; bytes = CH * H3 * 4; return; }
+      s -= 4;
+    }
     if (s < H3 / CH) { src = W3T + (size_t)s * CH * 128; bytes = CH * 128 * 4; return; }
     s -= H3 / CH;
     src = W2T + (size_t)s * CH * 128; bytes = CH * 128 * 4;
@@ -134,6 +143,7 @@ template <int H1, int H3, bool TRAIN> struct Ring {
     sm = s; W2 = w2; W3 = w3; W3T = wT; W2T = wT ? wT + (size_t)H3 * 128 : nullptr; g = 0; total = ntiles * P;
     if (threadIdx.x == 0) {
       for (int i = 0; i < NSLOT; ++i) acx_mbar_init(reinterpret_cast<uint64_t*>(&sm->bar[i]), 1);
+      acx_mbar_init(reinterpret_cast<uint64_t*>(&sm->bar_act), 1);
       acx_mbar_fence_init();
     }
     __syncthreads();
@@ -200,9 +210,11 @@ template <int TJ> __device__ inline void f_zero(float (&acc)[TJ][8]) {
 }
 
 // forward epilogue: OUT[j][m] = act(acc + bias[j])
+// gout (nullable): global copy of the tile, row j at gout + j * gld (column 0 = first sample of the tile)
 template <int TJ, bool LRELU>
 __device__ inline void f_store(float* __restrict__ OUT, const float* __restrict__ bias, float (&acc)[TJ][8],
-                               const Coord& c) {
+                               const Coord& c, float* __restrict__ gout = nullptr, size_t gld = 0, int valid = MT,
+                               bool vec_ok = false) {
 #pragma unroll
   for (int jj = 0; jj < TJ; ++jj) {
     const int j = f_col(jj, c);
@@ -214,8 +226,39 @@ __device__ inline void f_store(float* __restrict__ OUT, const float* __restrict_
       o.y = act_fn<LRELU>(__fadd_rn(acc[jj][4 * h + 1], bj));
       o.z = act_fn<LRELU>(__fadd_rn(acc[jj][4 * h + 2], bj));
       o.w = act_fn<LRELU>(__fadd_rn(acc[jj][4 * h + 3], bj));
-      *reinterpret_cast<float4*>(OUT + j * MS + 4 * c.b + 64 * h) = o;
+      const int m = 4 * c.b + 64 * h;
+      *reinterpret_cast<float4*>(OUT + j * MS + m) = o;
+      if (gout != nullptr) {
+        float* g = gout + (size_t)j * gld + m;
+        if (vec_ok && m + 3 < valid) {
+          *reinterpret_cast<float4*>(g) = o;
+        } else {
+          if (m + 0 < valid) g[0] = o.x;
+          if (m + 1 < valid) g[1] = o.y;
+          if (m + 2 < valid) g[2] = o.z;
+          if (m + 3 < valid) g[3] = o.w;
+        }
+      }
     }
+  }
+}
+
+// cached activations -> shared tile: DST[r][m] = src[r * gld + m] for r < rows_, m < valid (zero beyond)
+__device__ inline void load_tile(float* __restrict__ DST, const float* __restrict__ src, size_t gld, int rows_,
+                                 int valid, bool vec_ok) {
+  for (int idx = threadIdx.x; idx < rows_ * (MT / 4); idx += NT) {
+    const int r = idx >> 5, m = (idx & 31) * 4;
+    const float* g = src + (size_t)r * gld + m;
+    float4 v;
+    if (vec_ok && m + 3 < valid) {
+      v = __ldg(reinterpret_cast<const float4*>(g));
+    } else {
+      v.x = (m + 0 < valid) ? __ldg(g + 0) : 0.f;
+      v.y = (m + 1 < valid) ? __ldg(g + 1) : 0.f;
+      v.z = (m + 2 < valid) ? __ldg(g + 2) : 0.f;
+      v.w = (m + 3 < valid) ? __ldg(g + 3) : 0.f;
+    }
+    *reinterpret_cast<float4*>(DST + r * MS + m) = v;
   }
 }
 

@@ -57,7 +57,8 @@ class A2CTrainer:
     def __init__(self, env_id="Pendulum-v0", n_envs=65536, horizon=20, seed=12321, gamma=0.98, look_ahead=40,
                  desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1, actor_lr=0.005, critic_lr=0.001, beta=1.0,
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
-                 critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=False):
+                 critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=False,
+                 cache_activations=True):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
@@ -78,6 +79,9 @@ class A2CTrainer:
         # splits -- verified to the same tolerance, but measured slower than the FFMA engine in round 1
         # (profiles/r01_tc_forward.md), hence off by default; False keeps every GEMM on the FFMA engine
         self.tc = bool(tensor_cores)
+        # keep the hidden activations of the rollout / value passes in HBM and let the update read them instead of
+        # recomputing layers 2 and 3 (same weights => bit-identical; 2.4 GB at 65,536 envs x 20 steps)
+        self.cache = bool(cache_activations) and not self.tc
         d, f32 = self.dev, torch.float32
         N, T = self.N, self.T
 
@@ -118,6 +122,11 @@ class A2CTrainer:
         self.ws_bwd = torch.empty(self.ws_bwd_bytes, device=d, dtype=torch.uint8)
         self.kl_part = torch.zeros(L.load().acx_kl_workspace_bytes() // 8, device=d, dtype=torch.float64)
         self.kl_blocks = ctypes.c_int(0)
+        if self.cache:
+            self.ax2 = torch.empty((T, 128, N), device=d, dtype=f32)
+            self.ax3 = torch.empty((T, 64, N), device=d, dtype=f32)
+            self.cx2 = torch.empty((T + 1, 128, N), device=d, dtype=f32)
+            self.cx3 = torch.empty((T + 1, 128, N), device=d, dtype=f32)
         self.packed_a = torch.zeros(L.load().acx_tc_packed_floats(0, self.ob, self.num_ac, int(self.cont)), device=d)
         self.packed_c = torch.zeros(L.load().acx_tc_packed_floats(1, self.ob, 1, 0), device=d)
         # optional caller-supplied noise (parity / end-to-end mode), static so graphs can replay on them
@@ -159,12 +168,18 @@ class A2CTrainer:
             if self.cont and self.tc:
                 L.call("acx_policy_forward_sample_gauss_tc", L.ptr(self.actor), L.ptr(self.packed_a), self.ob,
                        self.num_ac, self.ac_scale, 1, N, *tail)
+            elif self.cont and self.cache:
+                L.call("acx_policy_forward_sample_gauss_cached", L.ptr(self.actor), self.ob, self.num_ac, self.ac_scale,
+                       1, N, *tail[:-1], self._row(self.ax2, t), self._row(self.ax3, t), s)
             elif self.cont:
                 L.call("acx_policy_forward_sample_gauss", L.ptr(self.actor), self.ob, self.num_ac, self.ac_scale, 1, N,
                        *tail)
             elif self.tc:
                 L.call("acx_policy_forward_sample_cat_tc", L.ptr(self.actor), L.ptr(self.packed_a), self.ob, self.n_act,
                        1, N, *tail)
+            elif self.cache:
+                L.call("acx_policy_forward_sample_cat_cached", L.ptr(self.actor), self.ob, self.n_act, 1, N, *tail[:-1],
+                       self._row(self.ax2, t), self._row(self.ax3, t), s)
             else:
                 L.call("acx_policy_forward_sample_cat", L.ptr(self.actor), self.ob, self.n_act, 1, N, *tail)
             L.call("acx_env_step", self.env, N, L.ptr(self.state), L.ptr(self.elapsed), self._row(self.acs, t),
@@ -179,6 +194,9 @@ class A2CTrainer:
         if self.tc:
             L.call("acx_value_forward_tc", L.ptr(self.critic), L.ptr(self.packed_c), self.ob, T + 1, N,
                    L.ptr(self.obs_buf), L.ptr(self.V), 0, s)
+        elif self.cache:
+            L.call("acx_value_forward_cached", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V),
+                   0, L.ptr(self.cx2), L.ptr(self.cx3), s)
         else:
             L.call("acx_value_forward", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V), 0, s)
         L.call("acx_returns_adv_scan", T, N, L.ptr(self.rew), L.ptr(self.done), L.ptr(self.V), self.gamma,
@@ -188,7 +206,15 @@ class A2CTrainer:
         common = (L.ptr(self.obs_buf), L.ptr(self.acs), L.ptr(self.adv), L.ptr(self.stats), L.ptr(self.logps),
                   L.ptr(self.G), L.ptr(self.opt), L.ptr(ga), L.ptr(gc), L.ptr(self.stats), L.ptr(self.ws_bwd),
                   self.ws_bwd_bytes, s)
-        if self.cont:
+        if self.cache:
+            cached = common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3)) + common[-3:]
+            if self.cont:
+                L.call("acx_loss_backward_gauss_cached", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.num_ac,
+                       self.ac_scale, T, N, *cached)
+            else:
+                L.call("acx_loss_backward_cat_cached", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.n_act, T, N,
+                       *cached)
+        elif self.cont:
             L.call("acx_loss_backward_gauss", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.num_ac,
                    self.ac_scale, T, N, *common)
         else:

@@ -161,7 +161,22 @@ def kernel_table(tr, flush, hbm_peak):
         "acx_policy_logp_gauss", L.ptr(tr.actor), tr.ob, tr.num_ac, tr.ac_scale, T, N, L.ptr(tr.obs_buf), L.ptr(tr.acs),
         None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part), __import__("ctypes").byref(tr.kl_blocks), s),
         FLOP_ACTOR_FWD * B, None)
-    TC_PEAK = None      # set by the caller through kernel_table.tc_peak
+    if getattr(tr, "cache", False):
+        cached = common[:-3] + (L.ptr(tr.ax2), L.ptr(tr.ax3), L.ptr(tr.cx2), L.ptr(tr.cx3)) + common[-3:]
+
+        def bwd_c(actor, critic):
+            return lambda: L.call("acx_loss_backward_gauss_cached", actor, critic, tr.ob, tr.num_ac, tr.ac_scale, T, N,
+                                  *cached)
+        # algorithmic FLOPs of the cached variant: backward only (2x forward) + layer 1 / head
+        ks["loss_backward_critic, cached activations (K4)"] = (bwd_c(None, L.ptr(tr.critic)), 2 * FLOP_CRITIC_FWD * B, None)
+        ks["loss_backward_actor, cached activations (K4)"] = (bwd_c(L.ptr(tr.actor), None), 2 * FLOP_ACTOR_FWD * B, None)
+        ks["value_forward + cache write (K2)"] = (lambda: L.call(
+            "acx_value_forward_cached", L.ptr(tr.critic), tr.ob, T + 1, N, L.ptr(tr.obs_buf), L.ptr(tr.V), 0,
+            L.ptr(tr.cx2), L.ptr(tr.cx3), s), FLOP_CRITIC_FWD * (T + 1) * N, None)
+        ks["policy_forward_sample + cache write (K2)"] = (lambda: L.call(
+            "acx_policy_forward_sample_gauss_cached", L.ptr(tr.actor), tr.ob, tr.num_ac, tr.ac_scale, 1, N,
+            L.ptr(tr.obs_buf), None, tr.seed, 0, 0, None, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent), None,
+            L.ptr(tr.ax2), L.ptr(tr.ax3), s), FLOP_ACTOR_FWD * N, None)
     ks["value_forward_tc (K2, tcgen05 3xTF32)"] = (lambda: L.call(
         "acx_value_forward_tc", L.ptr(tr.critic), L.ptr(tr.packed_c), tr.ob, T + 1, N, L.ptr(tr.obs_buf), L.ptr(tr.V), 0, s),
         FLOP_CRITIC_FWD * (T + 1) * N, "tc")

@@ -140,6 +140,25 @@ int acx_policy_logp_cat(const float* actor, int ob_dim, int n_act, int rows, int
 int acx_value_forward(const float* critic, int ob_dim, int rows, int n, const float* obs, float* v_out,
                       int basic_head, void* stream);
 
+/* Activation cache.  The reference makes ONE update per batch, on the weights that produced the batch
+ * (A3C/process.py:221-258), so the hidden activations the rollout and value passes compute are exactly what
+ * the update's forward pass would recompute.  The *_cached forwards also write them -- x2_out[rows][128][n]
+ * (second hidden layer) and x3_out[rows][64 actor | 128 critic][n] -- and acx_loss_backward_*_cached reads
+ * them instead of re-running those two GEMMs (650 k -> 500 k FLOP per env-step).  Results are
+ * bit-identical to the recomputing entry points. */
+int acx_policy_forward_sample_gauss_cached(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows,
+                                           int n, const float* obs, const float* eps, uint64_t seed,
+                                           uint64_t index0, uint32_t step0, const uint32_t* step_base,
+                                           float* ac_out, float* logp_out, float* ent_out, float* mu_out,
+                                           float* x2_out, float* x3_out, void* stream);
+int acx_policy_forward_sample_cat_cached(const float* actor, int ob_dim, int n_act, int rows, int n,
+                                         const float* obs, const float* u, uint64_t seed, uint64_t index0,
+                                         uint32_t step0, const uint32_t* step_base, int* ac_out, float* logp_out,
+                                         float* ent_out, float* logits_out, float* x2_out, float* x3_out,
+                                         void* stream);
+int acx_value_forward_cached(const float* critic, int ob_dim, int rows, int n, const float* obs, float* v_out,
+                             int basic_head, float* x2_out, float* x3_out, void* stream);
+
 /* ---------------------------------------------------------------- K2 on the tensor cores (tcgen05, 3xTF32)
  * Same contracts as the five forward entry points above (same reference lines), with the two 128-wide
  * hidden GEMMs issued as tcgen05.mma kind::tf32 on error-compensated operand splits (x = hi + lo;
@@ -222,6 +241,20 @@ int acx_loss_backward_cat(const float* actor, const float* critic, int ob_dim, i
                           const float* logp_old, const float* targets, const float* opt, float* grad_actor,
                           float* grad_critic, float* stats, void* workspace, size_t workspace_bytes,
                           void* stream);
+
+/* K4 reading the activation cache (see the *_cached forwards); a null x2/x3 pair recomputes that network. */
+int acx_loss_backward_gauss_cached(const float* actor, const float* critic, int ob_dim, int ac_dim, float ac_scale,
+                                   int rows, int n, const float* obs, const float* acs, const float* adv,
+                                   const float* adv_stats, const float* logp_old, const float* targets,
+                                   const float* opt, float* grad_actor, float* grad_critic, float* stats,
+                                   const float* actor_x2, const float* actor_x3, const float* critic_x2,
+                                   const float* critic_x3, void* workspace, size_t workspace_bytes, void* stream);
+int acx_loss_backward_cat_cached(const float* actor, const float* critic, int ob_dim, int n_act, int rows, int n,
+                                 const float* obs, const int* acs, const float* adv, const float* adv_stats,
+                                 const float* logp_old, const float* targets, const float* opt, float* grad_actor,
+                                 float* grad_critic, float* stats, const float* actor_x2, const float* actor_x3,
+                                 const float* critic_x2, const float* critic_x3, void* workspace,
+                                 size_t workspace_bytes, void* stream);
 
 /* Critic loss + gradient for the Basic_AC network, whose value head reads the SECOND layer
  * (Basic_AC/policies.py:134-135): the third layer gets a zero gradient, exactly as TF reports None

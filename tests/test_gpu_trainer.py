@@ -102,3 +102,17 @@ def test_checkpoint_export_loads_back(tmp_path):
     assert open(os.path.join(str(tmp_path), "checkpoint")).read().startswith('model_checkpoint_path: "model-Pendulum-600"')
     actor = process.load_actor(prefix, 3, 1, 'cont', 2.0)
     np.testing.assert_array_equal(actor.net.params.cpu().numpy(), tr.actor.cpu().numpy())
+
+
+@pytest.mark.parametrize("env_id", ["Pendulum-v0", "CartPole-v0"])
+def test_activation_cache_is_bit_identical_to_recomputing(env_id):
+    """The update reads the rollout's hidden activations from HBM instead of recomputing them (same weights)."""
+    outs = []
+    for cache in (False, True):
+        tr = A2CTrainer(env_id, n_envs=1000, horizon=6, seed=11, use_graph=False, cache_activations=cache)
+        for _ in range(3):
+            tr.iteration()
+        torch.cuda.synchronize()
+        outs.append((tr.params.cpu().numpy(), tr.grads.cpu().numpy(), tr.stats.cpu().numpy()))
+    for a, b in zip(*outs):
+        np.testing.assert_array_equal(a, b)
