@@ -2,6 +2,8 @@
 // D[128][N] = A[128][K] * B[N][K]^T with operands packed on the host in the canonical layouts.
 //   mode 0: A MN-major, B MN-major      mode 1: A K-major, B K-major
 //   mode 2: like 0, but fp32 operands split on the device into TF32 hi/lo, 3 MMAs per K block (3xTF32)
+//   mode 4: A operand in tensor memory (row-major A[128][K] from global, written with tcgen05.st), B K-major
+//   mode 5: like 4 with the 3xTF32 split
 #include "acx_umma.cuh"
 using namespace acxumma;
 
@@ -21,16 +23,46 @@ __global__ void __launch_bounds__(128) tc_gemm_test(const float* __restrict__ Ap
   }
   for (int i = tid; i < K * N; i += 128) {
     float x = Bp[i];
-    if (mode == 2) { float h, l; split_tf32(x, h, l); sB[i] = h; sBlo[i] = l; } else sB[i] = x;
+    if (mode == 2 || mode == 5) { float h, l; split_tf32(x, h, l); sB[i] = h; sBlo[i] = l; } else sB[i] = x;
   }
-  if (warp == 0) tmem_alloc(&tmem_base, 128);
+  if (warp == 0) tmem_alloc(&tmem_base, 512);
   if (tid == 0) { acx_mbar_init(&mbar, 1); acx_mbar_fence_init(); }
   fence_proxy_async();
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
   const uint32_t taddr = tmem_base;
-  if (tid == 0) {
+  if (mode >= 4) {
+    // A (row-major [128][K] in global for these modes) -> TMEM columns 128.. (hi) and 128+K.. (lo): thread = row
+    const int arow = warp * 32 + (tid & 31);
+    for (int c0 = 0; c0 < K; c0 += 32) {
+      float hi[32], lo[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float x = Ap[(size_t)arow * K + c0 + i];
+        if (mode == 5) split_tf32(x, hi[i], lo[i]); else { hi[i] = x; lo[i] = 0.f; }
+      }
+      tmem_st32(taddr + ((uint32_t)(warp * 32) << 16) + 128u + (uint32_t)c0, hi);
+      tmem_st32(taddr + ((uint32_t)(warp * 32) << 16) + 128u + (uint32_t)(K + c0), lo);
+    }
+    tmem_wait_st();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    if (tid == 0) {
+      const uint32_t idesc = idesc_tf32(128, N, false, false);
+      for (int kb = 0; kb < K / 8; ++kb) {
+        const uint64_t bd = smem_desc(sB + (size_t)kb * 2 * 32, 128, (K / 4) * 128);
+        const uint64_t bdl = smem_desc(sBlo + (size_t)kb * 2 * 32, 128, (K / 4) * 128);
+        mma_tf32_ts(taddr, taddr + 128u + (uint32_t)(kb * 8), bd, idesc, kb > 0);
+        if (mode == 5) {
+          mma_tf32_ts(taddr, taddr + 128u + (uint32_t)(kb * 8), bdl, idesc, true);
+          mma_tf32_ts(taddr, taddr + 128u + (uint32_t)(K + kb * 8), bd, idesc, true);
+        }
+      }
+      commit(&mbar);
+    }
+  } else if (tid == 0) {
     const bool mn = (mode != 1);
     const bool swap = (mode == 3);
     const uint32_t idesc = idesc_tf32(128, N, mn, mn);
@@ -70,11 +102,11 @@ __global__ void __launch_bounds__(128) tc_gemm_test(const float* __restrict__ Ap
   }
   fence_before_sync();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(taddr, 128);
+  if (warp == 0) tmem_dealloc(taddr, 512);
 }
 
 extern "C" int acx_tc_gemm_test(const float* Ap, const float* Bp, float* D, int K, int N, int mode, void* stream) {
-  const size_t bytes = (size_t)(K * 128 + K * N) * 4 * (mode == 2 ? 2 : 1) + 1024;
+  const size_t bytes = (size_t)(K * 128 + K * N) * 4 * (mode == 2 || mode == 5 ? 2 : 1) + 1024;
   cudaFuncSetAttribute(tc_gemm_test, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   tc_gemm_test<<<1, 128, bytes, (cudaStream_t)stream>>>(Ap, Bp, D, K, N, mode);
   return (int)cudaGetLastError();

@@ -57,7 +57,7 @@ class A2CTrainer:
     def __init__(self, env_id="Pendulum-v0", n_envs=65536, horizon=20, seed=12321, gamma=0.98, look_ahead=40,
                  desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1, actor_lr=0.005, critic_lr=0.001, beta=1.0,
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
-                 critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=False,
+                 critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=True,
                  cache_activations=True):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
@@ -76,12 +76,12 @@ class A2CTrainer:
         self.pg = process_group
         self.use_graph = bool(use_graph)
         # True: forward passes (rollout sampling, values, post-update log-prob/KL) on tcgen05 with 3xTF32 operand
-        # splits -- verified to the same tolerance, but measured slower than the FFMA engine in round 1
-        # (profiles/r01_tc_forward.md), hence off by default; False keeps every GEMM on the FFMA engine
+        # splits (fp32-class accuracy, same test tolerances, ~1.9x faster than the FFMA forward -- profiles/
+        # r01_tc_forward.md); False keeps every GEMM on the bit-stable FFMA engine
         self.tc = bool(tensor_cores)
         # keep the hidden activations of the rollout / value passes in HBM and let the update read them instead of
         # recomputing layers 2 and 3 (same weights => bit-identical; 2.4 GB at 65,536 envs x 20 steps)
-        self.cache = bool(cache_activations) and not self.tc
+        self.cache = bool(cache_activations)
         d, f32 = self.dev, torch.float32
         N, T = self.N, self.T
 
@@ -165,9 +165,10 @@ class A2CTrainer:
             ru = None if not buffered_noise else self._row(self.reset_u_buf, t)
             tail = (self._row(self.obs_buf, t), noise, self.seed, self.index0, t, L.ptr(self.step_ctr),
                     self._row(self.acs, t), self._row(self.logps, t), self._row(self.ent, t), None, s)
+            cache = (self._row(self.ax2, t), self._row(self.ax3, t)) if self.cache else (None, None)
             if self.cont and self.tc:
                 L.call("acx_policy_forward_sample_gauss_tc", L.ptr(self.actor), L.ptr(self.packed_a), self.ob,
-                       self.num_ac, self.ac_scale, 1, N, *tail)
+                       self.num_ac, self.ac_scale, 1, N, *tail[:-1], *cache, s)
             elif self.cont and self.cache:
                 L.call("acx_policy_forward_sample_gauss_cached", L.ptr(self.actor), self.ob, self.num_ac, self.ac_scale,
                        1, N, *tail[:-1], self._row(self.ax2, t), self._row(self.ax3, t), s)
@@ -176,7 +177,7 @@ class A2CTrainer:
                        *tail)
             elif self.tc:
                 L.call("acx_policy_forward_sample_cat_tc", L.ptr(self.actor), L.ptr(self.packed_a), self.ob, self.n_act,
-                       1, N, *tail)
+                       1, N, *tail[:-1], *cache, s)
             elif self.cache:
                 L.call("acx_policy_forward_sample_cat_cached", L.ptr(self.actor), self.ob, self.n_act, 1, N, *tail[:-1],
                        self._row(self.ax2, t), self._row(self.ax3, t), s)
@@ -193,7 +194,8 @@ class A2CTrainer:
         s, N, T = L.cur_stream(), self.N, self.T
         if self.tc:
             L.call("acx_value_forward_tc", L.ptr(self.critic), L.ptr(self.packed_c), self.ob, T + 1, N,
-                   L.ptr(self.obs_buf), L.ptr(self.V), 0, s)
+                   L.ptr(self.obs_buf), L.ptr(self.V), 0, L.ptr(self.cx2) if self.cache else None,
+                   L.ptr(self.cx3) if self.cache else None, s)
         elif self.cache:
             L.call("acx_value_forward_cached", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V),
                    0, L.ptr(self.cx2), L.ptr(self.cx3), s)

@@ -178,11 +178,13 @@ def kernel_table(tr, flush, hbm_peak):
             L.ptr(tr.obs_buf), None, tr.seed, 0, 0, None, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent), None,
             L.ptr(tr.ax2), L.ptr(tr.ax3), s), FLOP_ACTOR_FWD * N, None)
     ks["value_forward_tc (K2, tcgen05 3xTF32)"] = (lambda: L.call(
-        "acx_value_forward_tc", L.ptr(tr.critic), L.ptr(tr.packed_c), tr.ob, T + 1, N, L.ptr(tr.obs_buf), L.ptr(tr.V), 0, s),
+        "acx_value_forward_tc", L.ptr(tr.critic), L.ptr(tr.packed_c), tr.ob, T + 1, N, L.ptr(tr.obs_buf), L.ptr(tr.V), 0,
+        L.ptr(tr.cx2) if tr.cache else None, L.ptr(tr.cx3) if tr.cache else None, s),
         FLOP_CRITIC_FWD * (T + 1) * N, "tc")
     ks["policy_forward_sample_tc (K2, tcgen05 3xTF32)"] = (lambda: L.call(
         "acx_policy_forward_sample_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, 1, N,
-        L.ptr(tr.obs_buf), None, tr.seed, 0, 0, None, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent), None, s),
+        L.ptr(tr.obs_buf), None, tr.seed, 0, 0, None, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent), None,
+        L.ptr(tr.ax2) if tr.cache else None, L.ptr(tr.ax3) if tr.cache else None, s),
         FLOP_ACTOR_FWD * N, "tc")
     ks["policy_logp_kl_tc (K2/K5, tcgen05 3xTF32)"] = (lambda: L.call(
         "acx_policy_logp_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, T, N,
@@ -248,7 +250,7 @@ def run_ours(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     hbm_peak, bf16_peak, peaks_src = measured_peaks()
     tr = A2CTrainer(ENV_ID, n_envs=N_ENVS, horizon=HORIZON, seed=SEED, rank=rank, world=world, mode=args.mode,
-                    use_graph=not args.no_graph, tensor_cores=args.tc)
+                    use_graph=not args.no_graph, tensor_cores=not args.ffma_only)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
     clean_buf = torch.zeros(64 << 20, dtype=torch.float32, device="cuda")      # 256 MiB, only ever read
 
@@ -369,7 +371,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--mode", choices=["sync", "async"], default="sync")
     ap.add_argument("--no_graph", action="store_true", help="launch kernels eagerly (for ncu launch lists)")
-    ap.add_argument("--tc", action="store_true", help="forward passes on the tcgen05 3xTF32 engine (slower in round 1)")
+    ap.add_argument("--ffma_only", action="store_true", help="keep the forward passes on the FFMA engine as well")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))

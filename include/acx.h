@@ -166,7 +166,8 @@ int acx_value_forward_cached(const float* critic, int ob_dim, int rows, int n, c
  * same 1e-5 tolerance.  They take, besides the flat parameters (layer 1, biases and head are read from
  * there), the hidden-layer kernels pre-split and pre-arranged for the tensor cores:
  * acx_tc_pack_weights() fills `packed` (acx_tc_packed_floats() floats, 16-byte aligned) and must be
- * re-run whenever the parameters change.  The FFMA entry points stay the bit-stable reference. */
+ * re-run whenever the parameters change.  x2_out / x3_out (both or neither, nullable) fill the activation
+ * cache like the *_cached forwards.  The FFMA entry points stay the bit-stable reference. */
 size_t acx_tc_packed_floats(int net, int ob_dim, int num_ac, int cont);
 int acx_tc_pack_weights(int net, const float* params, int ob_dim, int num_ac, int cont, float* packed,
                         void* stream);
@@ -174,11 +175,13 @@ int acx_policy_forward_sample_gauss_tc(const float* actor, const float* packed, 
                                        float ac_scale, int rows, int n, const float* obs, const float* eps,
                                        uint64_t seed, uint64_t index0, uint32_t step0,
                                        const uint32_t* step_base, float* ac_out, float* logp_out,
-                                       float* ent_out, float* mu_out, void* stream);
+                                       float* ent_out, float* mu_out, float* x2_out, float* x3_out,
+                                       void* stream);
 int acx_policy_forward_sample_cat_tc(const float* actor, const float* packed, int ob_dim, int n_act, int rows,
                                      int n, const float* obs, const float* u, uint64_t seed, uint64_t index0,
                                      uint32_t step0, const uint32_t* step_base, int* ac_out, float* logp_out,
-                                     float* ent_out, float* logits_out, void* stream);
+                                     float* ent_out, float* logits_out, float* x2_out, float* x3_out,
+                                     void* stream);
 int acx_policy_logp_gauss_tc(const float* actor, const float* packed, int ob_dim, int ac_dim, float ac_scale,
                              int rows, int n, const float* obs, const float* acs, float* logp_out,
                              float* ent_out, float* mu_out, const float* logp_old, double* kl_partial,
@@ -188,7 +191,8 @@ int acx_policy_logp_cat_tc(const float* actor, const float* packed, int ob_dim, 
                            float* logits_out, const float* logp_old, double* kl_partial,
                            int* kl_blocks /*host*/, void* stream);
 int acx_value_forward_tc(const float* critic, const float* packed, int ob_dim, int rows, int n,
-                         const float* obs, float* v_out, int basic_head, void* stream);
+                         const float* obs, float* v_out, int basic_head, float* x2_out, float* x3_out,
+                         void* stream);
 
 /* ---------------------------------------------------------------- K3: returns / advantages
  * PathAdv.__call__ -- A3C/process.py:54-66 -- over time-major [T][n] buffers with done masks

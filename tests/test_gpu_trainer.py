@@ -106,13 +106,30 @@ def test_checkpoint_export_loads_back(tmp_path):
 
 @pytest.mark.parametrize("env_id", ["Pendulum-v0", "CartPole-v0"])
 def test_activation_cache_is_bit_identical_to_recomputing(env_id):
-    """The update reads the rollout's hidden activations from HBM instead of recomputing them (same weights)."""
+    """The update reads the rollout's hidden activations from HBM instead of recomputing them (same weights).
+    With the FFMA forward the cached values are the very numbers the recomputation produces."""
     outs = []
     for cache in (False, True):
-        tr = A2CTrainer(env_id, n_envs=1000, horizon=6, seed=11, use_graph=False, cache_activations=cache)
+        tr = A2CTrainer(env_id, n_envs=1000, horizon=6, seed=11, use_graph=False, cache_activations=cache,
+                        tensor_cores=False)
         for _ in range(3):
             tr.iteration()
         torch.cuda.synchronize()
         outs.append((tr.params.cpu().numpy(), tr.grads.cpu().numpy(), tr.stats.cpu().numpy()))
     for a, b in zip(*outs):
         np.testing.assert_array_equal(a, b)
+
+
+def test_activation_cache_from_the_tensor_core_forward_matches_recomputing():
+    """With the tcgen05 forward the cache holds 3xTF32 activations: gradients agree with the FFMA recomputation
+    to the fp32 tolerance (first iteration, same rollout because the forward engine is the same)."""
+    outs = []
+    for cache in (False, True):
+        tr = A2CTrainer("Pendulum-v0", n_envs=1024, horizon=6, seed=11, use_graph=False, cache_activations=cache,
+                        tensor_cores=True)
+        tr.iteration()
+        torch.cuda.synchronize()
+        outs.append((tr.grads[:tr.Pa].cpu().numpy(), tr.grads[tr.Pa:].cpu().numpy(), tr.acs.cpu().numpy()))
+    np.testing.assert_array_equal(outs[0][2], outs[1][2])
+    for i in (0, 1):
+        assert np.abs(outs[0][i] - outs[1][i]).max() <= 2e-5 * np.abs(outs[0][i]).max()
