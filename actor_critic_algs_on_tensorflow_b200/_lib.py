@@ -60,6 +60,10 @@ SIGNATURES = {
     "acx_value_forward_cached": (_i, [_p, _i, _i, _i, _p, _p, _i, _p, _p, _p]),
     "acx_loss_backward_gauss_cached": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_loss_backward_cat_cached": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "acx_tc_packed_bwd_floats": (_sz, [_i, _i, _i, _i]),
+    "acx_tc_pack_weights_bwd": (_i, [_i, _p, _i, _i, _i, _p, _p]),
+    "acx_loss_backward_gauss_tc": (_i, [_p, _p, _p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "acx_loss_backward_cat_tc": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_tc_packed_floats": (_sz, [_i, _i, _i, _i]),
     "acx_tc_pack_weights": (_i, [_i, _p, _i, _i, _i, _p, _p]),
     "acx_policy_forward_sample_gauss_tc": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _u64, _u64, _u32, _p, _p, _p, _p, _p, _p, _p, _p]),

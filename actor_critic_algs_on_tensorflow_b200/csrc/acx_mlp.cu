@@ -8,78 +8,11 @@
 //                        A3C/policies.py:74-85,152-158      -> acx_loss_backward_{gauss,cat}
 // See acx_mlp.cuh for the tile engine.  Head math follows oracle/policies.py line by line.
 #include "acx_mlp.cuh"
+#include "acx_head.cuh"
 
 using namespace acxmlp;
 
 namespace {
-
-template <int H1, bool LRELU>
-__device__ inline void layer1_block(Smem& sm, int h, int ob, float* __restrict__ dst) {
-  // dst[r][m] = X1[128h + r][m] = act(sum_i obs[i][m] * W1[i][k] + b1[k]), r < 128, m < 128
-  const int r = threadIdx.x >> 1, q = (threadIdx.x & 1) * 64, k = h * 128 + r;
-  const float bk = sm.b1[k];
-#pragma unroll 4
-  for (int m4 = 0; m4 < 16; ++m4) {
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int i = 0; i < ob; ++i) {
-      const float w = sm.W1[i * H1 + k];
-      const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + q + 4 * m4]);
-      s.x = fmaf(o.x, w, s.x); s.y = fmaf(o.y, w, s.y); s.z = fmaf(o.z, w, s.z); s.w = fmaf(o.w, w, s.w);
-    }
-    float4 o;
-    o.x = act_fn<LRELU>(__fadd_rn(s.x, bk)); o.y = act_fn<LRELU>(__fadd_rn(s.y, bk));
-    o.z = act_fn<LRELU>(__fadd_rn(s.z, bk)); o.w = act_fn<LRELU>(__fadd_rn(s.w, bk));
-    *reinterpret_cast<float4*>(dst + r * MS + q + 4 * m4) = o;
-  }
-}
-
-// dW1[i][128h + j] (+)= sum_m obs[i][m] * D[j][m], db1 likewise, from a 128-row block D of dPre1
-template <int H1>
-__device__ inline void layer1_grad(Smem& sm, int h, int ob, const float* __restrict__ D, float* __restrict__ scrW1,
-                                   float* __restrict__ scrb1, bool first) {
-  const int j = threadIdx.x;
-  if (j < 128) {
-    float sb = 0.f, sw[MAX_OB];
-#pragma unroll
-    for (int i = 0; i < MAX_OB; ++i) sw[i] = 0.f;
-#pragma unroll 4
-    for (int m4 = 0; m4 < MT / 4; ++m4) {
-      const float4 d = *reinterpret_cast<const float4*>(D + j * MS + 4 * m4);
-      sb += d.x; sb += d.y; sb += d.z; sb += d.w;
-#pragma unroll
-      for (int i = 0; i < MAX_OB; ++i)
-        if (i < ob) {
-          const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + 4 * m4]);
-          sw[i] = fmaf(o.x, d.x, sw[i]); sw[i] = fmaf(o.y, d.y, sw[i]);
-          sw[i] = fmaf(o.z, d.z, sw[i]); sw[i] = fmaf(o.w, d.w, sw[i]);
-        }
-    }
-    const int k = h * 128 + j;
-    scrb1[k] = first ? sb : scrb1[k] + sb;
-#pragma unroll
-    for (int i = 0; i < MAX_OB; ++i)
-      if (i < ob) {
-        float* p = scrW1 + i * H1 + k;
-        *p = first ? sw[i] : *p + sw[i];
-      }
-  }
-}
-
-// pre-activation of the head for sample m: pre[a] = sum_k Xh[k][m] * Wh[k][a] + bh[a]
-template <int HH>
-__device__ inline void head_pre(const Smem& sm, const float* __restrict__ Xh, int m, int nout, float (&pre)[MAX_OUT]) {
-#pragma unroll
-  for (int a = 0; a < MAX_OUT; ++a) pre[a] = 0.f;
-  for (int k = 0; k < HH; ++k) {
-    const float x = Xh[k * MS + m];
-#pragma unroll
-    for (int a = 0; a < MAX_OUT; ++a)
-      if (a < nout) pre[a] = fmaf(x, sm.Wh[k * nout + a], pre[a]);
-  }
-#pragma unroll
-  for (int a = 0; a < MAX_OUT; ++a)
-    if (a < nout) pre[a] = __fadd_rn(pre[a], sm.bh[a]);
-}
 
 template <int H1, int H3, bool LRELU, int HEAD, int MODE, bool REUSE = false>
 __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
@@ -117,6 +50,8 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
     beta = A.opt[ACX_OPT_BETA_KL]; gam = A.opt[ACX_OPT_GAMMA_ENT];
     if (A.adv_stats) { adv_mean = A.adv_stats[0]; adv_inv = A.adv_stats[1]; }
   }
+  HeadScalars hs;
+  hs.beta = beta; hs.gam = gam; hs.adv_mean = adv_mean; hs.adv_inv = adv_inv; hs.invB = invB; hs.step0 = step0;
   float* __restrict__ scr = TRAIN ? A.scratch + (size_t)blockIdx.x * L.size : nullptr;
   bool first = true;
   unsigned int act_phase = 0;
@@ -190,161 +125,10 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
       const int m = tid;
       const bool live = m < valid;
       const size_t col = (size_t)n0 + m;
-      const size_t s_idx = (size_t)row * A.n + col;                 // [rows][n] arrays
       float pre[MAX_OUT];
       head_pre<H3>(sm, Xh, m, nout, pre);
       float dh[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
-      if (HEAD == HEAD_VALUE) {
-        if (live) {
-          if (MODE != MODE_TRAIN) {
-            A.v_out[s_idx] = pre[0];
-          } else {
-            const float err = pre[0] - A.targets[s_idx];
-            lsum[0] += (double)err * (double)err;
-            dh[0] = (float)(2.0 * (double)err * invB);
-          }
-        }
-      } else if (HEAD == HEAD_GAUSS) {
-        if (live) {
-          float lp = 0.f, ent = 0.f, dlp = 0.f, dent = 0.f;
-          float z[MAX_OUT], sd[MAX_OUT], th[MAX_OUT], ls[MAX_OUT];
-          AcxRng4 g = {0u, 0u, 0u, 0u};
-          if (MODE == MODE_SAMPLE && A.noise == nullptr)
-            g = acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed);
-#pragma unroll
-          for (int d = 0; d < MAX_OUT; ++d)
-            if (d < nout) {
-              th[d] = tanhf(pre[d]);
-              const float mu = __fmul_rn(th[d], A.ac_scale);
-              ls[d] = fminf(fmaxf(sm.log_std[d], ACX_LOG_STD_MIN), ACX_LOG_STD_MAX);
-              sd[d] = expf(ls[d]);
-              const size_t a_idx = ((size_t)row * nout + d) * A.n + col;
-              float ac;
-              if (MODE == MODE_SAMPLE) {
-                float eps;
-                if (A.noise) eps = A.noise[a_idx];
-                else eps = (d == 0) ? acx_normal(g.x, g.y) : ((d == 1) ? acx_normal(g.z, g.w) : 0.f);
-                ac = __fadd_rn(mu, __fmul_rn(sd[d], eps));
-                A.ac_out_f[a_idx] = ac;
-              } else {
-                ac = A.ac_in_f[a_idx];
-              }
-              if (A.head_out) A.head_out[a_idx] = mu;
-              z[d] = __fdiv_rn(__fsub_rn(ac, mu), sd[d]);
-              lp += __fsub_rn(__fsub_rn(__fmul_rn(__fmul_rn(-0.5f, z[d]), z[d]), ls[d]), ACX_HALF_LOG_2PI);
-              ent += __fadd_rn(__fadd_rn(0.5f, ACX_HALF_LOG_2PI), ls[d]);
-            }
-          if (MODE != MODE_TRAIN) {
-            if (A.logp_out) A.logp_out[s_idx] = lp;
-            if (A.ent_out) A.ent_out[s_idx] = ent;
-            if (MODE == MODE_EVAL && A.logp_old) {
-              const double df = (double)A.logp_old[s_idx] - (double)lp;
-              lsum[1] += df * df;
-            }
-          } else {
-            const float advn = (A.adv[s_idx] - adv_mean) * adv_inv;
-            const float diff = A.logp_old[s_idx] - lp;
-            lsum[0] += (double)advn * (double)lp;
-            lsum[1] += (double)diff * (double)diff;
-            lsum[2] += (double)ent;
-            dlp = (float)((-(double)advn - 2.0 * (double)beta * (double)diff) * invB);
-            dent = (float)(-(double)gam * invB);
-#pragma unroll
-            for (int d = 0; d < MAX_OUT; ++d)
-              if (d < nout) {
-                const float dmu = dlp * z[d] / sd[d];
-                dh[d] = dmu * A.ac_scale * (1.0f - th[d] * th[d]);
-                const bool inside = sm.log_std[d] >= ACX_LOG_STD_MIN && sm.log_std[d] <= ACX_LOG_STD_MAX;
-                if (inside) dls[d] += dlp * (z[d] * z[d] - 1.0f) + dent;
-              }
-          }
-        }
-      } else {   // HEAD_CAT
-        if (live) {
-          float l1[MAX_OUT], logps[MAX_OUT], p[MAX_OUT];
-          float mx1 = -INFINITY, mx2 = -INFINITY;
-#pragma unroll
-          for (int a = 0; a < MAX_OUT; ++a)
-            if (a < nout) {
-              l1[a] = __fadd_rn(pre[a], 1e-8f);                 // policies.py:65
-              mx1 = fmaxf(mx1, l1[a]); mx2 = fmaxf(mx2, pre[a]);
-            }
-          float se1 = 0.f, se2 = 0.f;
-#pragma unroll
-          for (int a = 0; a < MAX_OUT; ++a)
-            if (a < nout) {
-              se1 += expf(l1[a] - mx1);
-              p[a] = expf(pre[a] - mx2);
-              se2 += p[a];
-            }
-          const float lse = mx1 + logf(se1);
-          float ent = 0.f;
-#pragma unroll
-          for (int a = 0; a < MAX_OUT; ++a)
-            if (a < nout) {
-              logps[a] = l1[a] - lse;
-              p[a] = p[a] / se2;
-              ent -= p[a] * logps[a];
-            }
-          int ac;
-          if (MODE == MODE_SAMPLE) {
-            float u;
-            if (A.noise) u = A.noise[s_idx];
-            else u = acx_u01(acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed).x);
-            // tf.multinomial: inverse CDF in double over exp(logit - max)
-            double cdf[MAX_OUT], run = 0.0;
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) { run += exp((double)pre[a] - (double)mx2); cdf[a] = run; }
-            const double thr = (double)u * run;
-            ac = 0;
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout && cdf[a] <= thr) ++ac;
-            if (ac > nout - 1) ac = nout - 1;
-            A.ac_out_i[s_idx] = ac;
-          } else {
-            ac = A.ac_in_i[s_idx];
-          }
-          float lp = 0.f;
-#pragma unroll
-          for (int a = 0; a < MAX_OUT; ++a)
-            if (a < nout && a == ac) lp = logps[a];
-          if (A.head_out) {
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) A.head_out[((size_t)row * nout + a) * A.n + col] = pre[a];
-          }
-          if (MODE != MODE_TRAIN) {
-            if (A.logp_out) A.logp_out[s_idx] = lp;
-            if (A.ent_out) A.ent_out[s_idx] = ent;
-            if (MODE == MODE_EVAL && A.logp_old) {
-              const double df = (double)A.logp_old[s_idx] - (double)lp;
-              lsum[1] += df * df;
-            }
-          } else {
-            const float advn = (A.adv[s_idx] - adv_mean) * adv_inv;
-            const float diff = A.logp_old[s_idx] - lp;
-            lsum[0] += (double)advn * (double)lp;
-            lsum[1] += (double)diff * (double)diff;
-            lsum[2] += (double)ent;
-            const float dlp = (float)((-(double)advn - 2.0 * (double)beta * (double)diff) * invB);
-            const float dent = (float)(-(double)gam * invB);
-            float dlogps[MAX_OUT], dpp[MAX_OUT], sdl = 0.f, sdp = 0.f;
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) {
-                dlogps[a] = (a == ac ? dlp : 0.f) - dent * p[a];
-                dpp[a] = -dent * logps[a];
-                sdl += dlogps[a];
-                sdp += dpp[a] * p[a];
-              }
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) dh[a] = dlogps[a] - expf(logps[a]) * sdl + p[a] * (dpp[a] - sdp);
-          }
-        }
-      }
+      head_apply<HEAD, MODE>(A, sm.log_std, nout, pre, live, row, col, hs, lsum, dls, dh);
       if (TRAIN) {
 #pragma unroll
         for (int a = 0; a < MAX_OUT; ++a)

@@ -335,4 +335,74 @@ __device__ inline void bias_grad(const float* __restrict__ D, int rows, float* _
   }
 }
 
+// ---------------------------------------------------------------- small pieces shared by the MLP kernels
+// (SM: the kernel's shared-memory struct; needs obs, W1, b1, Wh, bh)
+template <int H1, bool LRELU, class SM>
+__device__ inline void layer1_block(SM& sm, int h, int ob, float* __restrict__ dst) {
+  // dst[r][m] = X1[128h + r][m] = act(sum_i obs[i][m] * W1[i][k] + b1[k]), r < 128, m < 128
+  const int r = threadIdx.x >> 1, q = (threadIdx.x & 1) * 64, k = h * 128 + r;
+  const float bk = sm.b1[k];
+#pragma unroll 4
+  for (int m4 = 0; m4 < 16; ++m4) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < ob; ++i) {
+      const float w = sm.W1[i * H1 + k];
+      const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + q + 4 * m4]);
+      s.x = fmaf(o.x, w, s.x); s.y = fmaf(o.y, w, s.y); s.z = fmaf(o.z, w, s.z); s.w = fmaf(o.w, w, s.w);
+    }
+    float4 o;
+    o.x = act_fn<LRELU>(__fadd_rn(s.x, bk)); o.y = act_fn<LRELU>(__fadd_rn(s.y, bk));
+    o.z = act_fn<LRELU>(__fadd_rn(s.z, bk)); o.w = act_fn<LRELU>(__fadd_rn(s.w, bk));
+    *reinterpret_cast<float4*>(dst + r * MS + q + 4 * m4) = o;
+  }
+}
+
+// dW1[i][128h + j] (+)= sum_m obs[i][m] * D[j][m], db1 likewise, from a 128-row block D of dPre1
+template <int H1, class SM>
+__device__ inline void layer1_grad(SM& sm, int h, int ob, const float* __restrict__ D, float* __restrict__ scrW1,
+                                   float* __restrict__ scrb1, bool first) {
+  const int j = threadIdx.x;
+  if (j < 128) {
+    float sb = 0.f, sw[MAX_OB];
+#pragma unroll
+    for (int i = 0; i < MAX_OB; ++i) sw[i] = 0.f;
+#pragma unroll 4
+    for (int m4 = 0; m4 < MT / 4; ++m4) {
+      const float4 d = *reinterpret_cast<const float4*>(D + j * MS + 4 * m4);
+      sb += d.x; sb += d.y; sb += d.z; sb += d.w;
+#pragma unroll
+      for (int i = 0; i < MAX_OB; ++i)
+        if (i < ob) {
+          const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + 4 * m4]);
+          sw[i] = fmaf(o.x, d.x, sw[i]); sw[i] = fmaf(o.y, d.y, sw[i]);
+          sw[i] = fmaf(o.z, d.z, sw[i]); sw[i] = fmaf(o.w, d.w, sw[i]);
+        }
+    }
+    const int k = h * 128 + j;
+    scrb1[k] = first ? sb : scrb1[k] + sb;
+#pragma unroll
+    for (int i = 0; i < MAX_OB; ++i)
+      if (i < ob) {
+        float* p = scrW1 + i * H1 + k;
+        *p = first ? sw[i] : *p + sw[i];
+      }
+  }
+}
+
+// pre-activation of the head for sample m: pre[a] = sum_k Xh[k][m] * Wh[k][a] + bh[a]
+template <int HH, class SM>
+__device__ inline void head_pre(const SM& sm, const float* __restrict__ Xh, int m, int nout, float (&pre)[MAX_OUT]) {
+#pragma unroll
+  for (int a = 0; a < MAX_OUT; ++a) pre[a] = 0.f;
+  for (int k = 0; k < HH; ++k) {
+    const float x = Xh[k * MS + m];
+#pragma unroll
+    for (int a = 0; a < MAX_OUT; ++a)
+      if (a < nout) pre[a] = fmaf(x, sm.Wh[k * nout + a], pre[a]);
+  }
+#pragma unroll
+  for (int a = 0; a < MAX_OUT; ++a)
+    if (a < nout) pre[a] = __fadd_rn(pre[a], sm.bh[a]);
+}
+
 }  // namespace acxmlp

@@ -58,7 +58,7 @@ class A2CTrainer:
                  desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1, actor_lr=0.005, critic_lr=0.001, beta=1.0,
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
                  critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=True,
-                 cache_activations=True):
+                 cache_activations=True, tensor_core_backward=True):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
@@ -82,6 +82,9 @@ class A2CTrainer:
         # keep the hidden activations of the rollout / value passes in HBM and let the update read them instead of
         # recomputing layers 2 and 3 (same weights => bit-identical; 2.4 GB at 65,536 envs x 20 steps)
         self.cache = bool(cache_activations)
+        # back-propagation chain products on tcgen05 too (needs both of the above); the weight-gradient products stay
+        # fp32 FFMA in the same kernel
+        self.tc_bwd = bool(tensor_core_backward) and self.tc and self.cache
         d, f32 = self.dev, torch.float32
         N, T = self.N, self.T
 
@@ -129,6 +132,8 @@ class A2CTrainer:
             self.cx3 = torch.empty((T + 1, 128, N), device=d, dtype=f32)
         self.packed_a = torch.zeros(L.load().acx_tc_packed_floats(0, self.ob, self.num_ac, int(self.cont)), device=d)
         self.packed_c = torch.zeros(L.load().acx_tc_packed_floats(1, self.ob, 1, 0), device=d)
+        self.packed_bwd_a = torch.zeros(L.load().acx_tc_packed_bwd_floats(0, self.ob, self.num_ac, int(self.cont)), device=d)
+        self.packed_bwd_c = torch.zeros(L.load().acx_tc_packed_bwd_floats(1, self.ob, 1, 0), device=d)
         # optional caller-supplied noise (parity / end-to-end mode), static so graphs can replay on them
         self.noise_buf = None
         self.reset_u_buf = None
@@ -155,7 +160,12 @@ class A2CTrainer:
         s = L.cur_stream()
         L.call("acx_tc_pack_weights", 0, L.ptr(self.actor), self.ob, self.num_ac, int(self.cont), L.ptr(self.packed_a), s)
         L.call("acx_tc_pack_weights", 1, L.ptr(self.critic), self.ob, 1, 0, L.ptr(self.packed_c), s)
-        return 2
+        if not self.tc_bwd:
+            return 2
+        L.call("acx_tc_pack_weights_bwd", 0, L.ptr(self.actor), self.ob, self.num_ac, int(self.cont),
+               L.ptr(self.packed_bwd_a), s)
+        L.call("acx_tc_pack_weights_bwd", 1, L.ptr(self.critic), self.ob, 1, 0, L.ptr(self.packed_bwd_c), s)
+        return 4
 
     def _rollout(self, buffered_noise):
         s, N = L.cur_stream(), self.N
@@ -208,6 +218,14 @@ class A2CTrainer:
         common = (L.ptr(self.obs_buf), L.ptr(self.acs), L.ptr(self.adv), L.ptr(self.stats), L.ptr(self.logps),
                   L.ptr(self.G), L.ptr(self.opt), L.ptr(ga), L.ptr(gc), L.ptr(self.stats), L.ptr(self.ws_bwd),
                   self.ws_bwd_bytes, s)
+        if self.tc_bwd:
+            cached = common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3)) + common[-3:]
+            head = (L.ptr(self.actor), L.ptr(self.critic), L.ptr(self.packed_bwd_a), L.ptr(self.packed_bwd_c), self.ob)
+            if self.cont:
+                L.call("acx_loss_backward_gauss_tc", *head, self.num_ac, self.ac_scale, T, N, *cached)
+            else:
+                L.call("acx_loss_backward_cat_tc", *head, self.n_act, T, N, *cached)
+            return 2 + 4      # value, scan, 2 x (mlp train, grad reduce)
         if self.cache:
             cached = common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3)) + common[-3:]
             if self.cont:

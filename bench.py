@@ -190,6 +190,15 @@ def kernel_table(tr, flush, hbm_peak):
         "acx_policy_logp_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, T, N,
         L.ptr(tr.obs_buf), L.ptr(tr.acs), None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part),
         __import__("ctypes").byref(tr.kl_blocks), s), FLOP_ACTOR_FWD * B, "tc")
+    if getattr(tr, "tc_bwd", False):
+        def bwd_t(actor, critic):
+            return lambda: L.call("acx_loss_backward_gauss_tc", actor, critic, L.ptr(tr.packed_bwd_a),
+                                  L.ptr(tr.packed_bwd_c), tr.ob, tr.num_ac, tr.ac_scale, T, N, *cached)
+        # mixed kernel (chain products on tcgen05, weight-gradient products FFMA): reported against the fp32 peak
+        ks["loss_backward_critic_tc, cached activations (K4, tcgen05 dX + FFMA dW)"] = (
+            bwd_t(None, L.ptr(tr.critic)), 2 * FLOP_CRITIC_FWD * B, None)
+        ks["loss_backward_actor_tc, cached activations (K4, tcgen05 dX + FFMA dW)"] = (
+            bwd_t(L.ptr(tr.actor), None), 2 * FLOP_ACTOR_FWD * B, None)
     import torch
     st2, el2 = tr.state.clone(), tr.elapsed.clone()
     ks["env_step pendulum (K1)"] = (lambda: L.call(
@@ -329,12 +338,25 @@ def run_ours(args, rank, local_rank, world):
     if rank == 0:
         kernel_table.bf16_peak = bf16_peak
         kernels = kernel_table(tr, flush, hbm_peak)
-        dom = kernels["loss_backward_critic (K4)"]
+        if getattr(tr, "tc_bwd", False):
+            dom_name = "loss_backward_critic_tc, cached activations (K4, tcgen05 dX + FFMA dW)"
+            dom_kernel = "acx_mlp_tc_train_kernel<critic> (fused loss+backward on cached activations, K4)"
+            note = ("the weight-gradient half of the kernel's products is fp32 FFMA and bounds it; the chain half runs "
+                    "concurrently on tcgen05 (3xTF32)")
+        elif tr.cache:
+            dom_name = "loss_backward_critic, cached activations (K4)"
+            dom_kernel = "acx_mlp_kernel<critic, train, cached> (fused loss+backward, K4)"
+            note = "the kernel is fp32 FFMA, not a tensor-core kernel"
+        else:
+            dom_name = "loss_backward_critic (K4)"
+            dom_kernel = "acx_mlp_kernel<critic, train> (fused loss+backward, K4)"
+            note = "the kernel is fp32 FFMA, not a tensor-core kernel"
+        dom = kernels[dom_name]
         step_ms = sec / args.steps * 1e3
-        roof = {"kernel": "acx_mlp_kernel<critic, train> (fused loss+backward, K4)", "bound": "fp32",
+        roof = {"kernel": dom_kernel, "bound": "fp32",
                 "achieved": dom["achieved"], "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": dom["frac"],
-                "peak_source": "computed FFMA peak 148 SM x 128 lanes x 2 x 1.965 GHz; the kernel is fp32 FFMA, not a "
-                               "tensor-core kernel (bf16 tensor peak %s: %.0f TFLOP/s)" % (peaks_src, bf16_peak),
+                "peak_source": "computed FFMA peak 148 SM x 128 lanes x 2 x 1.965 GHz; %s (bf16 tensor peak %s: %.0f "
+                               "TFLOP/s)" % (note, peaks_src, bf16_peak),
                 "share_of_step": dom["ms"] / step_ms, "traffic": None,
                 "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
         total_flops = (FLOP_ACTOR_FWD * (1 + 3 + 1) + FLOP_CRITIC_FWD * (3 + (HORIZON + 1) / HORIZON)) * steps_per_it
@@ -345,7 +367,8 @@ def run_ours(args, rank, local_rank, world):
                 "config": {"workload": WORKLOAD, "envs_per_gpu": N_ENVS, "horizon": HORIZON, "mode": args.mode,
                            "l2": "flushed between timed steps (256 MiB write, then 256 MiB read to leave clean lines)", "weights": "glorot-uniform, seed 12321",
                            "rng": "device Philox4x32-10", "cuda_graphs": not args.no_graph,
-                           "forward_engine": "tcgen05 3xTF32" if tr.tc else "fp32 FFMA", "backward_engine": "fp32 FFMA",
+                           "forward_engine": "tcgen05 3xTF32" if tr.tc else "fp32 FFMA", "backward_engine": ("tcgen05 3xTF32 (dX) + fp32 FFMA (dW)" if getattr(tr, "tc_bwd", False)
+                                               else "fp32 FFMA"),
                            "parallelism": "dp%d (envs sharded by rank, NCCL all-reduce of the flat gradient)" % world},
                 "e2e": {"value": world * steps_per_it * args.steps / e_sec, "unit": "env-steps/s",
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e_sec / args.steps * 1e3},

@@ -260,6 +260,30 @@ int acx_loss_backward_cat_cached(const float* actor, const float* critic, int ob
                                  const float* critic_x2, const float* critic_x3, void* workspace,
                                  size_t workspace_bytes, void* stream);
 
+/* Same contract again (A3C/policies.py:74-85,152-158 on the cached activations), with the two back-propagation
+ * chain products  dX2 = dPre3 . W3^T  and  dX1 = dPre2 . W2^T  on the tcgen05 tensor cores (3xTF32 split, fp32
+ * accumulation, ~1e-6 relative per product) while the weight-gradient products run on the CUDA cores of the same
+ * CTA.  *_packed_bwd: acx_tc_packed_bwd_floats() floats each, 16-byte aligned, filled by
+ * acx_tc_pack_weights_bwd() and re-filled whenever the parameters change.  The activation cache is required.
+ * Gradients agree with acx_loss_backward_*_cached to 3xTF32 accuracy, not bit for bit. */
+size_t acx_tc_packed_bwd_floats(int net, int ob_dim, int num_ac, int cont);
+int acx_tc_pack_weights_bwd(int net, const float* params, int ob_dim, int num_ac, int cont, float* packed,
+                            void* stream);
+int acx_loss_backward_gauss_tc(const float* actor, const float* critic, const float* actor_packed_bwd,
+                               const float* critic_packed_bwd, int ob_dim, int ac_dim, float ac_scale, int rows,
+                               int n, const float* obs, const float* acs, const float* adv,
+                               const float* adv_stats, const float* logp_old, const float* targets,
+                               const float* opt, float* grad_actor, float* grad_critic, float* stats,
+                               const float* actor_x2, const float* actor_x3, const float* critic_x2,
+                               const float* critic_x3, void* workspace, size_t workspace_bytes, void* stream);
+int acx_loss_backward_cat_tc(const float* actor, const float* critic, const float* actor_packed_bwd,
+                             const float* critic_packed_bwd, int ob_dim, int n_act, int rows, int n,
+                             const float* obs, const int* acs, const float* adv, const float* adv_stats,
+                             const float* logp_old, const float* targets, const float* opt, float* grad_actor,
+                             float* grad_critic, float* stats, const float* actor_x2, const float* actor_x3,
+                             const float* critic_x2, const float* critic_x3, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
 /* Critic loss + gradient for the Basic_AC network, whose value head reads the SECOND layer
  * (Basic_AC/policies.py:134-135): the third layer gets a zero gradient, exactly as TF reports None
  * for it.  Workspace as for acx_loss_backward_gauss(ob_dim, 1, 1). */

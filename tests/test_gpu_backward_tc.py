@@ -1,0 +1,184 @@
+"""K4 with the back-propagation chain on the tensor cores (acx_loss_backward_{gauss,cat}_tc) through the C ABI:
+parity with the oracle's analytic fp64 gradients (same bar as tests/test_gpu_backward.py: 2e-5 relative per tensor, or
+twice the error of the oracle's own fp32 evaluation where the batch sum cancels heavily), agreement with the
+all-FFMA cached kernel to 3xTF32 accuracy, run-to-run determinism, argument checks."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import policies as P
+from gpu_util import dev_t, random_weights, rel_err, soa
+from test_gpu_backward import make_opt
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def check_grads(got, want, lay, tol, want32, batch):
+    """Per tensor: max-abs-diff <= bar * max-abs + floor.  bar as in tests/test_gpu_backward.py (tol, or twice the
+    error of the oracle's own fp32 evaluation where the batch sum cancels heavily).  floor = 3e-6 / sqrt(batch): a
+    gradient element is the mean of `batch` per-sample terms of magnitude O(1), each carrying ~1e-6 relative fp32
+    rounding (tanh, exp, the lp_old - lp difference), so the mean carries ~1e-6 / sqrt(batch) absolute noise however
+    small it is itself -- which matters for the one-element tensors (bh, log_std), where max-abs IS that element."""
+    floor = 3e-6 / np.sqrt(batch)
+    for k, o, s in P.items(lay):
+        sz = int(np.prod(s))
+        g, w = got[o:o + sz].astype(np.float64), want[o:o + sz]
+        bar = max(tol, 2.0 * rel_err(want32[o:o + sz], w))
+        err = np.abs(g - w).max()
+        assert err <= bar * np.abs(w).max() + floor, "%s: abs err %.3g (allowed %.3g)" % (k, err, bar * np.abs(w).max() + floor)
+    used = np.zeros(lay["_size"], bool)
+    for k, o, s in P.items(lay):
+        used[o:o + int(np.prod(s))] = True
+    assert not got[~used].any()          # alignment padding carries zero gradient
+
+
+class Case:
+    """Device buffers for one batch; the activation caches are filled by the FFMA *_cached forwards."""
+
+    def __init__(self, lib, dev, cont, ob, num_ac, rows, n, seed, beta=0.7, gam=0.03):
+        self.lib, self.dev, self.cont, self.ob, self.num_ac, self.rows, self.n = lib, dev, cont, ob, num_ac, rows, n
+        self.actor, self.critic = random_weights(ob, num_ac, cont, seed, bias_scale=0.2)
+        self.lay, self.clay = P.actor_layout(ob, num_ac, cont), P.critic_layout(ob)
+        rng = np.random.default_rng(seed + rows * 131 + n)
+        self.B = B = rows * n
+        self.obs = rng.normal(size=(rows, n, ob)).astype(np.float32)
+        self.adv = rng.normal(size=(rows, n)).astype(np.float32)
+        self.targets = (rng.normal(size=(rows, n)) * 2).astype(np.float32)
+        self.beta, self.gam = beta, gam
+        self.a, self.c = dev_t(self.actor, dev), dev_t(self.critic, dev)
+        self.o = dev_t(np.stack([soa(x) for x in self.obs]), dev)
+        H3a = 64
+        self.ax2, self.ax3 = torch.zeros((rows, 128, n), device=dev), torch.zeros((rows, H3a, n), device=dev)
+        self.cx2, self.cx3 = torch.zeros((rows, 128, n), device=dev), torch.zeros((rows, 128, n), device=dev)
+        s = lib.cur_stream()
+        lp = torch.empty((rows, n), device=dev)
+        if cont:
+            noise = dev_t(rng.normal(size=(rows, num_ac, n)).astype(np.float32), dev)
+            self.acs_d = torch.empty((rows, num_ac, n), device=dev)
+            lib.call("acx_policy_forward_sample_gauss_cached", lib.ptr(self.a), ob, num_ac, 2.0, rows, n, lib.ptr(self.o),
+                     lib.ptr(noise), 0, 0, 0, None, lib.ptr(self.acs_d), lib.ptr(lp), None, None, lib.ptr(self.ax2),
+                     lib.ptr(self.ax3), s)
+        else:
+            noise = dev_t(rng.uniform(size=(rows, n)).astype(np.float32), dev)
+            self.acs_d = torch.empty((rows, n), device=dev, dtype=torch.int32)
+            lib.call("acx_policy_forward_sample_cat_cached", lib.ptr(self.a), ob, num_ac, rows, n, lib.ptr(self.o),
+                     lib.ptr(noise), 0, 0, 0, None, lib.ptr(self.acs_d), lib.ptr(lp), None, None, lib.ptr(self.ax2),
+                     lib.ptr(self.ax3), s)
+        v = torch.empty((rows, n), device=dev)
+        lib.call("acx_value_forward_cached", lib.ptr(self.c), ob, rows, n, lib.ptr(self.o), lib.ptr(v), 0, lib.ptr(self.cx2),
+                 lib.ptr(self.cx3), s)
+        torch.cuda.synchronize()
+        self.lp_old = (lp.cpu().numpy() + rng.normal(size=(rows, n)).astype(np.float32) * 0.1).astype(np.float32)
+        acs = self.acs_d.cpu().numpy()
+        self.acs = np.ascontiguousarray(acs.transpose(0, 2, 1)) if cont else acs       # [rows, n, d] / [rows, n]
+        self.adv_d, self.lp_d, self.tg_d = (dev_t(x, dev) for x in (self.adv, self.lp_old, self.targets))
+        self.opt = make_opt(lib, dev, beta=beta, gamma_ent=gam)
+        self.nbytes = lib.load().acx_loss_backward_workspace_bytes(ob, num_ac, int(cont))
+        self.ws = torch.empty(self.nbytes, device=dev, dtype=torch.uint8)
+        self.pa = torch.zeros(lib.load().acx_tc_packed_bwd_floats(0, ob, num_ac, int(cont)), device=dev)
+        self.pc = torch.zeros(lib.load().acx_tc_packed_bwd_floats(1, ob, 1, 0), device=dev)
+        lib.call("acx_tc_pack_weights_bwd", 0, lib.ptr(self.a), ob, num_ac, int(cont), lib.ptr(self.pa), s)
+        lib.call("acx_tc_pack_weights_bwd", 1, lib.ptr(self.c), ob, 1, 0, lib.ptr(self.pc), s)
+
+    def run(self, which, actor=True, critic=True):
+        lib = self.lib
+        ga, gc = torch.full_like(self.a, 7.0), torch.full_like(self.c, 7.0)
+        stats = torch.zeros(16, device=self.dev)
+        tail = (self.rows, self.n, lib.ptr(self.o), lib.ptr(self.acs_d), lib.ptr(self.adv_d), None, lib.ptr(self.lp_d),
+                lib.ptr(self.tg_d), lib.ptr(self.opt), lib.ptr(ga), lib.ptr(gc), lib.ptr(stats), lib.ptr(self.ax2),
+                lib.ptr(self.ax3), lib.ptr(self.cx2), lib.ptr(self.cx3), lib.ptr(self.ws), self.nbytes, lib.cur_stream())
+        nets = (lib.ptr(self.a) if actor else None, lib.ptr(self.c) if critic else None)
+        dims = (self.ob, self.num_ac, 2.0) if self.cont else (self.ob, self.num_ac)
+        kind = "gauss" if self.cont else "cat"
+        for _ in range(2):      # twice into the same workspace: partials must not leak between calls
+            if which == "tc":
+                lib.call("acx_loss_backward_%s_tc" % kind, *nets, lib.ptr(self.pa), lib.ptr(self.pc), *dims, *tail)
+            else:
+                lib.call("acx_loss_backward_%s_cached" % kind, *nets, *dims, *tail)
+        torch.cuda.synchronize()
+        return ga.cpu().numpy(), gc.cpu().numpy(), stats.cpu().numpy()
+
+    def oracle(self, dtype):
+        B, ob = self.B, self.ob
+        acs = self.acs.reshape(B, self.num_ac) if self.cont else self.acs.reshape(B)
+        wa = P.actor_loss_grads(self.actor, self.lay, self.obs.reshape(B, ob), acs, self.adv.reshape(B),
+                                self.lp_old.reshape(B), self.beta, self.gam, self.cont, 2.0, clip=None, dtype=dtype)
+        wc = P.critic_loss_grads(self.critic, self.clay, self.obs.reshape(B, ob), self.targets.reshape(B), dtype=dtype)
+        return wa, wc
+
+
+@pytest.mark.parametrize("rows,n", [(1, 128), (1, 50), (2, 333), (20, 512), (3, 20000)])
+def test_gauss_tc_backward_matches_oracle(lib, dev, rows, n):
+    k = Case(lib, dev, True, 3, 1, rows, n, 21)
+    ga, gc, stats = k.run("tc")
+    wa, wc = k.oracle(np.float64)
+    wa32, wc32 = k.oracle(np.float32)
+    check_grads(ga, wa["grad_raw"], k.lay, 2 * TOL, wa32["grad_raw"], k.B)
+    check_grads(gc, wc["grad"], k.clay, 2 * TOL, wc32["grad"], k.B)
+    np.testing.assert_allclose(stats[3], wa["loss"], rtol=2 * TOL, atol=1e-6)
+    np.testing.assert_allclose(stats[4], wc["loss"], rtol=2 * TOL)
+    np.testing.assert_allclose(stats[5], wa["kl"], rtol=2 * TOL)
+    np.testing.assert_allclose(stats[6], wa["ent"], rtol=2 * TOL)
+
+
+@pytest.mark.parametrize("ob,n_act", [(4, 2), (6, 3)])
+@pytest.mark.parametrize("rows,n", [(1, 100), (5, 1000)])
+def test_cat_tc_backward_matches_oracle(lib, dev, ob, n_act, rows, n):
+    k = Case(lib, dev, False, ob, n_act, rows, n, 31, beta=1.0, gam=0.01)
+    ga, gc, stats = k.run("tc")
+    wa, wc = k.oracle(np.float64)
+    wa32, wc32 = k.oracle(np.float32)
+    check_grads(ga, wa["grad_raw"], k.lay, 2 * TOL, wa32["grad_raw"], k.B)
+    check_grads(gc, wc["grad"], k.clay, 2 * TOL, wc32["grad"], k.B)
+    np.testing.assert_allclose(stats[3], wa["loss"], rtol=2 * TOL, atol=1e-6)
+    np.testing.assert_allclose(stats[4], wc["loss"], rtol=2 * TOL)
+
+
+@pytest.mark.parametrize("cont,ob,num_ac", [(True, 3, 1), (False, 4, 2)])
+def test_tc_backward_agrees_with_the_ffma_kernel(lib, dev, cont, ob, num_ac):
+    k = Case(lib, dev, cont, ob, num_ac, 20, 4096, 5)
+    ta, tcg, ts = k.run("tc")
+    fa, fc, fs = k.run("ffma")
+    for got, want, lay in ((ta, fa, k.lay), (tcg, fc, k.clay)):
+        for name, o, s in P.items(lay):
+            sz = int(np.prod(s))
+            assert rel_err(got[o:o + sz], want[o:o + sz]) < 2e-5, name
+    # the head, its gradients and the loss sums never touch the tensor cores: identical
+    for lay, got, want in ((k.lay, ta, fa), (k.clay, tcg, fc)):
+        for name in ("Wh", "bh") if "Wh" in lay else ("Wv", "bv"):
+            o, s = lay[name]
+            sz = int(np.prod(s))
+            np.testing.assert_array_equal(got[o:o + sz], want[o:o + sz])
+    np.testing.assert_array_equal(ts, fs)
+
+
+def test_tc_backward_is_deterministic_and_takes_either_net(lib, dev):
+    k = Case(lib, dev, True, 3, 1, 20, 2048, 8)
+    r1, r2 = k.run("tc"), k.run("tc")
+    np.testing.assert_array_equal(r1[0], r2[0])
+    np.testing.assert_array_equal(r1[1], r2[1])
+    only_a, only_c = k.run("tc", critic=False), k.run("tc", actor=False)
+    np.testing.assert_array_equal(only_a[0], r1[0])
+    np.testing.assert_array_equal(only_c[1], r1[1])
+    assert (only_a[1] == 7.0).all() and (only_c[0] == 7.0).all()      # the absent net's gradient is untouched
+
+
+def test_tc_backward_rejects_bad_arguments(lib, dev):
+    k = Case(lib, dev, True, 3, 1, 1, 128, 2)
+    f = lib.load().acx_loss_backward_gauss_tc
+    ga, gc, st = torch.zeros_like(k.a), torch.zeros_like(k.c), torch.zeros(16, device=dev)
+
+    def call(pa, ax2, rows=1, nbytes=k.nbytes):
+        return f(k.a.data_ptr(), k.c.data_ptr(), pa, k.pc.data_ptr(), 3, 1, 2.0, rows, 128, k.o.data_ptr(),
+                 k.acs_d.data_ptr(), k.adv_d.data_ptr(), None, k.lp_d.data_ptr(), k.tg_d.data_ptr(), k.opt.data_ptr(),
+                 ga.data_ptr(), gc.data_ptr(), st.data_ptr(), ax2, k.ax3.data_ptr(), k.cx2.data_ptr(), k.cx3.data_ptr(),
+                 k.ws.data_ptr(), nbytes, None)
+
+    assert call(None, k.ax2.data_ptr()) == -1 and b"packed" in lib.load().acx_last_error()
+    assert call(k.pa.data_ptr(), None) == -1
+    assert call(k.pa.data_ptr() + 4, k.ax2.data_ptr()) == -1
+    assert call(k.pa.data_ptr(), k.ax2.data_ptr(), rows=0) == -1 and b"empty" in lib.load().acx_last_error()
+    assert call(k.pa.data_ptr(), k.ax2.data_ptr(), nbytes=1024) == -1 and b"workspace" in lib.load().acx_last_error()
+    assert call(k.pa.data_ptr(), k.ax2.data_ptr()) == 0
+    torch.cuda.synchronize()
