@@ -14,9 +14,15 @@
 //            A from TMEM, B = the weight rows themselves (K-major in j), pre-split and pre-arranged by
 //            acx_tc_pack_weights_bwd, streamed through a 4 x 16 KB ring (bulk-TMA), accumulators in TMEM.
 // Gradients are accumulated in the per-CTA scratch rows and reduced in fixed order exactly as in acx_mlp.cu.
+//
+// SPLIT = true (the default path, n % 4 == 0): the two big weight-gradient products leave this kernel as well.  It
+// then only streams dPre3, dPre2 and the recomputed X1 to HBM ([rows][feature][n], bulk-TMA stores of the shared
+// tiles) and acx_wgrad_kernel (acx_wgrad.cu) forms  dW3 = X2 dPre3^T  and  dW2 = X1 dPre2^T  on the tensor cores
+// from those arrays, accumulating over the CTA's whole share of the batch in tensor memory.
 #include "acx_mlp.cuh"
 #include "acx_head.cuh"
 #include "acx_umma.cuh"
+#include "acx_wgrad.cuh"
 
 using namespace acxmlp;
 using namespace acxumma;
@@ -96,8 +102,35 @@ __device__ inline void a_store32_tt(uint32_t tmem_lane, int j0, const float (&v)
   tmem_st32(tmem_lane + TT_A_LO + (uint32_t)j0, lo);
 }
 
-template <int H1, int H3, bool LRELU, int HEAD>
-__global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A, const float* __restrict__ packed) {
+// smem rows -> global rows (row r of `src`, MT floats, to dst + r * gld); full tiles go out as bulk-TMA stores
+__device__ inline void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ inline void store_rows(const float* __restrict__ src, float* __restrict__ dst, size_t gld, int nrows,
+                                  int valid, bool bulk) {
+  const int tid = threadIdx.x;
+  if (bulk) {
+    if (tid < nrows) {
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + (size_t)tid * gld),
+                   "r"(acx_smem_u32(src + tid * MS)), "r"(MT * 4)
+                   : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+  } else {
+    for (int idx = tid; idx < nrows * MT; idx += TT_WORK) {
+      const int r = idx >> 7, m = idx & 127;
+      if (m < valid) dst[(size_t)r * gld + m] = src[r * MS + m];
+    }
+  }
+}
+
+struct SplitOut {            // SPLIT: where dPre3 / dPre2 / X1 go ([rows][feature][n])
+  float* d3;
+  float* d2;
+  float* x1;
+};
+
+template <int H1, int H3, bool LRELU, int HEAD, bool SPLIT>
+__global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A, const float* __restrict__ packed,
+                                                                    const SplitOut so) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   TtSmem& sm = *reinterpret_cast<TtSmem*>(smem_raw);
   constexpr int TJ3 = H3 / 16, NB = H1 / 128, N3C = H3 / 16;
@@ -180,6 +213,8 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
       const int row = tile / tpr, n0 = (tile % tpr) * MT;
       const int valid = min(MT, A.n - n0);
       const unsigned int par = tiles_done & 1u;
+      const bool bulk = vec_ok && valid == MT;       // full, 16-byte aligned rows: bulk-TMA loads and stores
+      if (SPLIT) bulk_wait_read();                   // the previous tile's row stores have left shared memory
       work_sync();                                   // previous tile is done with every shared buffer
       for (int idx = tid; idx < ob * MT; idx += TT_WORK) {
         const int i = idx / MT, m = idx % MT;
@@ -188,7 +223,7 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
       {
         const float* g2 = A.x2_in + ((size_t)row * H2) * A.n + n0;
         const float* g3 = A.x3_in + ((size_t)row * H3) * A.n + n0;
-        if (vec_ok && valid == MT) {
+        if (bulk) {
           uint64_t* bar = reinterpret_cast<uint64_t*>(&sm.bar_act);
           if (tid == 0) acx_mbar_expect_tx(bar, (uint32_t)((H2 + H3) * MT * 4));
           work_sync();
@@ -256,9 +291,11 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
+      if (SPLIT) fence_proxy_async();              // dPre3 in shared memory -> visible to the bulk stores
       work_sync();
-      // ---------------------------------------------- dW3, db3 on the CUDA cores while dX2 runs on the tensor cores
-      g_stage<8, TJ3>(sm.X2, sm.X3, scr + L.W3, H3, first, c);
+      // ---------------------------------------------- dW3, db3 while dX2 runs on the tensor cores
+      if (SPLIT) store_rows(sm.X3, so.d3 + ((size_t)row * H3) * A.n + n0, (size_t)A.n, H3, valid, bulk);
+      else g_stage<8, TJ3>(sm.X2, sm.X3, scr + L.W3, H3, first, c);
       bias_grad(sm.X3, H3, scr + L.b3, first);
       work_sync();
       // ---------------------------------------------- dPre2 = dX2 * act'(X2): in place + next A operand
@@ -283,13 +320,21 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
+      if (SPLIT) { fence_proxy_async(); bulk_wait_read(); }      // (dPre3 has left X3: layer1_block may overwrite it)
       work_sync();
+      if (SPLIT) store_rows(sm.X2, so.d2 + ((size_t)row * H2) * A.n + n0, (size_t)A.n, H2, valid, bulk);
       bias_grad(sm.X2, H2, scr + L.b2, first);
       // ---------------------------------------------- layers 1/2: dW2 on the CUDA cores, dX1 on the tensor cores
       for (int h = 0; h < NB; ++h) {
         layer1_block<H1, LRELU>(sm, h, ob, sm.X3);
+        if (SPLIT) fence_proxy_async();
         work_sync();
-        g_stage<8, 8>(sm.X3, sm.X2, scr + L.W2 + (size_t)h * 128 * H2, H2, first, c);
+        if (SPLIT) {
+          store_rows(sm.X3, so.x1 + ((size_t)row * H1 + h * 128) * A.n + n0, (size_t)A.n, 128, valid, bulk);
+          bulk_wait_read();                          // X1 block has left X3 before dPre1 overwrites it
+        } else {
+          g_stage<8, 8>(sm.X3, sm.X2, scr + L.W2 + (size_t)h * 128 * H2, H2, first, c);
+        }
         work_sync();
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[1 + h]), par);
         fence_after_sync();
@@ -390,13 +435,28 @@ __global__ void __launch_bounds__(256) acx_grad_reduce_tc_kernel(const float* __
   }
 }
 
-template <int H1, int H3, bool LRELU, int HEAD>
-int launch_tt(const Args& a, const float* packed, int grid, cudaStream_t st) {
-  auto kern = acx_mlp_tc_train_kernel<H1, H3, LRELU, HEAD>;
+template <int H1, int H3, bool LRELU, int HEAD, bool SPLIT>
+int launch_tt1(const Args& a, const float* packed, const SplitOut& so, int grid, cudaStream_t st) {
+  auto kern = acx_mlp_tc_train_kernel<H1, H3, LRELU, HEAD, SPLIT>;
   ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TtSmem) + 1024));
-  kern<<<grid, TT_NT, sizeof(TtSmem) + 1024, st>>>(a, packed);
+  kern<<<grid, TT_NT, sizeof(TtSmem) + 1024, st>>>(a, packed, so);
   ACX_LAUNCH_OK("acx_mlp_tc_train_kernel");
   return ACX_OK;
+}
+
+// split == nullptr: everything in one kernel (weight gradients FFMA); else chain kernel + acx_wgrad_kernel
+template <int H1, int H3, bool LRELU, int HEAD>
+int launch_tt(const Args& a, const float* packed, float* split, int grid, cudaStream_t st) {
+  SplitOut so = {nullptr, nullptr, nullptr};
+  if (split == nullptr) return launch_tt1<H1, H3, LRELU, HEAD, false>(a, packed, so, grid, st);
+  const size_t bn = (size_t)a.rows * (size_t)a.n;
+  so.d3 = split; so.d2 = so.d3 + bn * H3; so.x1 = so.d2 + bn * H2;
+  int rc = launch_tt1<H1, H3, LRELU, HEAD, true>(a, packed, so, grid, st);
+  if (rc) return rc;
+  AcxWgradArgs w;
+  w.x2 = a.x2_in; w.d3 = so.d3; w.x1 = so.x1; w.d2 = so.d2; w.rows = a.rows; w.n = a.n; w.H1 = H1; w.H3 = H3;
+  w.scratch = a.scratch; w.scr_stride = a.L.size; w.offW3 = a.L.W3; w.offW2 = a.L.W2; w.grid = grid;
+  return acx_wgrad_launch(w, st);
 }
 
 int loss_backward_tc(int cont, const float* actor, const float* critic, const float* actor_packed,
@@ -424,6 +484,13 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
   float* scr_a = wT_a + (size_t)(ACX_A_H3 + ACX_A_H1 + ACX_C_H3 + ACX_C_H1) * 128;
   float* scr_c = scr_a + (size_t)sms * La.size;
   const double count = (double)rows * (double)n;
+  // room for dPre3 / dPre2 / X1 of one network at a time behind the base workspace -> two-kernel (split) path
+  float* split = nullptr;
+  {
+    const size_t base_bytes = (acx_loss_backward_workspace_bytes(ob_dim, num_ac, cont) + 255) & ~(size_t)255;
+    if ((n & 3) == 0 && workspace_bytes >= acx_loss_backward_tc_workspace_bytes(ob_dim, num_ac, cont, rows, n))
+      split = reinterpret_cast<float*>(wsb + base_bytes);
+  }
   if (actor) {
     ACX_REQUIRE(actor_packed && ax2 && ax3 && acs && adv && logp_old && opt && grad_actor && acx_aligned16(actor_packed),
                 "%s: null / misaligned actor-side buffer (packed weights and the activation cache are required)", fn);
@@ -433,8 +500,8 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
     a.ac_in_i = cont ? nullptr : reinterpret_cast<const int*>(acs);
     a.adv = adv; a.adv_stats = adv_stats; a.logp_old = logp_old; a.opt = opt;
     a.scratch = scr_a; a.loss_partial = lossp_a; a.x2_in = ax2; a.x3_in = ax3;
-    int rc = cont ? launch_tt<128, 64, true, HEAD_GAUSS>(a, actor_packed, grid, st)
-                  : launch_tt<128, 64, true, HEAD_CAT>(a, actor_packed, grid, st);
+    int rc = cont ? launch_tt<128, 64, true, HEAD_GAUSS>(a, actor_packed, split, grid, st)
+                  : launch_tt<128, 64, true, HEAD_CAT>(a, actor_packed, split, grid, st);
     if (rc) return rc;
     acx_grad_reduce_tc_kernel<<<(La.size + 255) / 256, 256, 0, st>>>(scr_a, grid, La.size, grad_actor, lossp_a, stats,
                                                                     opt, 1, count);
@@ -446,7 +513,7 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
     Args a; memset(&a, 0, sizeof(a));
     a.params = critic; a.L = Lc; a.rows = rows; a.n = n; a.obs = obs;
     a.targets = targets; a.scratch = scr_c; a.loss_partial = lossp_c; a.x2_in = cx2; a.x3_in = cx3;
-    int rc = launch_tt<256, 128, false, HEAD_VALUE>(a, critic_packed, grid, st);
+    int rc = launch_tt<256, 128, false, HEAD_VALUE>(a, critic_packed, split, grid, st);
     if (rc) return rc;
     acx_grad_reduce_tc_kernel<<<(Lc.size + 255) / 256, 256, 0, st>>>(scr_c, grid, Lc.size, grad_critic, lossp_c, stats,
                                                                     opt, 0, count);
@@ -456,6 +523,13 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
 }
 
 }  // namespace
+
+extern "C" size_t acx_loss_backward_tc_workspace_bytes(int ob_dim, int num_ac, int cont, int rows, int n) {
+  const size_t base_bytes = (acx_loss_backward_workspace_bytes(ob_dim, num_ac, cont) + 255) & ~(size_t)255;
+  const size_t feat = (size_t)(ACX_C_H3 + H2 + ACX_C_H1) > (size_t)(ACX_A_H3 + H2 + ACX_A_H1)
+                          ? (size_t)(ACX_C_H3 + H2 + ACX_C_H1) : (size_t)(ACX_A_H3 + H2 + ACX_A_H1);
+  return base_bytes + feat * (size_t)(rows > 0 ? rows : 0) * (size_t)(n > 0 ? n : 0) * sizeof(float);
+}
 
 extern "C" size_t acx_tc_packed_bwd_floats(int net, int ob_dim, int num_ac, int cont) {
   (void)ob_dim; (void)num_ac; (void)cont;

@@ -34,6 +34,15 @@ __device__ inline uint64_t smem_desc(const void* ptr, uint32_t lbo_bytes, uint32
          (1ull << 46);
 }
 
+// 128-byte-swizzled K-major operand (what a TMA tensor load with CU_TENSOR_MAP_SWIZZLE_128B produces from a box of
+// 32 fp32 = 128 bytes per row): rows of 128 bytes, 8-row groups of 1024 bytes (tile base 1024-byte aligned), the
+// 16-byte chunk c of row r stored at chunk c ^ (r % 8).  SBO = 1024 (next 8 rows), LBO unused, layout_type 2.
+// A K step inside the row is taken by advancing the start address (+32 bytes per kind::tf32 instruction).
+__device__ inline uint64_t smem_desc_sw128(const void* ptr) {
+  const uint64_t addr = (uint64_t)((acx_smem_u32(ptr) & 0x3FFFFu) >> 4);
+  return addr | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
 // 32-bit instruction descriptor: D = F32, A = B = TF32, dense, no negate
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, bool a_mn_major, bool b_mn_major) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
@@ -108,6 +117,8 @@ __device__ inline float round_tf32(float x) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
   return __uint_as_float(u);
 }
+// what kind::tf32 sees of a raw fp32 word: the low 13 mantissa bits are ignored
+__device__ inline float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 __device__ inline void split_tf32(float x, float& hi, float& lo) {
   hi = round_tf32(x);
   lo = round_tf32(x - hi);      // x - hi is exact in fp32

@@ -1,0 +1,214 @@
+// Weight-gradient products of K4 on the tensor cores (tcgen05, 3xTF32), one launch per network:
+//     dW3[k][j] = sum_s X2[k][s] * dPre3[j][s]          (A3C/policies.py:82,155: compute_gradients of the
+//     dW2[k][j] = sum_s X1[k][s] * dPre2[j][s]           third / second dense layer's kernel)
+// summed over the whole [rows x n] batch.  Operands are the [rows][feature][n] arrays acx_mlp_tc_train_kernel<SPLIT>
+// wrote (dPre3, dPre2, X1) and the activation cache (X2): the sample index is contiguous, i.e. both operands are
+// K-major as they lie in HBM.  Each persistent CTA owns the 128-sample tiles  blockIdx.x, +gridDim.x, ...  and keeps
+// its partial dW3 / dW2 in tensor memory (fp32, 128 + H1 columns) for the whole kernel; at the end they go to the CTA's
+// scratch row, which acx_grad_reduce sums in fixed order (bit-reproducible run to run).
+//   warp 0     producer: TMA tensor loads of [features x 32 samples] boxes, 128-byte swizzle, NSTAGE-deep ring
+//   warp 1     issuer:   per box 4 K-steps x 3 kind::tf32 MMAs (lo*hi, hi*lo, hi*hi) per 128-row block
+//   warps 2-9  splitters: lo = rna(x - trunc(x)) of every landed word into the stage's second buffer (the MMA itself
+//              ignores the low 13 mantissa bits of the raw word, which therefore serves as hi); warps 2-5 also run
+//              the epilogue (tcgen05.ld -> scratch row).
+// HBM-bound: 4 bytes per operand element, every element read once.
+#include "acx_wgrad.cuh"
+#include "acx_tmap.cuh"
+#include "acx_umma.cuh"
+
+using namespace acxumma;
+
+namespace {
+
+constexpr int WG_THREADS = 320;
+constexpr int BOX = 32;                    // samples per box row (128 bytes)
+constexpr int BLK = 128 * BOX;             // floats of a 128-row box
+
+template <int H1> struct WgCfg {
+  static constexpr int NB = H1 / 128;
+  static constexpr int STAGE = (NB + 1) * BLK;              // floats: A blocks, then the B box
+  static constexpr int NSTAGE = NB == 1 ? 3 : 2;
+  static constexpr size_t SMEM = (size_t)NSTAGE * STAGE * 2 * sizeof(float) + 1024 + 256;
+};
+
+struct WgBars {
+  unsigned long long full[3], split[3], empty[3], done;
+  unsigned int tmem_base;
+};
+
+__device__ inline void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(acx_smem_u32(bar)) : "memory");
+}
+
+template <int H1, int H3>
+__global__ void __launch_bounds__(WG_THREADS, 1)
+acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constant__ CUtensorMap mapD3,
+                 const __grid_constant__ CUtensorMap mapX1, const __grid_constant__ CUtensorMap mapD2, int rows, int n,
+                 float* __restrict__ scratch, int scr_stride, int offW3, int offW2) {
+  using Cfg = WgCfg<H1>;
+  constexpr int NB = Cfg::NB, NSTAGE = Cfg::NSTAGE;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* raw = reinterpret_cast<float*>(base);                         // [NSTAGE][STAGE]
+  float* lo = raw + (size_t)NSTAGE * Cfg::STAGE;                       // [NSTAGE][STAGE]
+  WgBars& B = *reinterpret_cast<WgBars*>(lo + (size_t)NSTAGE * Cfg::STAGE);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tpr = (n + 127) / 128;
+  const int ntiles = rows * tpr;
+
+  if (warp == 1) tmem_alloc(&B.tmem_base, 512);
+  if (tid == 0) {
+    for (int i = 0; i < NSTAGE; ++i) {
+      acx_mbar_init(reinterpret_cast<uint64_t*>(&B.full[i]), 1);
+      acx_mbar_init(reinterpret_cast<uint64_t*>(&B.split[i]), 256);
+      acx_mbar_init(reinterpret_cast<uint64_t*>(&B.empty[i]), 1);
+    }
+    acx_mbar_init(reinterpret_cast<uint64_t*>(&B.done), 1);
+    acx_mbar_fence_init();
+  }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = B.tmem_base;
+
+  // every role walks the same sequence of boxes: phase 0 = layer 3 (A = X2, B = dPre3), phase 1 = layer 2 (A = the NB
+  // 128-row blocks of X1, B = dPre2); per tile one box per started 32 samples
+  if (warp == 0) {
+    if (lane == 0) {
+      unsigned int it = 0;
+      for (int phase = 0; phase < 2; ++phase) {
+        const int nblk = phase == 0 ? 1 : NB, brows = phase == 0 ? H3 : 128, arows = phase == 0 ? 128 : H1;
+        const CUtensorMap* mA = phase == 0 ? &mapX2 : &mapX1;
+        const CUtensorMap* mB = phase == 0 ? &mapD3 : &mapD2;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+          const int row = tile / tpr, n0 = (tile % tpr) * 128;
+          const int nsub = (min(128, n - n0) + BOX - 1) / BOX;
+          for (int kk = 0; kk < nsub; ++kk, ++it) {
+            const unsigned int slot = it % NSTAGE;
+            if (it >= (unsigned)NSTAGE)
+              acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.empty[slot]), ((it / NSTAGE) - 1u) & 1u);
+            uint64_t* full = reinterpret_cast<uint64_t*>(&B.full[slot]);
+            acx_mbar_expect_tx(full, (uint32_t)((nblk * 128 + brows) * BOX * 4));
+            float* dst = raw + (size_t)slot * Cfg::STAGE;
+            for (int b = 0; b < nblk; ++b) tma_load_2d(dst + b * BLK, mA, n0 + kk * BOX, row * arows + b * 128, full);
+            tma_load_2d(dst + NB * BLK, mB, n0 + kk * BOX, row * brows, full);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      unsigned int it = 0;
+      for (int phase = 0; phase < 2; ++phase) {
+        const int nblk = phase == 0 ? 1 : NB;
+        const uint32_t idesc = idesc_tf32(128, phase == 0 ? H3 : 128, false, false);
+        bool fresh = true;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+          const int n0 = (tile % tpr) * 128;
+          const int nsub = (min(128, n - n0) + BOX - 1) / BOX;
+          for (int kk = 0; kk < nsub; ++kk, ++it) {
+            const unsigned int slot = it % NSTAGE;
+            acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.split[slot]), (it / NSTAGE) & 1u);
+            fence_after_sync();
+            const float* r = raw + (size_t)slot * Cfg::STAGE;
+            const float* l = lo + (size_t)slot * Cfg::STAGE;
+#pragma unroll
+            for (int ks = 0; ks < BOX / 8; ++ks) {
+              const uint64_t bh = smem_desc_sw128(r + NB * BLK + ks * 8), bl = smem_desc_sw128(l + NB * BLK + ks * 8);
+              for (int b = 0; b < nblk; ++b) {
+                const uint64_t ah = smem_desc_sw128(r + b * BLK + ks * 8), al = smem_desc_sw128(l + b * BLK + ks * 8);
+                const uint32_t d = tmem + (phase == 0 ? 0u : 128u + 128u * (uint32_t)b);
+                mma_tf32(d, al, bh, idesc, !(fresh && ks == 0));
+                mma_tf32(d, ah, bl, idesc, true);
+                mma_tf32(d, ah, bh, idesc, true);
+              }
+            }
+            fresh = false;
+            commit(reinterpret_cast<uint64_t*>(&B.empty[slot]));
+          }
+        }
+      }
+      commit(reinterpret_cast<uint64_t*>(&B.done));
+    }
+  } else {
+    const int t = tid - 64;                       // 0..255
+    unsigned int it = 0;
+    for (int phase = 0; phase < 2; ++phase) {
+      const int na4 = (phase == 0 ? 1 : NB) * (BLK / 4), nb4 = (phase == 0 ? H3 : 128) * (BOX / 4);
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int n0 = (tile % tpr) * 128;
+        const int nsub = (min(128, n - n0) + BOX - 1) / BOX;
+        for (int kk = 0; kk < nsub; ++kk, ++it) {
+          const unsigned int slot = it % NSTAGE;
+          acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.full[slot]), (it / NSTAGE) & 1u);
+          const float4* r4 = reinterpret_cast<const float4*>(raw + (size_t)slot * Cfg::STAGE);
+          float4* l4 = reinterpret_cast<float4*>(lo + (size_t)slot * Cfg::STAGE);
+          for (int i = t; i < na4 + nb4; i += 256) {
+            const int idx = i < na4 ? i : NB * (BLK / 4) + (i - na4);
+            const float4 x = r4[idx];
+            float4 y;
+            y.x = round_tf32(x.x - trunc_tf32(x.x)); y.y = round_tf32(x.y - trunc_tf32(x.y));
+            y.z = round_tf32(x.z - trunc_tf32(x.z)); y.w = round_tf32(x.w - trunc_tf32(x.w));
+            l4[idx] = y;
+          }
+          fence_proxy_async();
+          mbar_arrive(&B.split[slot]);
+        }
+      }
+    }
+    if (warp < 6) {
+      // ------------------------------------------------ epilogue: tensor memory -> this CTA's scratch row
+      acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.done), 0);
+      fence_after_sync();
+      const int r = (warp & 3) * 32 + lane;                   // TMEM lane = row of the A block
+      const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+      float* scr = scratch + (size_t)blockIdx.x * scr_stride;
+      float v[32];
+      for (int c0 = 0; c0 < H3; c0 += 32) {
+        tmem_ld32(tl + (uint32_t)c0, v);
+        float4* p = reinterpret_cast<float4*>(scr + offW3 + r * H3 + c0);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) p[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+      for (int b = 0; b < NB; ++b)
+        for (int c0 = 0; c0 < 128; c0 += 32) {
+          tmem_ld32(tl + 128u + 128u * (uint32_t)b + (uint32_t)c0, v);
+          float4* p = reinterpret_cast<float4*>(scr + offW2 + (b * 128 + r) * 128 + c0);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) p[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+template <int H1, int H3>
+int launch_wgrad(const AcxWgradArgs& a, cudaStream_t st) {
+  CUtensorMap mX2, mD3, mX1, mD2;
+  const uint64_t pitch = (uint64_t)a.n * 4;
+  int rc = acx_tmap_2d(&mX2, a.x2, (uint64_t)a.n, (uint64_t)a.rows * 128, pitch, BOX, 128);
+  if (!rc) rc = acx_tmap_2d(&mD3, a.d3, (uint64_t)a.n, (uint64_t)a.rows * H3, pitch, BOX, H3);
+  if (!rc) rc = acx_tmap_2d(&mX1, a.x1, (uint64_t)a.n, (uint64_t)a.rows * H1, pitch, BOX, 128);
+  if (!rc) rc = acx_tmap_2d(&mD2, a.d2, (uint64_t)a.n, (uint64_t)a.rows * 128, pitch, BOX, 128);
+  ACX_REQUIRE(rc == 0, "acx_wgrad: cuTensorMapEncodeTiled failed (%d) for rows=%d n=%d", rc, a.rows, a.n);
+  auto kern = acx_wgrad_kernel<H1, H3>;
+  ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgCfg<H1>::SMEM));
+  kern<<<a.grid, WG_THREADS, WgCfg<H1>::SMEM, st>>>(mX2, mD3, mX1, mD2, a.rows, a.n, a.scratch, a.scr_stride, a.offW3,
+                                                    a.offW2);
+  ACX_LAUNCH_OK("acx_wgrad_kernel");
+  return ACX_OK;
+}
+
+}  // namespace
+
+int acx_wgrad_launch(const AcxWgradArgs& a, void* stream) {
+  ACX_REQUIRE((a.n & 3) == 0, "acx_wgrad: n must be a multiple of 4 (16-byte row pitch for the TMA tensor maps), got %d", a.n);
+  ACX_REQUIRE(acx_aligned16(a.x2) && acx_aligned16(a.d3) && acx_aligned16(a.x1) && acx_aligned16(a.d2) &&
+                  acx_aligned16(a.scratch), "acx_wgrad: operands must be 16-byte aligned");
+  if (a.H1 == 128 && a.H3 == 64) return launch_wgrad<128, 64>(a, (cudaStream_t)stream);
+  if (a.H1 == 256 && a.H3 == 128) return launch_wgrad<256, 128>(a, (cudaStream_t)stream);
+  ACX_REQUIRE(false, "acx_wgrad: unsupported layer widths H1=%d H3=%d", a.H1, a.H3);
+  return ACX_OK;
+}

@@ -122,6 +122,8 @@ class A2CTrainer:
         self.ws_scan_bytes = L.load().acx_returns_adv_workspace_bytes(T, N)
         self.ws_scan = torch.zeros(self.ws_scan_bytes, device=d, dtype=torch.uint8)
         self.ws_bwd_bytes = L.load().acx_loss_backward_workspace_bytes(self.ob, self.num_ac, int(self.cont))
+        if self.tc_bwd and N % 4 == 0:       # room for dPre3 / dPre2 / X1: weight gradients on the tensor cores too
+            self.ws_bwd_bytes = L.load().acx_loss_backward_tc_workspace_bytes(self.ob, self.num_ac, int(self.cont), T, N)
         self.ws_bwd = torch.empty(self.ws_bwd_bytes, device=d, dtype=torch.uint8)
         self.kl_part = torch.zeros(L.load().acx_kl_workspace_bytes() // 8, device=d, dtype=torch.float64)
         self.kl_blocks = ctypes.c_int(0)
@@ -225,7 +227,8 @@ class A2CTrainer:
                 L.call("acx_loss_backward_gauss_tc", *head, self.num_ac, self.ac_scale, T, N, *cached)
             else:
                 L.call("acx_loss_backward_cat_tc", *head, self.n_act, T, N, *cached)
-            return 2 + 4      # value, scan, 2 x (mlp train, grad reduce)
+            split = self.N % 4 == 0
+            return 2 + (6 if split else 4)      # value, scan, 2 x (mlp train, [weight gradients,] grad reduce)
         if self.cache:
             cached = common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3)) + common[-3:]
             if self.cont:

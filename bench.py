@@ -191,14 +191,23 @@ def kernel_table(tr, flush, hbm_peak):
         L.ptr(tr.obs_buf), L.ptr(tr.acs), None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part),
         __import__("ctypes").byref(tr.kl_blocks), s), FLOP_ACTOR_FWD * B, "tc")
     if getattr(tr, "tc_bwd", False):
-        def bwd_t(actor, critic):
+        base_bytes = L.load().acx_loss_backward_workspace_bytes(tr.ob, tr.num_ac, int(tr.cont))
+
+        def bwd_t(actor, critic, nbytes):
+            args = cached[:-2] + (nbytes, s)
             return lambda: L.call("acx_loss_backward_gauss_tc", actor, critic, L.ptr(tr.packed_bwd_a),
-                                  L.ptr(tr.packed_bwd_c), tr.ob, tr.num_ac, tr.ac_scale, T, N, *cached)
-        # mixed kernel (chain products on tcgen05, weight-gradient products FFMA): reported against the fp32 peak
-        ks["loss_backward_critic_tc, cached activations (K4, tcgen05 dX + FFMA dW)"] = (
-            bwd_t(None, L.ptr(tr.critic)), 2 * FLOP_CRITIC_FWD * B, None)
-        ks["loss_backward_actor_tc, cached activations (K4, tcgen05 dX + FFMA dW)"] = (
-            bwd_t(L.ptr(tr.actor), None), 2 * FLOP_ACTOR_FWD * B, None)
+                                  L.ptr(tr.packed_bwd_c), tr.ob, tr.num_ac, tr.ac_scale, T, N, *args)
+        # one kernel: chain products on tcgen05, weight-gradient products FFMA (small workspace)
+        ks["loss_backward_critic_tc, one kernel (K4, tcgen05 dX + FFMA dW)"] = (
+            bwd_t(None, L.ptr(tr.critic), base_bytes), 2 * FLOP_CRITIC_FWD * B, None)
+        ks["loss_backward_actor_tc, one kernel (K4, tcgen05 dX + FFMA dW)"] = (
+            bwd_t(L.ptr(tr.actor), None, base_bytes), 2 * FLOP_ACTOR_FWD * B, None)
+        if tr.ws_bwd_bytes > base_bytes:
+            # two kernels: chain kernel + acx_wgrad_kernel, every product on tcgen05 (3xTF32)
+            ks["loss_backward_critic_tc, chain + wgrad kernels (K4, tcgen05 3xTF32)"] = (
+                bwd_t(None, L.ptr(tr.critic), tr.ws_bwd_bytes), 2 * FLOP_CRITIC_FWD * B, "tc")
+            ks["loss_backward_actor_tc, chain + wgrad kernels (K4, tcgen05 3xTF32)"] = (
+                bwd_t(L.ptr(tr.actor), None, tr.ws_bwd_bytes), 2 * FLOP_ACTOR_FWD * B, "tc")
     import torch
     st2, el2 = tr.state.clone(), tr.elapsed.clone()
     ks["env_step pendulum (K1)"] = (lambda: L.call(
@@ -338,8 +347,15 @@ def run_ours(args, rank, local_rank, world):
     if rank == 0:
         kernel_table.bf16_peak = bf16_peak
         kernels = kernel_table(tr, flush, hbm_peak)
-        if getattr(tr, "tc_bwd", False):
-            dom_name = "loss_backward_critic_tc, cached activations (K4, tcgen05 dX + FFMA dW)"
+        base_bytes_ = __import__("actor_critic_algs_on_tensorflow_b200._lib", fromlist=["x"]).load() \
+            .acx_loss_backward_workspace_bytes(tr.ob, tr.num_ac, int(tr.cont))
+        if getattr(tr, "tc_bwd", False) and tr.ws_bwd_bytes > base_bytes_:
+            dom_name = "loss_backward_critic_tc, chain + wgrad kernels (K4, tcgen05 3xTF32)"
+            dom_kernel = ("acx_mlp_tc_train_kernel<critic, split> + acx_wgrad_kernel<critic> (fused loss+backward on "
+                          "cached activations, K4)")
+            note = "every product of the pair runs on tcgen05 as 3xTF32"
+        elif getattr(tr, "tc_bwd", False):
+            dom_name = "loss_backward_critic_tc, one kernel (K4, tcgen05 dX + FFMA dW)"
             dom_kernel = "acx_mlp_tc_train_kernel<critic> (fused loss+backward on cached activations, K4)"
             note = ("the weight-gradient half of the kernel's products is fp32 FFMA and bounds it; the chain half runs "
                     "concurrently on tcgen05 (3xTF32)")
@@ -353,12 +369,22 @@ def run_ours(args, rank, local_rank, world):
             note = "the kernel is fp32 FFMA, not a tensor-core kernel"
         dom = kernels[dom_name]
         step_ms = sec / args.steps * 1e3
-        roof = {"kernel": dom_kernel, "bound": "fp32",
-                "achieved": dom["achieved"], "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": dom["frac"],
-                "peak_source": "computed FFMA peak 148 SM x 128 lanes x 2 x 1.965 GHz; %s (bf16 tensor peak %s: %.0f "
-                               "TFLOP/s)" % (note, peaks_src, bf16_peak),
-                "share_of_step": dom["ms"] / step_ms, "traffic": None,
-                "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
+        if dom["bound"] == "tensor":
+            roof = {"kernel": dom_kernel, "bound": "tensor", "achieved": dom["achieved"], "peak": dom["peak"],
+                    "unit": "TFLOP/s", "frac": dom["frac"],
+                    "peak_source": "measured bf16 dense peak (%s: %.0f TFLOP/s) / 2 (tf32) / 3 (three MMAs per product: "
+                                   "3xTF32 split for fp32-class accuracy); achieved = algorithmic FLOPs (2 per MAC of "
+                                   "the backward pass) per second; %s" % (peaks_src, bf16_peak, note),
+                    "frac_of_fp32_ffma_peak": dom["achieved"] / FP32_PEAK_TFLOPS,
+                    "share_of_step": dom["ms"] / step_ms, "traffic": None,
+                    "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
+        else:
+            roof = {"kernel": dom_kernel, "bound": "fp32",
+                    "achieved": dom["achieved"], "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": dom["frac"],
+                    "peak_source": "computed FFMA peak 148 SM x 128 lanes x 2 x 1.965 GHz; %s (bf16 tensor peak %s: %.0f "
+                                   "TFLOP/s)" % (note, peaks_src, bf16_peak),
+                    "share_of_step": dom["ms"] / step_ms, "traffic": None,
+                    "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
         total_flops = (FLOP_ACTOR_FWD * (1 + 3 + 1) + FLOP_CRITIC_FWD * (3 + (HORIZON + 1) / HORIZON)) * steps_per_it
         cb_v, cb_sec, cb_sample = (cpu_baseline() if world == 1 else (None, None, None))
         line = {"metric": "env-steps/sec (rollout+update)", "value": value, "unit": "env-steps/s", "n_gpus": world,
@@ -367,7 +393,8 @@ def run_ours(args, rank, local_rank, world):
                 "config": {"workload": WORKLOAD, "envs_per_gpu": N_ENVS, "horizon": HORIZON, "mode": args.mode,
                            "l2": "flushed between timed steps (256 MiB write, then 256 MiB read to leave clean lines)", "weights": "glorot-uniform, seed 12321",
                            "rng": "device Philox4x32-10", "cuda_graphs": not args.no_graph,
-                           "forward_engine": "tcgen05 3xTF32" if tr.tc else "fp32 FFMA", "backward_engine": ("tcgen05 3xTF32 (dX) + fp32 FFMA (dW)" if getattr(tr, "tc_bwd", False)
+                           "forward_engine": "tcgen05 3xTF32" if tr.tc else "fp32 FFMA", "backward_engine": ("tcgen05 3xTF32" if getattr(tr, "tc_bwd", False) and tr.N % 4 == 0
+                                               else "tcgen05 3xTF32 (dX) + fp32 FFMA (dW)" if getattr(tr, "tc_bwd", False)
                                                else "fp32 FFMA"),
                            "parallelism": "dp%d (envs sharded by rank, NCCL all-reduce of the flat gradient)" % world},
                 "e2e": {"value": world * steps_per_it * args.steps / e_sec, "unit": "env-steps/s",

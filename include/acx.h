@@ -265,7 +265,12 @@ int acx_loss_backward_cat_cached(const float* actor, const float* critic, int ob
  * accumulation, ~1e-6 relative per product) while the weight-gradient products run on the CUDA cores of the same
  * CTA.  *_packed_bwd: acx_tc_packed_bwd_floats() floats each, 16-byte aligned, filled by
  * acx_tc_pack_weights_bwd() and re-filled whenever the parameters change.  The activation cache is required.
- * Gradients agree with acx_loss_backward_*_cached to 3xTF32 accuracy, not bit for bit. */
+ * Gradients agree with acx_loss_backward_*_cached to 3xTF32 accuracy, not bit for bit.
+ * Workspace: with at least acx_loss_backward_workspace_bytes() the weight-gradient products run as fp32 FFMA
+ * inside the same kernel; with at least acx_loss_backward_tc_workspace_bytes(rows, n) (room for dPre3, dPre2 and the
+ * layer-1 activations of one network, [rows][feature][n] fp32) and n % 4 == 0 they run on the tensor cores too, in a
+ * second kernel per network (acx_wgrad_kernel: TMA tensor loads, 128-byte swizzle, accumulators in tensor memory). */
+size_t acx_loss_backward_tc_workspace_bytes(int ob_dim, int num_ac, int cont, int rows, int n);
 size_t acx_tc_packed_bwd_floats(int net, int ob_dim, int num_ac, int cont);
 int acx_tc_pack_weights_bwd(int net, const float* params, int ob_dim, int num_ac, int cont, float* packed,
                             void* stream);

@@ -36,7 +36,7 @@ def check_grads(got, want, lay, tol, want32, batch):
 class Case:
     """Device buffers for one batch; the activation caches are filled by the FFMA *_cached forwards."""
 
-    def __init__(self, lib, dev, cont, ob, num_ac, rows, n, seed, beta=0.7, gam=0.03):
+    def __init__(self, lib, dev, cont, ob, num_ac, rows, n, seed, beta=0.7, gam=0.03, split=True):
         self.lib, self.dev, self.cont, self.ob, self.num_ac, self.rows, self.n = lib, dev, cont, ob, num_ac, rows, n
         self.actor, self.critic = random_weights(ob, num_ac, cont, seed, bias_scale=0.2)
         self.lay, self.clay = P.actor_layout(ob, num_ac, cont), P.critic_layout(ob)
@@ -74,7 +74,10 @@ class Case:
         self.acs = np.ascontiguousarray(acs.transpose(0, 2, 1)) if cont else acs       # [rows, n, d] / [rows, n]
         self.adv_d, self.lp_d, self.tg_d = (dev_t(x, dev) for x in (self.adv, self.lp_old, self.targets))
         self.opt = make_opt(lib, dev, beta=beta, gamma_ent=gam)
-        self.nbytes = lib.load().acx_loss_backward_workspace_bytes(ob, num_ac, int(cont))
+        # split: room for dPre3 / dPre2 / X1 -> weight gradients by acx_wgrad_kernel (when n % 4 == 0);
+        # otherwise they are FFMA inside the one training kernel
+        self.nbytes = (lib.load().acx_loss_backward_tc_workspace_bytes(ob, num_ac, int(cont), rows, n) if split
+                       else lib.load().acx_loss_backward_workspace_bytes(ob, num_ac, int(cont)))
         self.ws = torch.empty(self.nbytes, device=dev, dtype=torch.uint8)
         self.pa = torch.zeros(lib.load().acx_tc_packed_bwd_floats(0, ob, num_ac, int(cont)), device=dev)
         self.pc = torch.zeros(lib.load().acx_tc_packed_bwd_floats(1, ob, 1, 0), device=dev)
@@ -108,9 +111,10 @@ class Case:
         return wa, wc
 
 
-@pytest.mark.parametrize("rows,n", [(1, 128), (1, 50), (2, 333), (20, 512), (3, 20000)])
-def test_gauss_tc_backward_matches_oracle(lib, dev, rows, n):
-    k = Case(lib, dev, True, 3, 1, rows, n, 21)
+@pytest.mark.parametrize("split", [False, True])
+@pytest.mark.parametrize("rows,n", [(1, 128), (1, 50), (2, 333), (2, 332), (20, 512), (3, 20000), (1, 4)])
+def test_gauss_tc_backward_matches_oracle(lib, dev, rows, n, split):
+    k = Case(lib, dev, True, 3, 1, rows, n, 21, split=split)
     ga, gc, stats = k.run("tc")
     wa, wc = k.oracle(np.float64)
     wa32, wc32 = k.oracle(np.float32)
@@ -122,10 +126,11 @@ def test_gauss_tc_backward_matches_oracle(lib, dev, rows, n):
     np.testing.assert_allclose(stats[6], wa["ent"], rtol=2 * TOL)
 
 
+@pytest.mark.parametrize("split", [False, True])
 @pytest.mark.parametrize("ob,n_act", [(4, 2), (6, 3)])
 @pytest.mark.parametrize("rows,n", [(1, 100), (5, 1000)])
-def test_cat_tc_backward_matches_oracle(lib, dev, ob, n_act, rows, n):
-    k = Case(lib, dev, False, ob, n_act, rows, n, 31, beta=1.0, gam=0.01)
+def test_cat_tc_backward_matches_oracle(lib, dev, ob, n_act, rows, n, split):
+    k = Case(lib, dev, False, ob, n_act, rows, n, 31, beta=1.0, gam=0.01, split=split)
     ga, gc, stats = k.run("tc")
     wa, wc = k.oracle(np.float64)
     wa32, wc32 = k.oracle(np.float32)
@@ -135,9 +140,10 @@ def test_cat_tc_backward_matches_oracle(lib, dev, ob, n_act, rows, n):
     np.testing.assert_allclose(stats[4], wc["loss"], rtol=2 * TOL)
 
 
+@pytest.mark.parametrize("split", [False, True])
 @pytest.mark.parametrize("cont,ob,num_ac", [(True, 3, 1), (False, 4, 2)])
-def test_tc_backward_agrees_with_the_ffma_kernel(lib, dev, cont, ob, num_ac):
-    k = Case(lib, dev, cont, ob, num_ac, 20, 4096, 5)
+def test_tc_backward_agrees_with_the_ffma_kernel(lib, dev, cont, ob, num_ac, split):
+    k = Case(lib, dev, cont, ob, num_ac, 20, 4096, 5, split=split)
     ta, tcg, ts = k.run("tc")
     fa, fc, fs = k.run("ffma")
     for got, want, lay in ((ta, fa, k.lay), (tcg, fc, k.clay)):
@@ -153,8 +159,9 @@ def test_tc_backward_agrees_with_the_ffma_kernel(lib, dev, cont, ob, num_ac):
     np.testing.assert_array_equal(ts, fs)
 
 
-def test_tc_backward_is_deterministic_and_takes_either_net(lib, dev):
-    k = Case(lib, dev, True, 3, 1, 20, 2048, 8)
+@pytest.mark.parametrize("split", [False, True])
+def test_tc_backward_is_deterministic_and_takes_either_net(lib, dev, split):
+    k = Case(lib, dev, True, 3, 1, 20, 2048, 8, split=split)
     r1, r2 = k.run("tc"), k.run("tc")
     np.testing.assert_array_equal(r1[0], r2[0])
     np.testing.assert_array_equal(r1[1], r2[1])
