@@ -1,0 +1,332 @@
+// K4, chain part of the two-kernel tensor-core form (A3C/policies.py:74-85,152-158 on the cached activations):
+// per 128-sample tile the head (loss terms, seed gradients, head-layer gradients), then back-propagation
+//     dPre3 = (Wh dHead) * act'(X3)          dPre2 = (dPre3 W3^T) * act'(X2)          dPre1 = (dPre2 W2^T) * act'(X1)
+// with both products on tcgen05 (3xTF32, A operand = dPre in tensor memory, B = packed weight chunks through a bulk-TMA
+// ring, accumulators in tensor memory) and the first-layer gradients dW1 / db1.  dPre3 and dPre2 leave as coalesced
+// stores ([rows][feature][n]) for acx_wgrad_kernel, which forms dW3 / dW2 / db3 / db2 from them.
+//
+// One persistent CTA per SM; warps 0-7 workers (thread = sample x half of the feature range = TMEM lane), warp 8 issuer.
+//  * X3 tiles arrive by bulk-TMA one tile ahead (two staging buffers); after dPre3 the tile's buffer becomes the
+//    transposition staging of the dPre1 blocks (thread = sample writes columns, layer1_grad reads rows).
+//  * X2 is needed only as act'(X2): each thread reads its 64 values straight from the cache (coalesced) into two
+//    32-bit masks at the start of the tile, long before the product they gate is done.
+//  * act'(X1) is recomputed per element from the thread's own observation (ob_dim FMAs, layer1_block's arithmetic).
+#include "acx_head.cuh"
+#include "acx_tc_bwd.cuh"
+#include "acx_wgrad.cuh"
+
+using namespace acxmlp;
+using namespace acxumma;
+using namespace acxtcbwd;
+
+namespace {
+
+struct TcSmem {
+  float S[2][128 * MS];
+  float slot[TT_NSLOT][TT_SLOT_FLOATS];
+  float obs[MAX_OB * MT];
+  float W1[MAX_OB * 256];
+  float b1[256];
+  float Wh[128 * MAX_OUT];
+  float bh[MAX_OUT];
+  float log_std[MAX_OUT];
+  float dHead[MAX_OUT * MT];
+  double red[8][4];
+  unsigned long long full[TT_NSLOT], empty[TT_NSLOT], a_ready, stage_done[3], bar_act[2];
+  unsigned int tmem_base;
+};
+
+template <int H1, int H3, bool LRELU, int HEAD>
+__global__ void __launch_bounds__(TT_NT, 1)
+acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* __restrict__ d3_out,
+                        float* __restrict__ d2_out) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  TcSmem& sm = *reinterpret_cast<TcSmem*>(smem_raw);
+  constexpr int NB = H1 / 128, N3C = H3 / 16;
+  const AcxNetLayout L = A.L;
+  const int ob = L.ob, nout = L.nout, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const float* __restrict__ P = A.params;
+
+  for (int i = tid; i < ob * H1; i += TT_NT) sm.W1[i] = P[L.W1 + i];
+  for (int i = tid; i < H1; i += TT_NT) sm.b1[i] = P[L.b1 + i];
+  for (int i = tid; i < H3 * nout; i += TT_NT) sm.Wh[i] = P[L.Wh + i];
+  if (tid < nout) {
+    sm.bh[tid] = P[L.bh + tid];
+    if (HEAD == HEAD_GAUSS) sm.log_std[tid] = P[L.log_std + tid];
+  }
+  const int tpr = (A.n + MT - 1) / MT;
+  const int ntiles = A.rows * tpr;
+  const unsigned int mine = ((int)blockIdx.x < ntiles) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+  if (warp == 8) tmem_alloc(&sm.tmem_base, 512);
+  if (tid == 0) {
+    for (int i = 0; i < TT_NSLOT; ++i) {
+      acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.full[i]), 1);
+      acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.empty[i]), 1);
+    }
+    acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.a_ready), TT_WORK);
+    for (int i = 0; i < 3; ++i) acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.stage_done[i]), 1);
+    for (int i = 0; i < 2; ++i) acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.bar_act[i]), 1);
+    acx_mbar_fence_init();
+  }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == 8) {
+    // ================================================================ issuer
+    if (lane == 0) {
+      TtPipe<TcSmem> pipe;
+      pipe.sm = &sm; pipe.packed = packed; pipe.g = 0; pipe.issued = 0;
+      pipe.chunks_per_tile = N3C + 8 * NB;
+      pipe.total = mine * pipe.chunks_per_tile;
+      pipe.prefetch();
+      unsigned int ready = 0;
+      for (unsigned int t = 0; t < mine; ++t) {
+        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready), ready & 1u); ++ready;       // dPre3 is the A operand
+        fence_after_sync();
+        for (int cc = 0; cc < N3C; ++cc) pipe.mma_chunk(tmem, cc * 16, tmem + TT_D0, cc == 0);
+        commit(reinterpret_cast<uint64_t*>(&sm.stage_done[0]));
+        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready), ready & 1u); ++ready;       // dPre2 is the A operand
+        fence_after_sync();
+        for (int h = 0; h < NB; ++h) {
+          for (int cc = 0; cc < 8; ++cc) pipe.mma_chunk(tmem, cc * 16, tmem + (h == 0 ? TT_D0 : TT_D1), cc == 0);
+          commit(reinterpret_cast<uint64_t*>(&sm.stage_done[1 + h]));
+        }
+      }
+    }
+  } else {
+    // ================================================================ workers
+    const int s = (warp & 3) * 32 + lane;          // sample = TMEM lane
+    const int half = warp >> 2;
+    const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    HeadScalars hs;
+    hs.beta = hs.gam = 0.f; hs.adv_mean = 0.f; hs.adv_inv = 1.f; hs.step0 = 0u;
+    hs.invB = 1.0 / ((double)A.rows * (double)A.n);
+    if (HEAD != HEAD_VALUE) {
+      hs.beta = A.opt[ACX_OPT_BETA_KL]; hs.gam = A.opt[ACX_OPT_GAMMA_ENT];
+      if (A.adv_stats) { hs.adv_mean = A.adv_stats[0]; hs.adv_inv = A.adv_stats[1]; }
+    }
+    double lsum[4] = {0.0, 0.0, 0.0, 0.0};
+    float dls[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
+    float* __restrict__ scr = A.scratch + (size_t)blockIdx.x * L.size;
+    bool first = true;
+    unsigned int act_phase[2] = {0u, 0u}, tiles_done = 0;
+    if (tid < L.size - L.bh) scr[L.bh + tid] = 0.f;
+    const bool vec_ok = (A.n & 3) == 0;
+    const size_t ld = (size_t)A.n;
+    constexpr float SLOPE = LRELU ? 0.2f : 0.0f;
+
+    // X3 tile -> staging buffer `buf` by bulk-TMA (full, 16-byte aligned tiles only)
+    auto tile_is_bulk = [&](int tile) { return vec_ok && (A.n - (tile % tpr) * MT) >= MT; };
+    auto issue_x3 = [&](int tile, int buf) {
+      const int row = tile / tpr, n0 = (tile % tpr) * MT;
+      const float* g3 = A.x3_in + ((size_t)row * H3) * ld + n0;
+      uint64_t* bar = reinterpret_cast<uint64_t*>(&sm.bar_act[buf]);
+      if (tid == 0) acx_mbar_expect_tx(bar, (uint32_t)(H3 * MT * 4));
+      if (tid < H3) acx_bulk_g2s(sm.S[buf] + tid * MS, g3 + (size_t)tid * ld, MT * 4, bar);
+    };
+    if ((int)blockIdx.x < ntiles && tile_is_bulk(blockIdx.x)) issue_x3(blockIdx.x, 0);
+
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tiles_done) {
+      const int row = tile / tpr, n0 = (tile % tpr) * MT;
+      const int valid = min(MT, A.n - n0);
+      const unsigned int par = tiles_done & 1u;
+      const int buf = tiles_done & 1;
+      float* __restrict__ S = sm.S[buf];
+      const bool live = s < valid;
+      const size_t col = (size_t)n0 + s;
+      // the other buffer is idle since the end of the previous tile: fetch the next tile's X3 into it
+      {
+        const int next = tile + gridDim.x;
+        if (next < ntiles && tile_is_bulk(next)) issue_x3(next, buf ^ 1);
+      }
+      // this thread's observation (registers; also the shared copy layer1_grad reads) and its act'(X2) bits
+      float ob_r[MAX_OB];
+#pragma unroll
+      for (int i = 0; i < MAX_OB; ++i) {
+        ob_r[i] = (i < ob && live) ? __ldg(A.obs + ((size_t)row * ob + i) * ld + col) : 0.f;
+        if (i < ob && half == 0) sm.obs[i * MT + s] = ob_r[i];
+      }
+      unsigned int m2[2] = {0u, 0u};
+      {
+        const float* g2 = A.x2_in + ((size_t)row * H2 + half * 64) * ld + col;
+#pragma unroll
+        for (int q = 0; q < 2; ++q)
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const float x = live ? __ldg(g2 + (size_t)(q * 32 + e) * ld) : 0.f;
+            m2[q] |= (x > 0.f ? 1u : 0u) << e;
+          }
+      }
+      if (tile_is_bulk(tile)) {
+        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[buf]), act_phase[buf] & 1u);
+        ++act_phase[buf];
+      } else {
+        load_tile(S, A.x3_in + ((size_t)row * H3) * ld + n0, ld, H3, valid, vec_ok);
+      }
+      work_sync();
+
+      // ---------------------------------------------- head
+      if (tid < MT) {
+        float pre[MAX_OUT];
+        head_pre<H3>(sm, S, tid, nout, pre);
+        float dh[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
+        head_apply<HEAD, MODE_TRAIN>(A, sm.log_std, nout, pre, live, row, col, hs, lsum, dls, dh);
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a)
+          if (a < nout) sm.dHead[a * MT + tid] = dh[a];
+      }
+      work_sync();
+      {   // head weights and bias
+        if (tid < H3) {
+          for (int a = 0; a < nout; ++a) {
+            float acc = 0.f;
+            for (int m4 = 0; m4 < MT / 4; ++m4) {
+              const float4 x = *reinterpret_cast<const float4*>(&S[tid * MS + 4 * m4]);
+              const float4 d = *reinterpret_cast<const float4*>(&sm.dHead[a * MT + 4 * m4]);
+              acc = fmaf(x.x, d.x, acc); acc = fmaf(x.y, d.y, acc); acc = fmaf(x.z, d.z, acc); acc = fmaf(x.w, d.w, acc);
+            }
+            float* p = scr + L.Wh + tid * nout + a;
+            *p = first ? acc : *p + acc;
+          }
+        } else if (tid >= 128 && tid < 128 + nout) {
+          const int a = tid - 128;
+          float acc = 0.f;
+          for (int m = 0; m < MT; ++m) acc += sm.dHead[a * MT + m];
+          float* p = scr + L.bh + a;
+          *p = first ? acc : *p + acc;
+        }
+      }
+      // ---------------------------------------------- dPre3: A operand + HBM stream (no barrier needed: reads only)
+      {
+        float dh[MAX_OUT];
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a) dh[a] = a < nout ? sm.dHead[a * MT + s] : 0.f;
+#pragma unroll 1
+        for (int gq = 0; gq < H3 / 64; ++gq) {
+          const int j0 = half * (H3 / 2) + gq * 32;
+          float v[32];
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] = S[(j0 + e) * MS + s];
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            float acc = 0.f;
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) acc = fmaf(sm.Wh[(j0 + e) * nout + a], dh[a], acc);
+            v[e] = acc * act_grad<LRELU>(v[e]);
+          }
+          a_store32_tt(tl, j0, v);
+          if (live) {
+            float* g = d3_out + ((size_t)row * H3 + j0) * ld + col;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) g[(size_t)e * ld] = v[e];
+          }
+        }
+      }
+      tmem_wait_st();
+      fence_before_sync();
+      mbar_arrive1(&sm.a_ready);
+      work_sync();                                  // every read of S as X3 is done: it may take the dPre1 blocks
+      // ---------------------------------------------- dPre2 = dX2 * act'(X2): next A operand + HBM stream
+      acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[0]), par);
+      fence_after_sync();
+#pragma unroll 1
+      for (int gq = 0; gq < 2; ++gq) {
+        float v[32];
+        const int k0 = half * 64 + gq * 32;
+        tmem_ld32(tl + TT_D0 + (uint32_t)k0, v);
+        const unsigned int bits = m2[gq];
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] *= ((bits >> e) & 1u) ? 1.0f : SLOPE;
+        a_store32_tt(tl, k0, v);
+        if (live) {
+          float* g = d2_out + ((size_t)row * H2 + k0) * ld + col;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) g[(size_t)e * ld] = v[e];
+        }
+      }
+      tmem_wait_st();
+      fence_before_sync();
+      mbar_arrive1(&sm.a_ready);
+      // ---------------------------------------------- layer 1: dPre1 = dX1 * act'(X1) per 128-row block, dW1, db1
+      for (int h = 0; h < NB; ++h) {
+        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[1 + h]), par);
+        fence_after_sync();
+#pragma unroll 1
+        for (int gq = 0; gq < 2; ++gq) {
+          float v[32];
+          const int k0 = half * 64 + gq * 32;
+          tmem_ld32(tl + (h == 0 ? TT_D0 : TT_D1) + (uint32_t)k0, v);
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int k = h * 128 + k0 + e;
+            float pre = 0.f;
+#pragma unroll
+            for (int i = 0; i < MAX_OB; ++i)
+              if (i < ob) pre = fmaf(ob_r[i], sm.W1[i * H1 + k], pre);
+            const float x1 = act_fn<LRELU>(__fadd_rn(pre, sm.b1[k]));
+            v[e] *= act_grad<LRELU>(x1);
+          }
+#pragma unroll
+          for (int e = 0; e < 32; ++e) S[(k0 + e) * MS + s] = v[e];
+        }
+        fence_before_sync();
+        work_sync();
+        layer1_grad<H1>(sm, h, ob, S, scr + L.W1, scr + L.b1, first);
+        fence_proxy_async();                        // S is next written by the async proxy (X3 prefetch)
+        work_sync();
+      }
+      first = false;
+    }
+
+    // ---------------------------------------------------- per-CTA scalar sums (head threads = warps 0..3)
+    work_sync();
+    double v4[4] = {lsum[0], lsum[1], lsum[2], 0.0};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) v4[q] = acx_warp_sum_d(v4[q]);
+    float dl[MAX_OUT];
+#pragma unroll
+    for (int d = 0; d < MAX_OUT; ++d) dl[d] = acx_warp_sum(dls[d]);
+    if (lane == 0 && warp < 4) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) sm.red[warp][q] = v4[q];
+#pragma unroll
+      for (int d = 0; d < MAX_OUT; ++d) sm.dHead[warp * MAX_OUT + d] = dl[d];
+    }
+    work_sync();
+    if (tid == 0) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        A.loss_partial[(size_t)blockIdx.x * 4 + q] = (sm.red[0][q] + sm.red[1][q]) + (sm.red[2][q] + sm.red[3][q]);
+      if (HEAD == HEAD_GAUSS)
+        for (int d = 0; d < nout; ++d)
+          scr[L.log_std + d] = (sm.dHead[d] + sm.dHead[MAX_OUT + d]) + (sm.dHead[2 * MAX_OUT + d] + sm.dHead[3 * MAX_OUT + d]);
+    }
+  }
+
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem, 512);
+}
+
+template <int H1, int H3, bool LRELU, int HEAD>
+int launch_chain(const Args& a, const float* packed, float* d3, float* d2, int grid, cudaStream_t st) {
+  auto kern = acx_mlp_tc_chain_kernel<H1, H3, LRELU, HEAD>;
+  ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024));
+  kern<<<grid, TT_NT, sizeof(TcSmem) + 1024, st>>>(a, packed, d3, d2);
+  ACX_LAUNCH_OK("acx_mlp_tc_chain_kernel");
+  return ACX_OK;
+}
+
+}  // namespace
+
+int acx_tc_chain_launch(const Args& a, const float* packed, float* d3, float* d2, int head, int grid, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  ACX_REQUIRE(a.x2_in && a.x3_in && packed && d3 && d2, "acx_tc_chain: null activation cache / packed weights / dPre buffer");
+  if (head == HEAD_GAUSS) return launch_chain<128, 64, true, HEAD_GAUSS>(a, packed, d3, d2, grid, st);
+  if (head == HEAD_CAT) return launch_chain<128, 64, true, HEAD_CAT>(a, packed, d3, d2, grid, st);
+  return launch_chain<256, 128, false, HEAD_VALUE>(a, packed, d3, d2, grid, st);
+}

@@ -15,25 +15,21 @@
 //            acx_tc_pack_weights_bwd, streamed through a 4 x 16 KB ring (bulk-TMA), accumulators in TMEM.
 // Gradients are accumulated in the per-CTA scratch rows and reduced in fixed order exactly as in acx_mlp.cu.
 //
-// SPLIT = true (the default path, n % 4 == 0): the two big weight-gradient products leave this kernel as well.  It
-// then only streams dPre3, dPre2 and the recomputed X1 to HBM ([rows][feature][n], bulk-TMA stores of the shared
-// tiles) and acx_wgrad_kernel (acx_wgrad.cu) forms  dW3 = X2 dPre3^T  and  dW2 = X1 dPre2^T  on the tensor cores
-// from those arrays, accumulating over the CTA's whole share of the batch in tensor memory.
+// This one-kernel form serves callers without room for the dPre streams (or with n % 4 != 0).  With the larger
+// workspace the entry points below run the two-kernel form instead: acx_mlp_tc_chain_kernel (acx_mlp_tc_chain.cu: the
+// chain only, dPre3 / dPre2 streamed to HBM) + acx_wgrad_kernel (acx_wgrad.cu: every weight-gradient product on the
+// tensor cores).
 #include "acx_mlp.cuh"
 #include "acx_head.cuh"
 #include "acx_umma.cuh"
 #include "acx_wgrad.cuh"
+#include "acx_tc_bwd.cuh"
 
 using namespace acxmlp;
 using namespace acxumma;
+using namespace acxtcbwd;
 
 namespace {
-
-constexpr int TT_WORK = 256;
-constexpr int TT_NT = TT_WORK + 32;
-constexpr int TT_SLOT_FLOATS = 4096;
-constexpr int TT_NSLOT = 4;
-constexpr uint32_t TT_A_HI = 0, TT_A_LO = 128, TT_D0 = 256, TT_D1 = 384;
 
 struct TtSmem {
   float X2[H2 * MS];
@@ -51,86 +47,8 @@ struct TtSmem {
   unsigned int tmem_base;
 };
 
-__device__ inline void work_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
-__device__ inline void mbar_arrive1(unsigned long long* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(acx_smem_u32(bar)) : "memory");
-}
-
-struct TtPipe {
-  TtSmem* sm;
-  const float* packed;
-  unsigned int g, issued, total;
-  int chunks_per_tile;
-  __device__ inline void prefetch() {
-    while (issued < total && issued < g + TT_NSLOT) {
-      const unsigned int q = issued % TT_NSLOT;
-      if (issued >= TT_NSLOT)
-        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm->empty[q]), ((issued / TT_NSLOT) - 1u) & 1u);
-      const float* src = packed + (size_t)(issued % (unsigned)chunks_per_tile) * TT_SLOT_FLOATS;
-      acx_mbar_expect_tx(reinterpret_cast<uint64_t*>(&sm->full[q]), TT_SLOT_FLOATS * 4);
-      acx_bulk_g2s(sm->slot[q], src, TT_SLOT_FLOATS * 4, reinterpret_cast<uint64_t*>(&sm->full[q]));
-      ++issued;
-    }
-  }
-  // 16 reduction rows (A columns k0..k0+15) x 128 outputs, accumulate into tmem_d
-  __device__ inline void mma_chunk(uint32_t tmem, int k0, uint32_t tmem_d, bool first) {
-    prefetch();
-    const unsigned int q = g % TT_NSLOT;
-    acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm->full[q]), (g / TT_NSLOT) & 1u);
-    fence_after_sync();
-    const float* b_hi = sm->slot[q];
-    const float* b_lo = b_hi + 128 * 16;
-    const uint32_t idesc = idesc_tf32(128, 128, false, false);
-#pragma unroll
-    for (int ks = 0; ks < 2; ++ks) {
-      const uint64_t bh = smem_desc(b_hi + ks * 64, 128, 512), bl = smem_desc(b_lo + ks * 64, 128, 512);
-      const uint32_t ah = tmem + TT_A_HI + (uint32_t)(k0 + ks * 8), al = tmem + TT_A_LO + (uint32_t)(k0 + ks * 8);
-      mma_tf32_ts(tmem_d, al, bh, idesc, !(first && ks == 0));
-      mma_tf32_ts(tmem_d, ah, bl, idesc, true);
-      mma_tf32_ts(tmem_d, ah, bh, idesc, true);
-    }
-    commit(reinterpret_cast<uint64_t*>(&sm->empty[q]));
-    ++g;
-  }
-};
-
-__device__ inline void a_store32_tt(uint32_t tmem_lane, int j0, const float (&v)[32]) {
-  float hi[32], lo[32];
-#pragma unroll
-  for (int i = 0; i < 32; ++i) split_tf32(v[i], hi[i], lo[i]);
-  tmem_st32(tmem_lane + TT_A_HI + (uint32_t)j0, hi);
-  tmem_st32(tmem_lane + TT_A_LO + (uint32_t)j0, lo);
-}
-
-// smem rows -> global rows (row r of `src`, MT floats, to dst + r * gld); full tiles go out as bulk-TMA stores
-__device__ inline void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ inline void store_rows(const float* __restrict__ src, float* __restrict__ dst, size_t gld, int nrows,
-                                  int valid, bool bulk) {
-  const int tid = threadIdx.x;
-  if (bulk) {
-    if (tid < nrows) {
-      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + (size_t)tid * gld),
-                   "r"(acx_smem_u32(src + tid * MS)), "r"(MT * 4)
-                   : "memory");
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    }
-  } else {
-    for (int idx = tid; idx < nrows * MT; idx += TT_WORK) {
-      const int r = idx >> 7, m = idx & 127;
-      if (m < valid) dst[(size_t)r * gld + m] = src[r * MS + m];
-    }
-  }
-}
-
-struct SplitOut {            // SPLIT: where dPre3 / dPre2 / X1 go ([rows][feature][n])
-  float* d3;
-  float* d2;
-  float* x1;
-};
-
-template <int H1, int H3, bool LRELU, int HEAD, bool SPLIT>
-__global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A, const float* __restrict__ packed,
-                                                                    const SplitOut so) {
+template <int H1, int H3, bool LRELU, int HEAD>
+__global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A, const float* __restrict__ packed) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   TtSmem& sm = *reinterpret_cast<TtSmem*>(smem_raw);
   constexpr int TJ3 = H3 / 16, NB = H1 / 128, N3C = H3 / 16;
@@ -168,7 +86,7 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
   if (warp == 8) {
     // ================================================================ issuer
     if (lane == 0) {
-      TtPipe pipe;
+      TtPipe<TtSmem> pipe;
       pipe.sm = &sm; pipe.packed = packed; pipe.g = 0; pipe.issued = 0;
       pipe.chunks_per_tile = N3C + 8 * NB;
       pipe.total = mine * pipe.chunks_per_tile;
@@ -214,7 +132,6 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
       const int valid = min(MT, A.n - n0);
       const unsigned int par = tiles_done & 1u;
       const bool bulk = vec_ok && valid == MT;       // full, 16-byte aligned rows: bulk-TMA loads and stores
-      if (SPLIT) bulk_wait_read();                   // the previous tile's row stores have left shared memory
       work_sync();                                   // previous tile is done with every shared buffer
       for (int idx = tid; idx < ob * MT; idx += TT_WORK) {
         const int i = idx / MT, m = idx % MT;
@@ -291,11 +208,9 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
-      if (SPLIT) fence_proxy_async();              // dPre3 in shared memory -> visible to the bulk stores
       work_sync();
-      // ---------------------------------------------- dW3, db3 while dX2 runs on the tensor cores
-      if (SPLIT) store_rows(sm.X3, so.d3 + ((size_t)row * H3) * A.n + n0, (size_t)A.n, H3, valid, bulk);
-      else g_stage<8, TJ3>(sm.X2, sm.X3, scr + L.W3, H3, first, c);
+      // ---------------------------------------------- dW3, db3 on the CUDA cores while dX2 runs on the tensor cores
+      g_stage<8, TJ3>(sm.X2, sm.X3, scr + L.W3, H3, first, c);
       bias_grad(sm.X3, H3, scr + L.b3, first);
       work_sync();
       // ---------------------------------------------- dPre2 = dX2 * act'(X2): in place + next A operand
@@ -320,21 +235,13 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
-      if (SPLIT) { fence_proxy_async(); bulk_wait_read(); }      // (dPre3 has left X3: layer1_block may overwrite it)
       work_sync();
-      if (SPLIT) store_rows(sm.X2, so.d2 + ((size_t)row * H2) * A.n + n0, (size_t)A.n, H2, valid, bulk);
       bias_grad(sm.X2, H2, scr + L.b2, first);
       // ---------------------------------------------- layers 1/2: dW2 on the CUDA cores, dX1 on the tensor cores
       for (int h = 0; h < NB; ++h) {
         layer1_block<H1, LRELU>(sm, h, ob, sm.X3);
-        if (SPLIT) fence_proxy_async();
         work_sync();
-        if (SPLIT) {
-          store_rows(sm.X3, so.x1 + ((size_t)row * H1 + h * 128) * A.n + n0, (size_t)A.n, 128, valid, bulk);
-          bulk_wait_read();                          // X1 block has left X3 before dPre1 overwrites it
-        } else {
-          g_stage<8, 8>(sm.X3, sm.X2, scr + L.W2 + (size_t)h * 128 * H2, H2, first, c);
-        }
+        g_stage<8, 8>(sm.X3, sm.X2, scr + L.W2 + (size_t)h * 128 * H2, H2, first, c);
         work_sync();
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[1 + h]), par);
         fence_after_sync();
@@ -435,27 +342,26 @@ __global__ void __launch_bounds__(256) acx_grad_reduce_tc_kernel(const float* __
   }
 }
 
-template <int H1, int H3, bool LRELU, int HEAD, bool SPLIT>
-int launch_tt1(const Args& a, const float* packed, const SplitOut& so, int grid, cudaStream_t st) {
-  auto kern = acx_mlp_tc_train_kernel<H1, H3, LRELU, HEAD, SPLIT>;
-  ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TtSmem) + 1024));
-  kern<<<grid, TT_NT, sizeof(TtSmem) + 1024, st>>>(a, packed, so);
-  ACX_LAUNCH_OK("acx_mlp_tc_train_kernel");
-  return ACX_OK;
-}
-
 // split == nullptr: everything in one kernel (weight gradients FFMA); else chain kernel + acx_wgrad_kernel
 template <int H1, int H3, bool LRELU, int HEAD>
 int launch_tt(const Args& a, const float* packed, float* split, int grid, cudaStream_t st) {
-  SplitOut so = {nullptr, nullptr, nullptr};
-  if (split == nullptr) return launch_tt1<H1, H3, LRELU, HEAD, false>(a, packed, so, grid, st);
+  if (split == nullptr) {
+    auto kern = acx_mlp_tc_train_kernel<H1, H3, LRELU, HEAD>;
+    ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TtSmem) + 1024));
+    kern<<<grid, TT_NT, sizeof(TtSmem) + 1024, st>>>(a, packed);
+    ACX_LAUNCH_OK("acx_mlp_tc_train_kernel");
+    return ACX_OK;
+  }
   const size_t bn = (size_t)a.rows * (size_t)a.n;
-  so.d3 = split; so.d2 = so.d3 + bn * H3; so.x1 = so.d2 + bn * H2;
-  int rc = launch_tt1<H1, H3, LRELU, HEAD, true>(a, packed, so, grid, st);
+  float* d3 = split;
+  float* d2 = d3 + bn * H3;
+  int rc = acx_tc_chain_launch(a, packed, d3, d2, HEAD, grid, st);
   if (rc) return rc;
   AcxWgradArgs w;
-  w.x2 = a.x2_in; w.d3 = so.d3; w.x1 = so.x1; w.d2 = so.d2; w.rows = a.rows; w.n = a.n; w.H1 = H1; w.H3 = H3;
-  w.scratch = a.scratch; w.scr_stride = a.L.size; w.offW3 = a.L.W3; w.offW2 = a.L.W2; w.grid = grid;
+  w.x2 = a.x2_in; w.d3 = d3; w.d2 = d2; w.obs = a.obs; w.params = a.params; w.ob = a.L.ob; w.offW1 = a.L.W1;
+  w.offb1 = a.L.b1; w.lrelu = LRELU ? 1 : 0; w.rows = a.rows; w.n = a.n; w.H1 = H1; w.H3 = H3;
+  w.scratch = a.scratch; w.scr_stride = a.L.size; w.offW3 = a.L.W3; w.offW2 = a.L.W2; w.offb3 = a.L.b3;
+  w.offb2 = a.L.b2; w.grid = grid;
   return acx_wgrad_launch(w, st);
 }
 
@@ -526,8 +432,7 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
 
 extern "C" size_t acx_loss_backward_tc_workspace_bytes(int ob_dim, int num_ac, int cont, int rows, int n) {
   const size_t base_bytes = (acx_loss_backward_workspace_bytes(ob_dim, num_ac, cont) + 255) & ~(size_t)255;
-  const size_t feat = (size_t)(ACX_C_H3 + H2 + ACX_C_H1) > (size_t)(ACX_A_H3 + H2 + ACX_A_H1)
-                          ? (size_t)(ACX_C_H3 + H2 + ACX_C_H1) : (size_t)(ACX_A_H3 + H2 + ACX_A_H1);
+  const size_t feat = (size_t)(ACX_C_H3 > ACX_A_H3 ? ACX_C_H3 : ACX_A_H3) + H2;      // dPre3 + dPre2 of one network
   return base_bytes + feat * (size_t)(rows > 0 ? rows : 0) * (size_t)(n > 0 ? n : 0) * sizeof(float);
 }
 

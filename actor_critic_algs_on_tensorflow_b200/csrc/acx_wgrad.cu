@@ -1,17 +1,21 @@
 // Weight-gradient products of K4 on the tensor cores (tcgen05, 3xTF32), one launch per network:
 //     dW3[k][j] = sum_s X2[k][s] * dPre3[j][s]          (A3C/policies.py:82,155: compute_gradients of the
-//     dW2[k][j] = sum_s X1[k][s] * dPre2[j][s]           third / second dense layer's kernel)
-// summed over the whole [rows x n] batch.  Operands are the [rows][feature][n] arrays acx_mlp_tc_train_kernel<SPLIT>
-// wrote (dPre3, dPre2, X1) and the activation cache (X2): the sample index is contiguous, i.e. both operands are
-// K-major as they lie in HBM.  Each persistent CTA owns the 128-sample tiles  blockIdx.x, +gridDim.x, ...  and keeps
+//     dW2[k][j] = sum_s X1[k][s] * dPre2[j][s]           third / second dense layer's kernel and bias)
+//     db3[j] = sum_s dPre3[j][s],   db2[j] = sum_s dPre2[j][s]
+// summed over the whole [rows x n] batch.  Operands are the [rows][feature][n] arrays the chain kernel wrote (dPre3,
+// dPre2) and the activation cache (X2): the sample index is contiguous, i.e. both operands are K-major as they lie
+// in HBM.  X1 = act(obs W1 + b1) is not read but recomputed (ob_dim <= 8 FMAs per element) straight into the swizzled
+// operand layout.  Each persistent CTA owns the 128-sample tiles  blockIdx.x, +gridDim.x, ...  and keeps
 // its partial dW3 / dW2 in tensor memory (fp32, 128 + H1 columns) for the whole kernel; at the end they go to the CTA's
 // scratch row, which acx_grad_reduce sums in fixed order (bit-reproducible run to run).
 //   warp 0     producer: TMA tensor loads of [features x 32 samples] boxes, 128-byte swizzle, NSTAGE-deep ring
 //   warp 1     issuer:   per box 4 K-steps x 3 kind::tf32 MMAs (lo*hi, hi*lo, hi*hi) per 128-row block
 //   warps 2-9  splitters: lo = rna(x - trunc(x)) of every landed word into the stage's second buffer (the MMA itself
-//              ignores the low 13 mantissa bits of the raw word, which therefore serves as hi); warps 2-5 also run
-//              the epilogue (tcgen05.ld -> scratch row).
-// HBM-bound: 4 bytes per operand element, every element read once.
+//              ignores the low 13 mantissa bits of the raw word, which therefore serves as hi); they also generate the
+//              X1 boxes, keep the bias-gradient sums of the dPre rows they pass over, and warps 2-5 run the epilogue
+//              (tcgen05.ld -> scratch row).
+// HBM-bound: 4 bytes per streamed operand element, every element read once.
+#include "acx_mlp.cuh"
 #include "acx_wgrad.cuh"
 #include "acx_tmap.cuh"
 #include "acx_umma.cuh"
@@ -24,27 +28,40 @@ constexpr int WG_THREADS = 320;
 constexpr int BOX = 32;                    // samples per box row (128 bytes)
 constexpr int BLK = 128 * BOX;             // floats of a 128-row box
 
+struct WgBars {
+  unsigned long long full[3], split[3], empty[3], done;
+  unsigned int tmem_base;
+  float W1[acxmlp::MAX_OB * 256];
+  float b1[256];
+};
+
 template <int H1> struct WgCfg {
   static constexpr int NB = H1 / 128;
   static constexpr int STAGE = (NB + 1) * BLK;              // floats: A blocks, then the B box
   static constexpr int NSTAGE = NB == 1 ? 3 : 2;
-  static constexpr size_t SMEM = (size_t)NSTAGE * STAGE * 2 * sizeof(float) + 1024 + 256;
-};
-
-struct WgBars {
-  unsigned long long full[3], split[3], empty[3], done;
-  unsigned int tmem_base;
+  static constexpr size_t SMEM = (size_t)NSTAGE * STAGE * 2 * sizeof(float) + 1024 + sizeof(WgBars);
 };
 
 __device__ inline void mbar_arrive(unsigned long long* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(acx_smem_u32(bar)) : "memory");
 }
 
-template <int H1, int H3>
+// float4 slot of (row r, 16-byte chunk c) inside a 128-row, 128-byte-swizzled box
+__device__ inline int sw128_f4(int r, int c) { return (r >> 3) * 64 + (r & 7) * 8 + (c ^ (r & 7)); }
+
+__device__ inline float4 lo_of(const float4 x) {
+  float4 y;
+  y.x = round_tf32(x.x - trunc_tf32(x.x)); y.y = round_tf32(x.y - trunc_tf32(x.y));
+  y.z = round_tf32(x.z - trunc_tf32(x.z)); y.w = round_tf32(x.w - trunc_tf32(x.w));
+  return y;
+}
+
+template <int H1, int H3, bool LRELU>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constant__ CUtensorMap mapD3,
-                 const __grid_constant__ CUtensorMap mapX1, const __grid_constant__ CUtensorMap mapD2, int rows, int n,
-                 float* __restrict__ scratch, int scr_stride, int offW3, int offW2) {
+                 const __grid_constant__ CUtensorMap mapD2, const float* __restrict__ obs,
+                 const float* __restrict__ params, int ob, int offW1, int offb1, int rows, int n,
+                 float* __restrict__ scratch, int scr_stride, int offW3, int offW2, int offb3, int offb2) {
   using Cfg = WgCfg<H1>;
   constexpr int NB = Cfg::NB, NSTAGE = Cfg::NSTAGE;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -57,6 +74,8 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
   const int ntiles = rows * tpr;
 
   if (warp == 1) tmem_alloc(&B.tmem_base, 512);
+  for (int i = tid; i < ob * H1; i += WG_THREADS) B.W1[i] = params[offW1 + i];
+  for (int i = tid; i < H1; i += WG_THREADS) B.b1[i] = params[offb1 + i];
   if (tid == 0) {
     for (int i = 0; i < NSTAGE; ++i) {
       acx_mbar_init(reinterpret_cast<uint64_t*>(&B.full[i]), 1);
@@ -77,8 +96,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
     if (lane == 0) {
       unsigned int it = 0;
       for (int phase = 0; phase < 2; ++phase) {
-        const int nblk = phase == 0 ? 1 : NB, brows = phase == 0 ? H3 : 128, arows = phase == 0 ? 128 : H1;
-        const CUtensorMap* mA = phase == 0 ? &mapX2 : &mapX1;
+        const int brows = phase == 0 ? H3 : 128;
         const CUtensorMap* mB = phase == 0 ? &mapD3 : &mapD2;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
           const int row = tile / tpr, n0 = (tile % tpr) * 128;
@@ -88,9 +106,9 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             if (it >= (unsigned)NSTAGE)
               acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.empty[slot]), ((it / NSTAGE) - 1u) & 1u);
             uint64_t* full = reinterpret_cast<uint64_t*>(&B.full[slot]);
-            acx_mbar_expect_tx(full, (uint32_t)((nblk * 128 + brows) * BOX * 4));
+            acx_mbar_expect_tx(full, (uint32_t)(((phase == 0 ? 128 : 0) + brows) * BOX * 4));
             float* dst = raw + (size_t)slot * Cfg::STAGE;
-            for (int b = 0; b < nblk; ++b) tma_load_2d(dst + b * BLK, mA, n0 + kk * BOX, row * arows + b * 128, full);
+            if (phase == 0) tma_load_2d(dst, &mapX2, n0 + kk * BOX, row * 128, full);      // phase 1: X1 is generated
             tma_load_2d(dst + NB * BLK, mB, n0 + kk * BOX, row * brows, full);
           }
         }
@@ -132,28 +150,77 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
     }
   } else {
     const int t = tid - 64;                       // 0..255
+    const int c4 = t & 7, r0 = t >> 3;            // this thread's 16-byte chunk and its rows r0 + 32 m of every box
     unsigned int it = 0;
     for (int phase = 0; phase < 2; ++phase) {
-      const int na4 = (phase == 0 ? 1 : NB) * (BLK / 4), nb4 = (phase == 0 ? H3 : 128) * (BOX / 4);
+      const int brows = phase == 0 ? H3 : 128;
+      float bacc[4] = {0.f, 0.f, 0.f, 0.f};       // bias-gradient partials of rows r0 + 32 m (chunk c4 of every box)
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int n0 = (tile % tpr) * 128;
+        const int row = tile / tpr, n0 = (tile % tpr) * 128;
         const int nsub = (min(128, n - n0) + BOX - 1) / BOX;
         for (int kk = 0; kk < nsub; ++kk, ++it) {
           const unsigned int slot = it % NSTAGE;
-          acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.full[slot]), (it / NSTAGE) & 1u);
-          const float4* r4 = reinterpret_cast<const float4*>(raw + (size_t)slot * Cfg::STAGE);
+          float4* r4 = reinterpret_cast<float4*>(raw + (size_t)slot * Cfg::STAGE);
           float4* l4 = reinterpret_cast<float4*>(lo + (size_t)slot * Cfg::STAGE);
-          for (int i = t; i < na4 + nb4; i += 256) {
-            const int idx = i < na4 ? i : NB * (BLK / 4) + (i - na4);
-            const float4 x = r4[idx];
-            float4 y;
-            y.x = round_tf32(x.x - trunc_tf32(x.x)); y.y = round_tf32(x.y - trunc_tf32(x.y));
-            y.z = round_tf32(x.z - trunc_tf32(x.z)); y.w = round_tf32(x.w - trunc_tf32(x.w));
-            l4[idx] = y;
+          float4 o[acxmlp::MAX_OB];
+          if (phase == 1) {                        // observations of this thread's 4 samples (0 beyond the batch)
+            const int col = n0 + kk * BOX + 4 * c4;
+#pragma unroll
+            for (int i = 0; i < acxmlp::MAX_OB; ++i)
+              o[i] = (i < ob && col < n) ? __ldg(reinterpret_cast<const float4*>(obs + ((size_t)row * ob + i) * n + col))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
           }
+          acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.full[slot]), (it / NSTAGE) & 1u);
+          if (phase == 0) {
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {          // A = X2 box: rows r0 + 32 m, stored chunk c4 (any bijection works)
+              const int idx = (r0 + 32 * m) * 8 + c4;
+              l4[idx] = lo_of(r4[idx]);
+            }
+          } else {
+            // A = X1 blocks, generated: X1[k][s] = act(sum_i obs[i][s] W1[i][k] + b1[k])  (layer1_block's arithmetic)
+#pragma unroll
+            for (int m = 0; m < H1 / 32; ++m) {
+              const int k = r0 + 32 * m;
+              float4 sacc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+              for (int i = 0; i < acxmlp::MAX_OB; ++i)
+                if (i < ob) {
+                  const float w = B.W1[i * H1 + k];
+                  sacc.x = fmaf(o[i].x, w, sacc.x); sacc.y = fmaf(o[i].y, w, sacc.y);
+                  sacc.z = fmaf(o[i].z, w, sacc.z); sacc.w = fmaf(o[i].w, w, sacc.w);
+                }
+              const float bk = B.b1[k];
+              float4 x;
+              x.x = acxmlp::act_fn<LRELU>(__fadd_rn(sacc.x, bk)); x.y = acxmlp::act_fn<LRELU>(__fadd_rn(sacc.y, bk));
+              x.z = acxmlp::act_fn<LRELU>(__fadd_rn(sacc.z, bk)); x.w = acxmlp::act_fn<LRELU>(__fadd_rn(sacc.w, bk));
+              const int idx = (k >> 7) * (BLK / 4) + sw128_f4(k & 127, c4);
+              r4[idx] = x;
+              l4[idx] = lo_of(x);
+            }
+          }
+          // B = dPre box: split, and add this thread's 4 samples of rows r0 + 32 m to the bias-gradient partials
+#pragma unroll
+          for (int m = 0; m < 4; ++m)
+            if (r0 + 32 * m < brows) {
+              const int idx = NB * (BLK / 4) + (r0 + 32 * m) * 8 + c4;
+              const float4 x = r4[idx];
+              l4[idx] = lo_of(x);
+              bacc[m] += (x.x + x.y) + (x.z + x.w);
+            }
           fence_proxy_async();
           mbar_arrive(&B.split[slot]);
         }
+      }
+      // the 8 threads of a row (consecutive lanes) fold their partials; fixed order -> reproducible
+      float* scr = scratch + (size_t)blockIdx.x * scr_stride + (phase == 0 ? offb3 : offb2);
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        float v = bacc[m];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        if (c4 == 0 && r0 + 32 * m < brows) scr[r0 + 32 * m] = v;
       }
     }
     if (warp < 6) {
@@ -184,19 +251,18 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
-template <int H1, int H3>
+template <int H1, int H3, bool LRELU>
 int launch_wgrad(const AcxWgradArgs& a, cudaStream_t st) {
-  CUtensorMap mX2, mD3, mX1, mD2;
+  CUtensorMap mX2, mD3, mD2;
   const uint64_t pitch = (uint64_t)a.n * 4;
   int rc = acx_tmap_2d(&mX2, a.x2, (uint64_t)a.n, (uint64_t)a.rows * 128, pitch, BOX, 128);
   if (!rc) rc = acx_tmap_2d(&mD3, a.d3, (uint64_t)a.n, (uint64_t)a.rows * H3, pitch, BOX, H3);
-  if (!rc) rc = acx_tmap_2d(&mX1, a.x1, (uint64_t)a.n, (uint64_t)a.rows * H1, pitch, BOX, 128);
   if (!rc) rc = acx_tmap_2d(&mD2, a.d2, (uint64_t)a.n, (uint64_t)a.rows * 128, pitch, BOX, 128);
   ACX_REQUIRE(rc == 0, "acx_wgrad: cuTensorMapEncodeTiled failed (%d) for rows=%d n=%d", rc, a.rows, a.n);
-  auto kern = acx_wgrad_kernel<H1, H3>;
+  auto kern = acx_wgrad_kernel<H1, H3, LRELU>;
   ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgCfg<H1>::SMEM));
-  kern<<<a.grid, WG_THREADS, WgCfg<H1>::SMEM, st>>>(mX2, mD3, mX1, mD2, a.rows, a.n, a.scratch, a.scr_stride, a.offW3,
-                                                    a.offW2);
+  kern<<<a.grid, WG_THREADS, WgCfg<H1>::SMEM, st>>>(mX2, mD3, mD2, a.obs, a.params, a.ob, a.offW1, a.offb1, a.rows, a.n,
+                                                    a.scratch, a.scr_stride, a.offW3, a.offW2, a.offb3, a.offb2);
   ACX_LAUNCH_OK("acx_wgrad_kernel");
   return ACX_OK;
 }
@@ -205,10 +271,11 @@ int launch_wgrad(const AcxWgradArgs& a, cudaStream_t st) {
 
 int acx_wgrad_launch(const AcxWgradArgs& a, void* stream) {
   ACX_REQUIRE((a.n & 3) == 0, "acx_wgrad: n must be a multiple of 4 (16-byte row pitch for the TMA tensor maps), got %d", a.n);
-  ACX_REQUIRE(acx_aligned16(a.x2) && acx_aligned16(a.d3) && acx_aligned16(a.x1) && acx_aligned16(a.d2) &&
+  ACX_REQUIRE(acx_aligned16(a.x2) && acx_aligned16(a.d3) && acx_aligned16(a.obs) && acx_aligned16(a.d2) &&
                   acx_aligned16(a.scratch), "acx_wgrad: operands must be 16-byte aligned");
-  if (a.H1 == 128 && a.H3 == 64) return launch_wgrad<128, 64>(a, (cudaStream_t)stream);
-  if (a.H1 == 256 && a.H3 == 128) return launch_wgrad<256, 128>(a, (cudaStream_t)stream);
+  ACX_REQUIRE(a.ob >= 1 && a.ob <= acxmlp::MAX_OB, "acx_wgrad: ob_dim %d outside [1,%d]", a.ob, acxmlp::MAX_OB);
+  if (a.H1 == 128 && a.H3 == 64 && a.lrelu) return launch_wgrad<128, 64, true>(a, (cudaStream_t)stream);
+  if (a.H1 == 256 && a.H3 == 128 && !a.lrelu) return launch_wgrad<256, 128, false>(a, (cudaStream_t)stream);
   ACX_REQUIRE(false, "acx_wgrad: unsupported layer widths H1=%d H3=%d", a.H1, a.H3);
   return ACX_OK;
 }
