@@ -394,11 +394,15 @@ template <int HH, class SM>
 __device__ inline void head_pre(const SM& sm, const float* __restrict__ Xh, int m, int nout, float (&pre)[MAX_OUT]) {
 #pragma unroll
   for (int a = 0; a < MAX_OUT; ++a) pre[a] = 0.f;
-  for (int k = 0; k < HH; ++k) {
-    const float x = Xh[k * MS + m];
+  for (int k0 = 0; k0 < HH; k0 += 8) {        // loads batched ahead of the k-ascending FMA chain
+    float x[8];
 #pragma unroll
-    for (int a = 0; a < MAX_OUT; ++a)
-      if (a < nout) pre[a] = fmaf(x, sm.Wh[k * nout + a], pre[a]);
+    for (int u = 0; u < 8; ++u) x[u] = Xh[(k0 + u) * MS + m];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+#pragma unroll
+      for (int a = 0; a < MAX_OUT; ++a)
+        if (a < nout) pre[a] = fmaf(x[u], sm.Wh[(k0 + u) * nout + a], pre[a]);
   }
 #pragma unroll
   for (int a = 0; a < MAX_OUT; ++a)

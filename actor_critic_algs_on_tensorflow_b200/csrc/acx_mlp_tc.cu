@@ -27,7 +27,7 @@ using namespace acxumma;
 namespace {
 
 constexpr int TC_EPI = 256;                      // epilogue threads (warps 0-7)
-constexpr int TC_NT = TC_EPI + 32;               // + issuer warp
+constexpr int TC_NT = TC_EPI + 64;               // + issuer warp (8) + producer warp (9)
 constexpr int TC_SLOT_FLOATS = 4096;             // 16 KB: hi + lo planes of one weight chunk
 constexpr int TC_NSLOT = 12;
 constexpr int TC_KC2 = 16;                       // layer-2 input rows per chunk (128 outputs)
@@ -59,25 +59,25 @@ __device__ inline void mbar_arrive(unsigned long long* bar) {
 struct TcPipe {
   TcSmem* sm;
   const float* packed;
-  unsigned int g, issued, total;
+  unsigned int g, total;
   int chunks_per_tile;
   bool resident;
 
-  __device__ inline void prefetch() {
-    const unsigned int limit = resident ? (unsigned)TC_NSLOT : g + TC_NSLOT;
-    while (issued < total && issued < limit) {
-      const unsigned int q = issued % TC_NSLOT;
-      if (!resident && issued >= TC_NSLOT)
-        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm->empty[q]), ((issued / TC_NSLOT) - 1u) & 1u);
-      const float* src = packed + (size_t)(issued % (unsigned)chunks_per_tile) * TC_SLOT_FLOATS;
+  // producer (its own warp, see acx_tc_bwd.cuh): streams the CTA's chunks in order as slots free up (resident: the
+  // first TC_NSLOT chunks only -- they are the whole network and stay)
+  __device__ inline void produce() {
+    const unsigned int n = resident ? (total < (unsigned)TC_NSLOT ? total : (unsigned)TC_NSLOT) : total;
+    for (unsigned int c = 0; c < n; ++c) {
+      const unsigned int q = c % TC_NSLOT;
+      if (c >= (unsigned)TC_NSLOT)
+        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm->empty[q]), ((c / TC_NSLOT) - 1u) & 1u);
+      const float* src = packed + (size_t)(c % (unsigned)chunks_per_tile) * TC_SLOT_FLOATS;
       acx_mbar_expect_tx(reinterpret_cast<uint64_t*>(&sm->full[q]), TC_SLOT_FLOATS * 4);
       acx_bulk_g2s(sm->slot[q], src, TC_SLOT_FLOATS * 4, reinterpret_cast<uint64_t*>(&sm->full[q]));
-      ++issued;
     }
   }
   // one chunk: kc input rows starting at A column k0, n_out outputs, accumulate into tmem_d
   __device__ inline void mma_chunk(uint32_t tmem, int k0, int kc, int n_out, uint32_t tmem_d, bool first) {
-    prefetch();
     const unsigned int q = g % TC_NSLOT;
     acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm->full[q]), resident ? 0u : ((g / TC_NSLOT) & 1u));
     fence_after_sync();
@@ -145,15 +145,17 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
   fence_after_sync();
   const uint32_t tmem = sm.tmem_base;
 
-  if (warp == 8) {
+  TcPipe pipe;
+  pipe.sm = &sm; pipe.packed = packed; pipe.g = 0;
+  pipe.chunks_per_tile = H1 / TC_KC2 + N3C;
+  pipe.resident = (pipe.chunks_per_tile == TC_NSLOT);
+  pipe.total = mine * pipe.chunks_per_tile;
+  if (warp == 9) {
+    // ================================================================ producer of the weight-chunk ring
+    if (lane == 0) pipe.produce();
+  } else if (warp == 8) {
     // ================================================================ issuer
     if (lane == 0) {
-      TcPipe pipe;
-      pipe.sm = &sm; pipe.packed = packed; pipe.g = 0; pipe.issued = 0;
-      pipe.chunks_per_tile = H1 / TC_KC2 + N3C;
-      pipe.resident = (pipe.chunks_per_tile == TC_NSLOT);
-      pipe.total = mine * pipe.chunks_per_tile;
-      pipe.prefetch();
       unsigned int ready = 0;
       for (unsigned int t = 0; t < mine; ++t) {
         for (int blk = 0; blk < NB; ++blk) {                     // layer 2, one 128-feature block of X1 at a time

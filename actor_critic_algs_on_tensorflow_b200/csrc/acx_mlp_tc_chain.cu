@@ -19,6 +19,13 @@ using namespace acxmlp;
 using namespace acxumma;
 using namespace acxtcbwd;
 
+#ifdef ACX_CHAIN_PROF
+__device__ unsigned long long acx_chain_prof[16];
+#define PROF_MARK(i) do { if (tid == 0) { const long long now_ = clock64(); prof_[i] += now_ - last_; last_ = now_; } } while (0)
+#else
+#define PROF_MARK(i) do { } while (0)
+#endif
+
 namespace {
 
 struct TcSmem {
@@ -31,6 +38,8 @@ struct TcSmem {
   float bh[MAX_OUT];
   float log_std[MAX_OUT];
   float dHead[MAX_OUT * MT];
+  float4 W1p[256];             // ob_dim <= 3: {W1[0][k], W1[1][k], W1[2][k], b1[k]} -- one 16-byte load per neuron
+  float l1p[128 * (MAX_OB + 1)];   // layer1 gradient partials of the second half of the samples
   double red[8][4];
   unsigned long long full[TT_NSLOT], empty[TT_NSLOT], a_ready, stage_done[3], bar_act[2];
   unsigned int tmem_base;
@@ -50,6 +59,9 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
   for (int i = tid; i < ob * H1; i += TT_NT) sm.W1[i] = P[L.W1 + i];
   for (int i = tid; i < H1; i += TT_NT) sm.b1[i] = P[L.b1 + i];
   for (int i = tid; i < H3 * nout; i += TT_NT) sm.Wh[i] = P[L.Wh + i];
+  if (ob <= 3)
+    for (int k = tid; k < H1; k += TT_NT)
+      sm.W1p[k] = make_float4(P[L.W1 + k], ob > 1 ? P[L.W1 + H1 + k] : 0.f, ob > 2 ? P[L.W1 + 2 * H1 + k] : 0.f, P[L.b1 + k]);
   if (tid < nout) {
     sm.bh[tid] = P[L.bh + tid];
     if (HEAD == HEAD_GAUSS) sm.log_std[tid] = P[L.log_std + tid];
@@ -74,14 +86,16 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
   fence_after_sync();
   const uint32_t tmem = sm.tmem_base;
 
-  if (warp == 8) {
+  TtPipe<TcSmem> pipe;
+  pipe.sm = &sm; pipe.packed = packed; pipe.g = 0;
+  pipe.chunks_per_tile = N3C + 8 * NB;
+  pipe.total = mine * pipe.chunks_per_tile;
+  if (warp == 9) {
+    // ================================================================ producer of the weight-chunk ring
+    if (lane == 0) pipe.produce();
+  } else if (warp == 8) {
     // ================================================================ issuer
     if (lane == 0) {
-      TtPipe<TcSmem> pipe;
-      pipe.sm = &sm; pipe.packed = packed; pipe.g = 0; pipe.issued = 0;
-      pipe.chunks_per_tile = N3C + 8 * NB;
-      pipe.total = mine * pipe.chunks_per_tile;
-      pipe.prefetch();
       unsigned int ready = 0;
       for (unsigned int t = 0; t < mine; ++t) {
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready), ready & 1u); ++ready;       // dPre3 is the A operand
@@ -129,6 +143,9 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
     };
     if ((int)blockIdx.x < ntiles && tile_is_bulk(blockIdx.x)) issue_x3(blockIdx.x, 0);
 
+#ifdef ACX_CHAIN_PROF
+    long long prof_[16] = {0}, last_ = clock64();
+#endif
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tiles_done) {
       const int row = tile / tpr, n0 = (tile % tpr) * MT;
       const int valid = min(MT, A.n - n0);
@@ -142,24 +159,6 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         const int next = tile + gridDim.x;
         if (next < ntiles && tile_is_bulk(next)) issue_x3(next, buf ^ 1);
       }
-      // this thread's observation (registers; also the shared copy layer1_grad reads) and its act'(X2) bits
-      float ob_r[MAX_OB];
-#pragma unroll
-      for (int i = 0; i < MAX_OB; ++i) {
-        ob_r[i] = (i < ob && live) ? __ldg(A.obs + ((size_t)row * ob + i) * ld + col) : 0.f;
-        if (i < ob && half == 0) sm.obs[i * MT + s] = ob_r[i];
-      }
-      unsigned int m2[2] = {0u, 0u};
-      {
-        const float* g2 = A.x2_in + ((size_t)row * H2 + half * 64) * ld + col;
-#pragma unroll
-        for (int q = 0; q < 2; ++q)
-#pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const float x = live ? __ldg(g2 + (size_t)(q * 32 + e) * ld) : 0.f;
-            m2[q] |= (x > 0.f ? 1u : 0u) << e;
-          }
-      }
       if (tile_is_bulk(tile)) {
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[buf]), act_phase[buf] & 1u);
         ++act_phase[buf];
@@ -167,6 +166,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         load_tile(S, A.x3_in + ((size_t)row * H3) * ld + n0, ld, H3, valid, vec_ok);
       }
       work_sync();
+      PROF_MARK(0);
 
       // ---------------------------------------------- head
       if (tid < MT) {
@@ -179,6 +179,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
           if (a < nout) sm.dHead[a * MT + tid] = dh[a];
       }
       work_sync();
+      PROF_MARK(1);
       {   // head weights and bias
         if (tid < H3) {
           for (int a = 0; a < nout; ++a) {
@@ -199,6 +200,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
           *p = first ? acc : *p + acc;
         }
       }
+      PROF_MARK(2);
       // ---------------------------------------------- dPre3: A operand + HBM stream (no barrier needed: reads only)
       {
         float dh[MAX_OUT];
@@ -229,16 +231,30 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
+      // act'(X2) of this thread's 64 features straight from the cache (coalesced): the first 32 loads fly while the
+      // tensor cores form dX2, the other 32 while the first half of dPre2 is worked on
+      const float* g2 = A.x2_in + ((size_t)row * H2 + half * 64) * ld + col;
+      float xm[32];
+#pragma unroll
+      for (int e = 0; e < 32; ++e) xm[e] = live ? __ldg(g2 + (size_t)e * ld) : 0.f;
       work_sync();                                  // every read of S as X3 is done: it may take the dPre1 blocks
+      PROF_MARK(3);
       // ---------------------------------------------- dPre2 = dX2 * act'(X2): next A operand + HBM stream
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[0]), par);
       fence_after_sync();
+      PROF_MARK(4);
 #pragma unroll 1
       for (int gq = 0; gq < 2; ++gq) {
+        unsigned int bits = 0u;
+#pragma unroll
+        for (int e = 0; e < 32; ++e) bits |= (xm[e] > 0.f ? 1u : 0u) << e;
+        if (gq == 0) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) xm[e] = live ? __ldg(g2 + (size_t)(32 + e) * ld) : 0.f;
+        }
         float v[32];
         const int k0 = half * 64 + gq * 32;
         tmem_ld32(tl + TT_D0 + (uint32_t)k0, v);
-        const unsigned int bits = m2[gq];
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] *= ((bits >> e) & 1u) ? 1.0f : SLOPE;
         a_store32_tt(tl, k0, v);
@@ -251,37 +267,102 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
+      // this thread's observation (registers; also the shared copy layer1_grad reads), while dX1 is formed
+      float ob_r[MAX_OB];
+#pragma unroll
+      for (int i = 0; i < MAX_OB; ++i) {
+        ob_r[i] = (i < ob && live) ? __ldg(A.obs + ((size_t)row * ob + i) * ld + col) : 0.f;
+        if (i < ob && half == 0) sm.obs[i * MT + s] = ob_r[i];
+      }
+      PROF_MARK(5);
       // ---------------------------------------------- layer 1: dPre1 = dX1 * act'(X1) per 128-row block, dW1, db1
       for (int h = 0; h < NB; ++h) {
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[1 + h]), par);
         fence_after_sync();
+        PROF_MARK(6 + 3 * h);
 #pragma unroll 1
         for (int gq = 0; gq < 2; ++gq) {
           float v[32];
           const int k0 = half * 64 + gq * 32;
           tmem_ld32(tl + (h == 0 ? TT_D0 : TT_D1) + (uint32_t)k0, v);
+          if (ob <= 3) {
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const int k = h * 128 + k0 + e;
-            float pre = 0.f;
+            for (int e = 0; e < 32; ++e) {
+              const float4 w = sm.W1p[h * 128 + k0 + e];
+              float pre = fmaf(ob_r[0], w.x, 0.f);
+              if (ob > 1) pre = fmaf(ob_r[1], w.y, pre);
+              if (ob > 2) pre = fmaf(ob_r[2], w.z, pre);
+              const float x1 = act_fn<LRELU>(__fadd_rn(pre, w.w));
+              v[e] *= act_grad<LRELU>(x1);
+            }
+          } else {
 #pragma unroll
-            for (int i = 0; i < MAX_OB; ++i)
-              if (i < ob) pre = fmaf(ob_r[i], sm.W1[i * H1 + k], pre);
-            const float x1 = act_fn<LRELU>(__fadd_rn(pre, sm.b1[k]));
-            v[e] *= act_grad<LRELU>(x1);
+            for (int e = 0; e < 32; ++e) {
+              const int k = h * 128 + k0 + e;
+              float pre = 0.f;
+#pragma unroll
+              for (int i = 0; i < MAX_OB; ++i)
+                if (i < ob) pre = fmaf(ob_r[i], sm.W1[i * H1 + k], pre);
+              const float x1 = act_fn<LRELU>(__fadd_rn(pre, sm.b1[k]));
+              v[e] *= act_grad<LRELU>(x1);
+            }
           }
 #pragma unroll
           for (int e = 0; e < 32; ++e) S[(k0 + e) * MS + s] = v[e];
         }
         fence_before_sync();
         work_sync();
-        layer1_grad<H1>(sm, h, ob, S, scr + L.W1, scr + L.b1, first);
-        fence_proxy_async();                        // S is next written by the async proxy (X3 prefetch)
-        work_sync();
+        PROF_MARK(7 + 3 * h);
+        {
+          // dW1[i][128h + j] (+)= sum_m obs[i][m] dPre1[j][m], db1 likewise: thread (j, sample half); the second half's
+          // partials go through shared memory, the first half adds them and updates the scratch row
+          const int j = tid & 127, hs = tid >> 7;
+          float sb = 0.f, sw[MAX_OB];
+#pragma unroll
+          for (int i = 0; i < MAX_OB; ++i) sw[i] = 0.f;
+#pragma unroll 4
+          for (int m4 = 16 * hs; m4 < 16 * hs + 16; ++m4) {
+            const float4 d = *reinterpret_cast<const float4*>(S + j * MS + 4 * m4);
+            sb += d.x; sb += d.y; sb += d.z; sb += d.w;
+#pragma unroll
+            for (int i = 0; i < MAX_OB; ++i)
+              if (i < ob) {
+                const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + 4 * m4]);
+                sw[i] = fmaf(o.x, d.x, sw[i]); sw[i] = fmaf(o.y, d.y, sw[i]);
+                sw[i] = fmaf(o.z, d.z, sw[i]); sw[i] = fmaf(o.w, d.w, sw[i]);
+              }
+          }
+          if (hs == 1) {
+            sm.l1p[j] = sb;
+#pragma unroll
+            for (int i = 0; i < MAX_OB; ++i)
+              if (i < ob) sm.l1p[(i + 1) * 128 + j] = sw[i];
+          }
+          fence_proxy_async();                      // S is next written by the async proxy (X3 prefetch)
+          work_sync();
+          if (hs == 0) {
+            const int k = h * 128 + j;
+            sb += sm.l1p[j];
+            float* pb = scr + L.b1 + k;
+            *pb = first ? sb : *pb + sb;
+#pragma unroll
+            for (int i = 0; i < MAX_OB; ++i)
+              if (i < ob) {
+                const float wsum = sw[i] + sm.l1p[(i + 1) * 128 + j];
+                float* pw = scr + L.W1 + i * H1 + k;
+                *pw = first ? wsum : *pw + wsum;
+              }
+          }
+        }
+        PROF_MARK(8 + 3 * h);
       }
       first = false;
     }
 
+#ifdef ACX_CHAIN_PROF
+    if (tid == 0 && blockIdx.x == 0)
+      for (int i = 0; i < 16; ++i) acx_chain_prof[i] = (unsigned long long)prof_[i];
+#endif
     // ---------------------------------------------------- per-CTA scalar sums (head threads = warps 0..3)
     work_sync();
     double v4[4] = {lsum[0], lsum[1], lsum[2], 0.0};
@@ -330,3 +411,9 @@ int acx_tc_chain_launch(const Args& a, const float* packed, float* d3, float* d2
   if (head == HEAD_CAT) return launch_chain<128, 64, true, HEAD_CAT>(a, packed, d3, d2, grid, st);
   return launch_chain<256, 128, false, HEAD_VALUE>(a, packed, d3, d2, grid, st);
 }
+
+#ifdef ACX_CHAIN_PROF
+extern "C" int acx_chain_prof_read(unsigned long long* out16) {
+  return (int)cudaMemcpyFromSymbol(out16, acx_chain_prof, sizeof(unsigned long long) * 16);
+}
+#endif

@@ -83,14 +83,16 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
   fence_after_sync();
   const uint32_t tmem = sm.tmem_base;
 
-  if (warp == 8) {
+  TtPipe<TtSmem> pipe;
+  pipe.sm = &sm; pipe.packed = packed; pipe.g = 0;
+  pipe.chunks_per_tile = N3C + 8 * NB;
+  pipe.total = mine * pipe.chunks_per_tile;
+  if (warp == 9) {
+    // ================================================================ producer of the weight-chunk ring
+    if (lane == 0) pipe.produce();
+  } else if (warp == 8) {
     // ================================================================ issuer
     if (lane == 0) {
-      TtPipe<TtSmem> pipe;
-      pipe.sm = &sm; pipe.packed = packed; pipe.g = 0; pipe.issued = 0;
-      pipe.chunks_per_tile = N3C + 8 * NB;
-      pipe.total = mine * pipe.chunks_per_tile;
-      pipe.prefetch();
       unsigned int ready = 0;
       for (unsigned int t = 0; t < mine; ++t) {
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready), ready & 1u); ++ready;       // dPre3 is the A operand

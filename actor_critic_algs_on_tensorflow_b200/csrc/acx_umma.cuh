@@ -119,6 +119,11 @@ __device__ inline float round_tf32(float x) {
 }
 // what kind::tf32 sees of a raw fp32 word: the low 13 mantissa bits are ignored
 __device__ inline float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+// lo part when the raw word itself serves as hi: x - trunc(x) is exact; adding half an ulp of the kept 10 bits to its
+// bit pattern makes the MMA's own truncation a round-to-nearest (ties away), i.e. what cvt.rna.tf32 would keep
+__device__ inline float lo_trunc_tf32(float x) {
+  return __uint_as_float(__float_as_uint(x - trunc_tf32(x)) + 0x1000u);
+}
 __device__ inline void split_tf32(float x, float& hi, float& lo) {
   hi = round_tf32(x);
   lo = round_tf32(x - hi);      // x - hi is exact in fp32

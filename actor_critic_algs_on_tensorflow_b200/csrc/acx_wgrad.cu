@@ -50,13 +50,10 @@ __device__ inline void mbar_arrive(unsigned long long* bar) {
 __device__ inline int sw128_f4(int r, int c) { return (r >> 3) * 64 + (r & 7) * 8 + (c ^ (r & 7)); }
 
 __device__ inline float4 lo_of(const float4 x) {
-  float4 y;
-  y.x = round_tf32(x.x - trunc_tf32(x.x)); y.y = round_tf32(x.y - trunc_tf32(x.y));
-  y.z = round_tf32(x.z - trunc_tf32(x.z)); y.w = round_tf32(x.w - trunc_tf32(x.w));
-  return y;
+  return make_float4(lo_trunc_tf32(x.x), lo_trunc_tf32(x.y), lo_trunc_tf32(x.z), lo_trunc_tf32(x.w));
 }
 
-template <int H1, int H3, bool LRELU>
+template <int H1, int H3, bool LRELU, int OBM>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constant__ CUtensorMap mapD3,
                  const __grid_constant__ CUtensorMap mapD2, const float* __restrict__ obs,
@@ -152,39 +149,41 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
     const int t = tid - 64;                       // 0..255
     const int c4 = t & 7, r0 = t >> 3;            // this thread's 16-byte chunk and its rows r0 + 32 m of every box
     unsigned int it = 0;
+    // observations of this thread's 4 samples of box (tile, kk); zeros beyond the batch
+    auto load_obs = [&](int tile, int kk, float4 (&o)[OBM]) {
+      const int row = tile / tpr, col = (tile % tpr) * 128 + kk * BOX + 4 * c4;
+#pragma unroll
+      for (int i = 0; i < OBM; ++i)
+        o[i] = (i < ob && tile < ntiles && col < n)
+                   ? __ldg(reinterpret_cast<const float4*>(obs + ((size_t)row * ob + i) * n + col))
+                   : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
     for (int phase = 0; phase < 2; ++phase) {
       const int brows = phase == 0 ? H3 : 128;
       float bacc[4] = {0.f, 0.f, 0.f, 0.f};       // bias-gradient partials of rows r0 + 32 m (chunk c4 of every box)
+      float4 o[OBM], o_next[OBM];
+      if (phase == 1) load_obs(blockIdx.x, 0, o_next);
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int row = tile / tpr, n0 = (tile % tpr) * 128;
+        const int n0 = (tile % tpr) * 128;
         const int nsub = (min(128, n - n0) + BOX - 1) / BOX;
         for (int kk = 0; kk < nsub; ++kk, ++it) {
           const unsigned int slot = it % NSTAGE;
           float4* r4 = reinterpret_cast<float4*>(raw + (size_t)slot * Cfg::STAGE);
           float4* l4 = reinterpret_cast<float4*>(lo + (size_t)slot * Cfg::STAGE);
-          float4 o[acxmlp::MAX_OB];
-          if (phase == 1) {                        // observations of this thread's 4 samples (0 beyond the batch)
-            const int col = n0 + kk * BOX + 4 * c4;
+          if (phase == 1) {
+            // A = X1 blocks, generated: X1[k][s] = act(sum_i obs[i][s] W1[i][k] + b1[k])  (layer1_block's arithmetic).
+            // Needs no loaded data, only the slot: start as soon as the MMAs that read it last are done.
 #pragma unroll
-            for (int i = 0; i < acxmlp::MAX_OB; ++i)
-              o[i] = (i < ob && col < n) ? __ldg(reinterpret_cast<const float4*>(obs + ((size_t)row * ob + i) * n + col))
-                                         : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-          acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.full[slot]), (it / NSTAGE) & 1u);
-          if (phase == 0) {
-#pragma unroll
-            for (int m = 0; m < 4; ++m) {          // A = X2 box: rows r0 + 32 m, stored chunk c4 (any bijection works)
-              const int idx = (r0 + 32 * m) * 8 + c4;
-              l4[idx] = lo_of(r4[idx]);
-            }
-          } else {
-            // A = X1 blocks, generated: X1[k][s] = act(sum_i obs[i][s] W1[i][k] + b1[k])  (layer1_block's arithmetic)
+            for (int i = 0; i < OBM; ++i) o[i] = o_next[i];
+            if (kk + 1 < nsub) load_obs(tile, kk + 1, o_next); else load_obs(tile + gridDim.x, 0, o_next);
+            if (it >= (unsigned)NSTAGE)
+              acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.empty[slot]), ((it / NSTAGE) - 1u) & 1u);
 #pragma unroll
             for (int m = 0; m < H1 / 32; ++m) {
               const int k = r0 + 32 * m;
               float4 sacc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-              for (int i = 0; i < acxmlp::MAX_OB; ++i)
+              for (int i = 0; i < OBM; ++i)
                 if (i < ob) {
                   const float w = B.W1[i * H1 + k];
                   sacc.x = fmaf(o[i].x, w, sacc.x); sacc.y = fmaf(o[i].y, w, sacc.y);
@@ -197,6 +196,14 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
               const int idx = (k >> 7) * (BLK / 4) + sw128_f4(k & 127, c4);
               r4[idx] = x;
               l4[idx] = lo_of(x);
+            }
+          }
+          acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.full[slot]), (it / NSTAGE) & 1u);
+          if (phase == 0) {
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {          // A = X2 box: rows r0 + 32 m, stored chunk c4 (any bijection works)
+              const int idx = (r0 + 32 * m) * 8 + c4;
+              l4[idx] = lo_of(r4[idx]);
             }
           }
           // B = dPre box: split, and add this thread's 4 samples of rows r0 + 32 m to the bias-gradient partials
@@ -251,7 +258,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
-template <int H1, int H3, bool LRELU>
+template <int H1, int H3, bool LRELU, int OBM>
 int launch_wgrad(const AcxWgradArgs& a, cudaStream_t st) {
   CUtensorMap mX2, mD3, mD2;
   const uint64_t pitch = (uint64_t)a.n * 4;
@@ -259,7 +266,7 @@ int launch_wgrad(const AcxWgradArgs& a, cudaStream_t st) {
   if (!rc) rc = acx_tmap_2d(&mD3, a.d3, (uint64_t)a.n, (uint64_t)a.rows * H3, pitch, BOX, H3);
   if (!rc) rc = acx_tmap_2d(&mD2, a.d2, (uint64_t)a.n, (uint64_t)a.rows * 128, pitch, BOX, 128);
   ACX_REQUIRE(rc == 0, "acx_wgrad: cuTensorMapEncodeTiled failed (%d) for rows=%d n=%d", rc, a.rows, a.n);
-  auto kern = acx_wgrad_kernel<H1, H3, LRELU>;
+  auto kern = acx_wgrad_kernel<H1, H3, LRELU, OBM>;
   ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgCfg<H1>::SMEM));
   kern<<<a.grid, WG_THREADS, WgCfg<H1>::SMEM, st>>>(mX2, mD3, mD2, a.obs, a.params, a.ob, a.offW1, a.offb1, a.rows, a.n,
                                                     a.scratch, a.scr_stride, a.offW3, a.offW2, a.offb3, a.offb2);
@@ -274,8 +281,11 @@ int acx_wgrad_launch(const AcxWgradArgs& a, void* stream) {
   ACX_REQUIRE(acx_aligned16(a.x2) && acx_aligned16(a.d3) && acx_aligned16(a.obs) && acx_aligned16(a.d2) &&
                   acx_aligned16(a.scratch), "acx_wgrad: operands must be 16-byte aligned");
   ACX_REQUIRE(a.ob >= 1 && a.ob <= acxmlp::MAX_OB, "acx_wgrad: ob_dim %d outside [1,%d]", a.ob, acxmlp::MAX_OB);
-  if (a.H1 == 128 && a.H3 == 64 && a.lrelu) return launch_wgrad<128, 64, true>(a, (cudaStream_t)stream);
-  if (a.H1 == 256 && a.H3 == 128 && !a.lrelu) return launch_wgrad<256, 128, false>(a, (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (a.H1 == 128 && a.H3 == 64 && a.lrelu)
+    return a.ob <= 4 ? launch_wgrad<128, 64, true, 4>(a, st) : launch_wgrad<128, 64, true, 8>(a, st);
+  if (a.H1 == 256 && a.H3 == 128 && !a.lrelu)
+    return a.ob <= 4 ? launch_wgrad<256, 128, false, 4>(a, st) : launch_wgrad<256, 128, false, 8>(a, st);
   ACX_REQUIRE(false, "acx_wgrad: unsupported layer widths H1=%d H3=%d", a.H1, a.H3);
   return ACX_OK;
 }

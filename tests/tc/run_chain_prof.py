@@ -1,0 +1,36 @@
+"""Dev: per-phase cycle counts of the chain kernel (CTA 0, thread 0) from a -DACX_CHAIN_PROF build (libacx_prof.so)."""
+import ctypes as C
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch  # noqa: E402
+from actor_critic_algs_on_tensorflow_b200 import _lib as L  # noqa: E402
+
+L.LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libacx_prof.so")
+from actor_critic_algs_on_tensorflow_b200.trainer import A2CTrainer  # noqa: E402
+
+tr = A2CTrainer("Pendulum-v0", n_envs=65536, horizon=20, seed=12321, use_graph=False)
+for _ in range(2):
+    tr.iteration()
+torch.cuda.synchronize()
+lib = L.load()
+names = ["load+wait X3", "head", "head grads", "dPre3+sync", "wait MMA3", "dPre2", "wait MMA2 b0", "dPre1 b0", "l1grad b0",
+         "wait MMA2 b1", "dPre1 b1", "l1grad b1"]
+buf = (C.c_ulonglong * 16)()
+s = L.cur_stream()
+for which in ("actor", "critic"):
+    ga, gc = tr.grads[:tr.Pa], tr.grads[tr.Pa:]
+    common = (L.ptr(tr.obs_buf), L.ptr(tr.acs), L.ptr(tr.adv), L.ptr(tr.stats), L.ptr(tr.logps), L.ptr(tr.G), L.ptr(tr.opt),
+              L.ptr(ga), L.ptr(gc), L.ptr(tr.stats), L.ptr(tr.ax2), L.ptr(tr.ax3), L.ptr(tr.cx2), L.ptr(tr.cx3),
+              L.ptr(tr.ws_bwd), tr.ws_bwd_bytes, s)
+    L.call("acx_loss_backward_gauss_tc", L.ptr(tr.actor) if which == "actor" else None,
+           L.ptr(tr.critic) if which == "critic" else None, L.ptr(tr.packed_bwd_a), L.ptr(tr.packed_bwd_c), tr.ob,
+           tr.num_ac, tr.ac_scale, tr.T, tr.N, *common)
+    torch.cuda.synchronize()
+    lib.acx_chain_prof_read.argtypes = [C.c_void_p]
+    lib.acx_chain_prof_read(buf)
+    tot = sum(buf[i] for i in range(12))
+    print(which, "total cycles", tot, "tiles ~", 20 * 512 / 148)
+    for i, nm in enumerate(names):
+        print("  %-14s %9d  %5.1f%%  per tile %7.0f" % (nm, buf[i], 100.0 * buf[i] / tot, buf[i] / (20 * 512 / 148)))
