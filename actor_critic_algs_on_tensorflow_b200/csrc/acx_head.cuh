@@ -12,6 +12,25 @@ struct HeadScalars {          // per-kernel constants of the training head
   unsigned int step0;
 };
 
+// MODE_TRAIN reads per-sample inputs (targets | adv, logp_old, actions) that nothing else touches: a kernel that knows
+// its next tile can pull them towards the SM ahead of time
+template <int HEAD>
+__device__ inline void head_train_prefetch(const Args& A, int nout, int row, size_t col) {
+  const size_t s_idx = (size_t)row * A.n + col;
+  if (HEAD == HEAD_VALUE) {
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(A.targets + s_idx));
+  } else {
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(A.adv + s_idx));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(A.logp_old + s_idx));
+    if (HEAD == HEAD_GAUSS) {
+      for (int d = 0; d < nout; ++d)
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(A.ac_in_f + ((size_t)row * nout + d) * A.n + col));
+    } else {
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(A.ac_in_i + s_idx));
+    }
+  }
+}
+
 // pre[a]: head pre-activation (bias added).  Outputs are written to the Args buffers at (row, col).
 // lsum: {sum adv*lp | sum err^2, sum (lp_old-lp)^2, sum entropy, -}; dls: d loss / d log_std; dh: d loss / d pre.
 template <int HEAD, int MODE>

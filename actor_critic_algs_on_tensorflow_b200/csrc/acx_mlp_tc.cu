@@ -44,6 +44,7 @@ struct TcSmem {
   float bh[MAX_OUT];
   float log_std[MAX_OUT];
   float pre[MAX_OUT * MT];                       // partial head sums of the second warpgroup
+  float4 W1p[256];                               // ob_dim <= 3: {W1[0][k], W1[1][k], W1[2][k], b1[k]}
   double red[8];
   unsigned long long full[TC_NSLOT], empty[TC_NSLOT], a_ready, stage_done;
   unsigned int tmem_base;
@@ -99,10 +100,11 @@ struct TcPipe {
 
 // 32 activations of sample `s` (features j0..j0+31) -> A operand columns, hi and lo
 __device__ inline void a_store32(uint32_t tmem_lane, int j0, const float (&v)[32]) {
-  float hi[32], lo[32];
+  // hi = the raw word (kind::tf32 ignores its low 13 mantissa bits), lo = the rounded remainder
+  float lo[32];
 #pragma unroll
-  for (int i = 0; i < 32; ++i) split_tf32(v[i], hi[i], lo[i]);
-  tmem_st32(tmem_lane + TC_A_HI + (uint32_t)j0, hi);
+  for (int i = 0; i < 32; ++i) lo[i] = lo_trunc_tf32(v[i]);
+  tmem_st32(tmem_lane + TC_A_HI + (uint32_t)j0, v);
   tmem_st32(tmem_lane + TC_A_LO + (uint32_t)j0, lo);
 }
 
@@ -119,6 +121,9 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
 
   for (int i = tid; i < ob * H1; i += TC_NT) sm.W1[i] = P[L.W1 + i];
   for (int i = tid; i < H1; i += TC_NT) sm.b1[i] = P[L.b1 + i];
+  if (ob <= 3)
+    for (int k = tid; k < H1; k += TC_NT)
+      sm.W1p[k] = make_float4(P[L.W1 + k], ob > 1 ? P[L.W1 + H1 + k] : 0.f, ob > 2 ? P[L.W1 + 2 * H1 + k] : 0.f, P[L.b1 + k]);
   for (int i = tid; i < H2; i += TC_NT) sm.b2[i] = P[L.b2 + i];
   for (int i = tid; i < H3; i += TC_NT) sm.b3[i] = P[L.b3 + i];
   for (int i = tid; i < H3 * nout; i += TC_NT) sm.Wh[i] = P[L.Wh + i];
@@ -181,39 +186,55 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
     double kl_sum = 0.0;
     unsigned int done = 0;                         // completed waits on stage_done
 
+    // this thread's observation of tile `tile` (coalesced; zeros beyond the batch), fetched one tile ahead
+    auto load_obs = [&](int tile, float (&o)[MAX_OB]) {
+      const int row = tile / tpr, c = (tile % tpr) * MT + s;
+#pragma unroll
+      for (int i = 0; i < MAX_OB; ++i)
+        o[i] = (i < ob && tile < ntiles && c < A.n) ? __ldg(A.obs + ((size_t)row * ob + i) * A.n + c) : 0.f;
+    };
+    float o_next[MAX_OB];
+    load_obs(blockIdx.x, o_next);
+
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int row = tile / tpr, n0 = (tile % tpr) * MT;
       const int valid = min(MT, A.n - n0);
       const bool live = s < valid;
       const size_t col = (size_t)n0 + s;
-      epi_sync();                                  // everybody is done with the previous tile's obs / pre
-      for (int idx = tid; idx < ob * MT; idx += TC_EPI) {
-        const int i = idx / MT, m = idx % MT;
-        sm.obs[idx] = (m < valid) ? A.obs[((size_t)row * ob + i) * A.n + n0 + m] : 0.f;
-      }
-      epi_sync();
       float o[MAX_OB];
 #pragma unroll
-      for (int i = 0; i < MAX_OB; ++i) o[i] = (i < ob) ? sm.obs[i * MT + s] : 0.f;
+      for (int i = 0; i < MAX_OB; ++i) o[i] = o_next[i];
+      load_obs(tile + gridDim.x, o_next);
 
       // ---------------------------------------------- layer 1 -> A operand, one 128-feature block per stage
       for (int blk = 0; blk < NB; ++blk) {
-        if (blk > 0) {                             // the MMAs reading the previous block must be done
-          acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
-          fence_after_sync();
-        }
 #pragma unroll 1
         for (int gq = 0; gq < 2; ++gq) {           // this thread: features half*64 + gq*32 .. +31 of the block
           float v[32];
           const int j0 = half * 64 + gq * 32;
+          if (ob <= 3) {
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const int k = blk * 128 + j0 + e;
-            float acc = 0.f;
+            for (int e = 0; e < 32; ++e) {
+              const float4 w = sm.W1p[blk * 128 + j0 + e];
+              float acc = fmaf(o[0], w.x, 0.f);
+              if (ob > 1) acc = fmaf(o[1], w.y, acc);
+              if (ob > 2) acc = fmaf(o[2], w.z, acc);
+              v[e] = act_fn<LRELU>(__fadd_rn(acc, w.w));
+            }
+          } else {
 #pragma unroll
-            for (int i = 0; i < MAX_OB; ++i)
-              if (i < ob) acc = fmaf(o[i], sm.W1[i * H1 + k], acc);
-            v[e] = act_fn<LRELU>(__fadd_rn(acc, sm.b1[k]));
+            for (int e = 0; e < 32; ++e) {
+              const int k = blk * 128 + j0 + e;
+              float acc = 0.f;
+#pragma unroll
+              for (int i = 0; i < MAX_OB; ++i)
+                if (i < ob) acc = fmaf(o[i], sm.W1[i * H1 + k], acc);
+              v[e] = act_fn<LRELU>(__fadd_rn(acc, sm.b1[k]));
+            }
+          }
+          if (blk > 0 && gq == 0) {                // the MMAs reading the previous block must be done
+            acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
+            fence_after_sync();
           }
           a_store32(tl, j0, v);
         }

@@ -125,7 +125,16 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
     double lsum[4] = {0.0, 0.0, 0.0, 0.0};
     float dls[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
     float* __restrict__ scr = A.scratch + (size_t)blockIdx.x * L.size;
-    bool first = true;
+    // gradients this thread owns, summed over all of the CTA's tiles in registers and stored once at the end:
+    // head weights (thread = feature k < H3; thread 128 + a: head bias a), layer 1 (thread = (neuron j, sample half))
+    float gWh[MAX_OUT] = {0.f, 0.f, 0.f, 0.f}, gbh = 0.f;
+    float gW1[NB][MAX_OB], gb1[NB];
+#pragma unroll
+    for (int h = 0; h < NB; ++h) {
+      gb1[h] = 0.f;
+#pragma unroll
+      for (int i = 0; i < MAX_OB; ++i) gW1[h][i] = 0.f;
+    }
     unsigned int act_phase[2] = {0u, 0u}, tiles_done = 0;
     if (tid < L.size - L.bh) scr[L.bh + tid] = 0.f;
     const bool vec_ok = (A.n & 3) == 0;
@@ -158,13 +167,25 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       {
         const int next = tile + gridDim.x;
         if (next < ntiles && tile_is_bulk(next)) issue_x3(next, buf ^ 1);
+        if (next < ntiles && tid < MT && (next % tpr) * MT + tid < A.n)
+          head_train_prefetch<HEAD>(A, nout, next / tpr, (size_t)(next % tpr) * MT + tid);
       }
+      // act'(X2) of this thread's 64 features straight from the cache (coalesced), as two 32-bit masks: the upper 32
+      // loads fly while the X3 tile lands, the lower 32 while the tensor cores form dX2
+      const float* g2 = A.x2_in + ((size_t)row * H2 + half * 64) * ld + col;
+      float xm[32];
+      unsigned int m2[2];
+#pragma unroll
+      for (int e = 0; e < 32; ++e) xm[e] = live ? __ldg(g2 + (size_t)(32 + e) * ld) : 0.f;
       if (tile_is_bulk(tile)) {
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[buf]), act_phase[buf] & 1u);
         ++act_phase[buf];
       } else {
         load_tile(S, A.x3_in + ((size_t)row * H3) * ld + n0, ld, H3, valid, vec_ok);
       }
+      m2[1] = 0u;
+#pragma unroll
+      for (int e = 0; e < 32; ++e) m2[1] |= (xm[e] > 0.f ? 1u : 0u) << e;
       work_sync();
       PROF_MARK(0);
 
@@ -189,15 +210,13 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
               const float4 d = *reinterpret_cast<const float4*>(&sm.dHead[a * MT + 4 * m4]);
               acc = fmaf(x.x, d.x, acc); acc = fmaf(x.y, d.y, acc); acc = fmaf(x.z, d.z, acc); acc = fmaf(x.w, d.w, acc);
             }
-            float* p = scr + L.Wh + tid * nout + a;
-            *p = first ? acc : *p + acc;
+            gWh[a] += acc;
           }
         } else if (tid >= 128 && tid < 128 + nout) {
           const int a = tid - 128;
           float acc = 0.f;
           for (int m = 0; m < MT; ++m) acc += sm.dHead[a * MT + m];
-          float* p = scr + L.bh + a;
-          *p = first ? acc : *p + acc;
+          gbh += acc;
         }
       }
       PROF_MARK(2);
@@ -231,10 +250,6 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
-      // act'(X2) of this thread's 64 features straight from the cache (coalesced): the first 32 loads fly while the
-      // tensor cores form dX2, the other 32 while the first half of dPre2 is worked on
-      const float* g2 = A.x2_in + ((size_t)row * H2 + half * 64) * ld + col;
-      float xm[32];
 #pragma unroll
       for (int e = 0; e < 32; ++e) xm[e] = live ? __ldg(g2 + (size_t)e * ld) : 0.f;
       work_sync();                                  // every read of S as X3 is done: it may take the dPre1 blocks
@@ -243,15 +258,12 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[0]), par);
       fence_after_sync();
       PROF_MARK(4);
+      m2[0] = 0u;
+#pragma unroll
+      for (int e = 0; e < 32; ++e) m2[0] |= (xm[e] > 0.f ? 1u : 0u) << e;
 #pragma unroll 1
       for (int gq = 0; gq < 2; ++gq) {
-        unsigned int bits = 0u;
-#pragma unroll
-        for (int e = 0; e < 32; ++e) bits |= (xm[e] > 0.f ? 1u : 0u) << e;
-        if (gq == 0) {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) xm[e] = live ? __ldg(g2 + (size_t)(32 + e) * ld) : 0.f;
-        }
+        const unsigned int bits = m2[gq];
         float v[32];
         const int k0 = half * 64 + gq * 32;
         tmem_ld32(tl + TT_D0 + (uint32_t)k0, v);
@@ -276,6 +288,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       }
       PROF_MARK(5);
       // ---------------------------------------------- layer 1: dPre1 = dX1 * act'(X1) per 128-row block, dW1, db1
+#pragma unroll
       for (int h = 0; h < NB; ++h) {
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[1 + h]), par);
         fence_after_sync();
@@ -314,8 +327,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         work_sync();
         PROF_MARK(7 + 3 * h);
         {
-          // dW1[i][128h + j] (+)= sum_m obs[i][m] dPre1[j][m], db1 likewise: thread (j, sample half); the second half's
-          // partials go through shared memory, the first half adds them and updates the scratch row
+          // dW1[i][128h + j] += sum_m obs[i][m] dPre1[j][m], db1 likewise: thread (j, sample half), in registers
           const int j = tid & 127, hs = tid >> 7;
           float sb = 0.f, sw[MAX_OB];
 #pragma unroll
@@ -332,37 +344,47 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
                 sw[i] = fmaf(o.z, d.z, sw[i]); sw[i] = fmaf(o.w, d.w, sw[i]);
               }
           }
-          if (hs == 1) {
-            sm.l1p[j] = sb;
+          gb1[h] += sb;
 #pragma unroll
-            for (int i = 0; i < MAX_OB; ++i)
-              if (i < ob) sm.l1p[(i + 1) * 128 + j] = sw[i];
-          }
+          for (int i = 0; i < MAX_OB; ++i)
+            if (i < ob) gW1[h][i] += sw[i];
           fence_proxy_async();                      // S is next written by the async proxy (X3 prefetch)
           work_sync();
-          if (hs == 0) {
-            const int k = h * 128 + j;
-            sb += sm.l1p[j];
-            float* pb = scr + L.b1 + k;
-            *pb = first ? sb : *pb + sb;
-#pragma unroll
-            for (int i = 0; i < MAX_OB; ++i)
-              if (i < ob) {
-                const float wsum = sw[i] + sm.l1p[(i + 1) * 128 + j];
-                float* pw = scr + L.W1 + i * H1 + k;
-                *pw = first ? wsum : *pw + wsum;
-              }
-          }
         }
         PROF_MARK(8 + 3 * h);
       }
-      first = false;
     }
 
 #ifdef ACX_CHAIN_PROF
     if (tid == 0 && blockIdx.x == 0)
       for (int i = 0; i < 16; ++i) acx_chain_prof[i] = (unsigned long long)prof_[i];
 #endif
+    // ---------------------------------------------------- the register-held gradients -> this CTA's scratch row
+    if (tid < H3)
+      for (int a = 0; a < nout; ++a) scr[L.Wh + tid * nout + a] = gWh[a];
+    else if (tid >= 128 && tid < 128 + nout)
+      scr[L.bh + tid - 128] = gbh;
+    {
+      const int j = tid & 127, hs = tid >> 7;
+#pragma unroll
+      for (int h = 0; h < NB; ++h) {
+        work_sync();
+        if (hs == 1) {                              // second sample half -> shared memory, first half adds and stores
+          sm.l1p[j] = gb1[h];
+#pragma unroll
+          for (int i = 0; i < MAX_OB; ++i)
+            if (i < ob) sm.l1p[(i + 1) * 128 + j] = gW1[h][i];
+        }
+        work_sync();
+        if (hs == 0) {
+          const int k = h * 128 + j;
+          scr[L.b1 + k] = gb1[h] + sm.l1p[j];
+#pragma unroll
+          for (int i = 0; i < MAX_OB; ++i)
+            if (i < ob) scr[L.W1 + i * H1 + k] = gW1[h][i] + sm.l1p[(i + 1) * 128 + j];
+        }
+      }
+    }
     // ---------------------------------------------------- per-CTA scalar sums (head threads = warps 0..3)
     work_sync();
     double v4[4] = {lsum[0], lsum[1], lsum[2], 0.0};
