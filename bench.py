@@ -376,7 +376,11 @@ def run_ours(args, rank, local_rank, world):
                                    "3xTF32 split for fp32-class accuracy); achieved = algorithmic FLOPs (2 per MAC of "
                                    "the backward pass) per second; %s" % (peaks_src, bf16_peak, note),
                     "frac_of_fp32_ffma_peak": dom["achieved"] / FP32_PEAK_TFLOPS,
-                    "share_of_step": dom["ms"] / step_ms, "traffic": None,
+                    "share_of_step": dom["ms"] / step_ms,
+                    # dram__bytes_read.sum + dram__bytes_write.sum of the two kernels, one ncu --set full capture of this
+                    # workload (profiles/r01_ncu_tc_backward.md): chain 1.366 + 1.301 GB, wgrad 2.029 + 0.004 GB
+                    "traffic": 4.700e9 if (N_ENVS, HORIZON) == (65536, 20) else None, "traffic_unit": "bytes per launch",
+                    "algorithmic_bytes": 4.697e9 if (N_ENVS, HORIZON) == (65536, 20) else None,
                     "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
         else:
             roof = {"kernel": dom_kernel, "bound": "fp32",
