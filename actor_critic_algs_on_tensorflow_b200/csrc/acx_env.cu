@@ -229,3 +229,35 @@ extern "C" int acx_env_dims(int env, int* state_dim, int* obs_dim, int* n_action
   if (max_episode_steps) *max_episode_steps = m;
   return ACX_OK;
 }
+
+// ------------------------------------------------------------------ frame stacking (Framer, A3C/process.py:25-43)
+// out[f][i][e] = the observation f - (frames-1) steps back from `obs`, within the episode: where the transition that
+// produced `obs` ended an episode (done) -- or there is no history at all (prev == NULL) -- every frame is `obs`
+// (the reference pads a fresh episode with copies of its first observation).  Frame 0 is the oldest.
+__global__ void __launch_bounds__(256) acx_frame_push_kernel(int n, int ob, int frames, const float* __restrict__ prev,
+                                                             const float* __restrict__ obs,
+                                                             const unsigned char* __restrict__ done,
+                                                             float* __restrict__ out) {
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+    const bool fresh = prev == nullptr || (done != nullptr && done[e] != 0);
+    for (int i = 0; i < ob; ++i) {
+      const float cur = obs[(size_t)i * n + e];
+      for (int f = 0; f < frames; ++f) {
+        const float v = (fresh || f == frames - 1) ? cur : prev[((size_t)(f + 1) * ob + i) * n + e];
+        out[((size_t)f * ob + i) * n + e] = v;
+      }
+    }
+  }
+}
+
+extern "C" int acx_frame_push(int n, int ob_dim, int frames, const float* prev, const float* obs,
+                              const unsigned char* done, float* out, void* stream) {
+  ACX_REQUIRE(n >= 0, "acx_frame_push: n must be >= 0 (got %d)", n);
+  ACX_REQUIRE(ob_dim >= 1 && frames >= 1, "acx_frame_push: ob_dim %d / frames %d must be >= 1", ob_dim, frames);
+  if (n == 0) return ACX_OK;
+  ACX_REQUIRE(obs && out, "acx_frame_push: null obs / out");
+  ACX_REQUIRE(out != prev, "acx_frame_push: out must not alias prev (frames are shifted)");
+  acx_frame_push_kernel<<<env_grid(n, 1), 256, 0, (cudaStream_t)stream>>>(n, ob_dim, frames, prev, obs, done, out);
+  ACX_LAUNCH_OK("acx_frame_push_kernel");
+  return ACX_OK;
+}

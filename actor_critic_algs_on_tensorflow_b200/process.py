@@ -264,8 +264,6 @@ def process_fn(cluster, task_id, job, env_id, logger, save_path, stdout_freq, ra
     if job == 'ps':
         print("ps %d: parameters are replicated on every GPU and reduced over NCCL; nothing to serve" % task_id)
         return None
-    if stack_frames != 1:
-        raise L.AcxError("--frames > 1 is not implemented on the fused path yet (SURVEY.md 8f row 4)")
     world = len(cluster['worker'])
     is_chief = (task_id == 0)
     if world > 1:
@@ -277,7 +275,7 @@ def process_fn(cluster, task_id, job, env_id, logger, save_path, stdout_freq, ra
             dist.init_process_group("nccl", rank=task_id, world_size=world)
     tr = A2CTrainer(env_id, n_envs=n_envs, horizon=horizon, seed=random_seed - task_id, gamma=gamma,
                     look_ahead=look_ahead, desired_kl=desired_kl, min_lr=MIN_LR, max_lr=MAX_LR, rank=task_id,
-                    world=world, mode=mode, use_graph=use_graph)
+                    world=world, mode=mode, use_graph=use_graph, frames=stack_frames)
     if is_chief:
         print('Initilizing chief. Envirnoment action type {}.'.format('cont' if tr.cont else 'disc'))
     print('\n\nREACHING THE MAIN LOOP OF WORKER %d\n' % task_id)

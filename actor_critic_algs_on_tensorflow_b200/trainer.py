@@ -58,12 +58,18 @@ class A2CTrainer:
                  desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1, actor_lr=0.005, critic_lr=0.001, beta=1.0,
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
                  critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=True,
-                 cache_activations=True, tensor_core_backward=True):
+                 cache_activations=True, tensor_core_backward=True, frames=1):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
         self.env = ENV_IDS[env_id] if isinstance(env_id, str) else int(env_id)
-        self.S, self.ob, self.n_act, default_max = env_dims(self.env)
+        self.S, self.env_ob, self.n_act, default_max = env_dims(self.env)
+        # Framer (A3C/process.py:25-43, --frames k): the networks see the last k observations of the episode
+        self.frames = int(frames)
+        self.ob = self.env_ob * self.frames
+        if self.frames < 1 or self.ob > 8:
+            raise L.AcxError("frames=%d: the MLP kernels take at most 8 input features (%d observation components x "
+                             "frames)" % (self.frames, self.env_ob))
         self.cont = self.n_act == 0
         self.num_ac = 1 if self.cont else self.n_act
         self.ac_scale = 2.0                       # max(|low|, high) of Pendulum (A3C/process.py:186)
@@ -107,6 +113,7 @@ class A2CTrainer:
         self.state = torch.empty((self.S, N), device=d, dtype=f32)
         self.elapsed = torch.zeros(N, device=d, dtype=torch.int32)
         self.obs_buf = torch.empty((T + 1, self.ob, N), device=d, dtype=f32)
+        self.raw_obs = torch.empty((self.env_ob, N), device=d, dtype=f32) if self.frames > 1 else None
         self.acs = (torch.empty((T, self.num_ac, N), device=d, dtype=f32) if self.cont
                     else torch.empty((T, N), device=d, dtype=torch.int32))
         self.logps = torch.empty((T, N), device=d, dtype=f32)
@@ -147,8 +154,10 @@ class A2CTrainer:
         s = L.cur_stream()
         L.call("acx_opt_init", L.ptr(self.opt), actor_lr, critic_lr, beta, gamma_ent, clip, desired_kl, min_lr, max_lr,
                int(bool(schedule)), s)
-        L.call("acx_env_reset", self.env, N, L.ptr(self.state), L.ptr(self.elapsed), L.ptr(self.obs_buf[0]), None,
-               self.seed, self.index0, 0xFFFFFFFF, s)
+        L.call("acx_env_reset", self.env, N, L.ptr(self.state), L.ptr(self.elapsed),
+               L.ptr(self.obs_buf[0] if self.frames == 1 else self.raw_obs), None, self.seed, self.index0, 0xFFFFFFFF, s)
+        if self.frames > 1:
+            L.call("acx_frame_push", N, self.env_ob, self.frames, None, L.ptr(self.raw_obs), None, L.ptr(self.obs_buf[0]), s)
         self._pack()
 
     # ------------------------------------------------------------------ pieces (all enqueue on the current stream)
@@ -196,9 +205,13 @@ class A2CTrainer:
             else:
                 L.call("acx_policy_forward_sample_cat", L.ptr(self.actor), self.ob, self.n_act, 1, N, *tail)
             L.call("acx_env_step", self.env, N, L.ptr(self.state), L.ptr(self.elapsed), self._row(self.acs, t),
-                   self._row(self.obs_buf, t + 1), self._row(self.rew, t), self._row(self.done, t), ru, self.seed,
-                   self.index0, t, L.ptr(self.step_ctr), self.max_steps, s)
+                   self._row(self.obs_buf, t + 1) if self.frames == 1 else L.ptr(self.raw_obs), self._row(self.rew, t),
+                   self._row(self.done, t), ru, self.seed, self.index0, t, L.ptr(self.step_ctr), self.max_steps, s)
             n += 2
+            if self.frames > 1:
+                L.call("acx_frame_push", N, self.env_ob, self.frames, self._row(self.obs_buf, t), L.ptr(self.raw_obs),
+                       self._row(self.done, t), self._row(self.obs_buf, t + 1), s)
+                n += 1
         L.call("acx_counter_add", L.ptr(self.step_ctr), self.T, s)
         return n + 1
 

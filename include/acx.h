@@ -111,6 +111,14 @@ int acx_env_step_acrobot(int n, float* state, int* elapsed, const int* action, f
                          uint64_t index0, uint32_t step, const uint32_t* step_base, int max_steps,
                           void* stream);
 
+/* Framer (A3C/process.py:25-43, `--frames k`): the network input is the last `frames` observations of the episode,
+ * oldest first, a fresh episode padded with copies of its first observation.  prev[frames*ob_dim][n] is the stacked
+ * input one step earlier (NULL: no history, e.g. right after acx_env_reset), obs[ob_dim][n] the new observation,
+ * done[n] the done flags of the transition that produced it (NULL: none ended); out[frames*ob_dim][n] must not
+ * alias prev.  The MLP entry points then run with ob_dim = frames * ob_dim (<= 8). */
+int acx_frame_push(int n, int ob_dim, int frames, const float* prev, const float* obs, const unsigned char* done,
+                   float* out, void* stream);
+
 /* ---------------------------------------------------------------- K2: policy / value forward
  * Actor.act, Gaussian head -- A3C/policies.py:44-58,110-115.  eps[rows][ac_dim][n] standard
  * normals or NULL (Philox; ac_dim <= 2).  Outputs: ac_out[rows][ac_dim][n], logp_out,

@@ -23,7 +23,9 @@ class A2CState:
         self.env, self.N, self.seed, self.rank, self.world = env, n_envs, seed, rank, world
         self.f = dtype
         self.cont = env == E.PENDULUM
-        self.ob_dim = E.OBS_DIM[env]
+        self.frames = int(frames)                      # Framer (A3C/process.py:25-43): network input = last k observations
+        self.env_ob = E.OBS_DIM[env]
+        self.ob_dim = self.env_ob * self.frames
         self.num_ac = 1 if self.cont else E.N_ACTIONS[env]
         self.ac_scale = 2.0
         self.alay = P.actor_layout(self.ob_dim, self.num_ac, self.cont)
@@ -43,7 +45,7 @@ class A2CState:
         u = R.uniforms(self.idx, 0xFFFFFFFF, R.STREAM_RESET, seed).T            # [4, N]
         self.state = E.reset_from_uniforms(env, u[:E.STATE_DIM[env]], dtype)
         self.elapsed = np.zeros(n_envs, dtype=np.int32)
-        self.obs = E.observe(env, self.state, dtype)
+        self.obs = np.tile(E.observe(env, self.state, dtype), (self.frames, 1))     # fresh episode: k copies
 
 
 def rollout(S, T, max_steps=None):
@@ -64,7 +66,12 @@ def rollout(S, T, max_steps=None):
         ac, lp, ent, _ = P.actor_act(S.actor, S.alay, S.obs.T, noise, S.cont, S.ac_scale, dtype=f)
         ru = R.uniforms(S.idx, S.gstep, R.STREAM_RESET, S.seed).T[:E.STATE_DIM[S.env]]
         env_ac = ac.T if S.cont else ac
-        S.state, S.elapsed, S.obs, rew[t], done[t] = E.step(S.env, S.state, S.elapsed, env_ac, ru, max_steps, f)
+        S.state, S.elapsed, raw, rew[t], done[t] = E.step(S.env, S.state, S.elapsed, env_ac, ru, max_steps, f)
+        if S.frames == 1:
+            S.obs = raw
+        else:       # drop the oldest frame, append the newest; a finished episode restarts with k copies (auto-reset)
+            shifted = np.concatenate([S.obs[S.env_ob:], raw], axis=0)
+            S.obs = np.where(done[t][None, :] != 0, np.tile(raw, (S.frames, 1)), shifted).astype(f)
         acs[t] = ac.T if S.cont else ac[None, :]
         logps[t] = lp
         ent_sum += float(np.sum(ent, dtype=np.float64))

@@ -126,3 +126,32 @@ def test_env_edge_cases(lib, dev):
     rc = lib.load().acx_env_step(9, 4, t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(),
                                  t.data_ptr(), None, 0, 0, 0, None, 0, None)
     assert rc == -1 and b"unknown env" in lib.load().acx_last_error()
+
+
+@pytest.mark.parametrize("ob,frames,n", [(3, 2, 1000), (4, 2, 77), (2, 4, 513), (6, 1, 64)])
+def test_frame_push_is_the_reference_framer(lib, dev, ob, frames, n):
+    """acx_frame_push over a sequence with random episode ends == Framer.full (A3C/process.py:36-43) per episode."""
+    from oracle.pathadv import framer_full
+    from gpu_util import dev_t
+    rng = np.random.default_rng(ob * 100 + frames)
+    T = 9
+    obs = rng.normal(size=(T + 1, ob, n)).astype(np.float32)
+    done = (rng.uniform(size=(T, n)) < 0.3).astype(np.uint8)
+    o_d, d_d = dev_t(obs, dev), dev_t(done, dev)
+    out = torch.full((T + 1, ob * frames, n), -7.0, device=dev)
+    s = lib.cur_stream()
+    lib.call("acx_frame_push", n, ob, frames, None, lib.ptr(o_d[0]), None, lib.ptr(out[0]), s)
+    for t in range(T):
+        lib.call("acx_frame_push", n, ob, frames, lib.ptr(out[t]), lib.ptr(o_d[t + 1]), lib.ptr(d_d[t]), lib.ptr(out[t + 1]), s)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    for e in range(0, n, max(1, n // 25)):                  # per env: split into episodes, stack with the reference rule
+        want, start = [], 0
+        for t in range(T + 1):
+            if t > 0 and done[t - 1, e]:
+                start = t
+            want.append(framer_full([obs[u, :, e] for u in range(start, t + 1)], frames)[-1])
+        np.testing.assert_array_equal(got[:, :, e], np.stack(want))
+    f = lib.load().acx_frame_push
+    assert f(8, ob, frames, out[0].data_ptr(), o_d[0].data_ptr(), None, out[0].data_ptr(), None) == -1      # aliasing
+    assert f(0, ob, frames, None, None, None, None, None) == 0

@@ -54,6 +54,33 @@ def test_first_iteration_matches_oracle(env_id, env, N, T, tensor_cores):
     np.testing.assert_allclose(tr.read_stats()["next_lr"], S.actor_lr, rtol=1e-6)
 
 
+@pytest.mark.parametrize("env_id,env,N,T", [("Pendulum-v0", E.PENDULUM, 256, 8), ("CartPole-v0", E.CARTPOLE, 192, 12)])
+def test_frame_stacking_matches_oracle(env_id, env, N, T):
+    """--frames 2 (Framer, A3C/process.py:25-43) on the fused path: stacked observations, 2 x ob_dim network inputs."""
+    S = a2c.A2CState(env, N, seed=31, frames=2)
+    tr = A2CTrainer(env_id, n_envs=N, horizon=T, seed=31, actor_params=S.actor.copy(), critic_params=S.critic.copy(),
+                    use_graph=False, max_episode_steps=5 if env != E.PENDULUM else 3, frames=2)
+    assert tr.ob == 2 * E.OBS_DIM[env]
+    for _ in range(2):                       # the second iteration starts from a stacked observation with history
+        tr.iteration()
+        torch.cuda.synchronize()
+        st = a2c.iteration(S, T=T, max_steps=5 if env != E.PENDULUM else 3)
+        _cmp_iteration(tr, st, env == E.PENDULUM)
+    assert tr.done.sum().item() > 0
+    ob = E.OBS_DIM[env]
+    o, d = tr.obs_buf.cpu().numpy(), tr.done.cpu().numpy()
+    for t in range(T):                       # Framer semantics, directly: shift within an episode, k copies at its start
+        cont = d[t] == 0
+        np.testing.assert_array_equal(o[t + 1, :ob][:, cont], o[t, ob:][:, cont])
+        np.testing.assert_array_equal(o[t + 1, :ob][:, ~cont], o[t + 1, ob:][:, ~cont])
+
+
+def test_frames_beyond_the_kernel_input_width_are_refused():
+    from actor_critic_algs_on_tensorflow_b200 import _lib
+    with pytest.raises(_lib.AcxError, match="at most 8 input features"):
+        A2CTrainer("Pendulum-v0", n_envs=64, horizon=2, frames=3)
+
+
 def test_graph_replay_equals_eager_launches():
     outs = []
     for use_graph in (False, True):

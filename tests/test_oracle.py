@@ -260,3 +260,20 @@ def test_a2c_iteration_runs_and_is_reproducible():
     S = a2c.A2CState(E.CARTPOLE, 32, seed=5)
     st = a2c.iteration(S, T=8)
     assert np.isfinite(st["actor_loss"]) and S.it == 1
+
+
+def test_a2c_rollout_stacks_frames_like_the_reference_framer():
+    """oracle/a2c.py with frames=2: every stacked observation equals Framer.full over the episode it belongs to."""
+    from oracle import a2c, envs as E
+    S = a2c.A2CState(E.CARTPOLE, 16, seed=5, frames=2)
+    assert S.ob_dim == 8 and S.obs.shape == (8, 16)
+    ro = a2c.rollout(S, 12, max_steps=4)
+    obs, done = ro["obs"], ro["done"]
+    assert done.sum() > 0
+    for e in range(16):
+        start = 0
+        for t in range(13):
+            if t > 0 and done[t - 1, e]:
+                start = t
+            raw = [obs[u, 4:, e] for u in range(start, t + 1)]          # newest frame = the raw observation
+            np.testing.assert_array_equal(obs[t, :, e], PA.framer_full(raw, 2)[-1])
