@@ -151,7 +151,40 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       if (tid < H3) acx_bulk_g2s(sm.S[buf] + tid * MS, g3 + (size_t)tid * ld, MT * 4, bar);
     };
     if ((int)blockIdx.x < ntiles && tile_is_bulk(blockIdx.x)) issue_x3(blockIdx.x, 0);
+    // act'(X2) of this thread's 64 features comes straight from the cache (coalesced loads) as two 32-bit masks.  The
+    // loads are software-pipelined so that none is waited for: the upper 32 of a tile are issued during the previous
+    // tile's layer-1 phase, the lower 32 at the start of the tile (they have until dX2 is done).
+    float xm[32];
+    auto load_x2 = [&](int tile, int q) {
+      const int row = tile / tpr, c = (tile % tpr) * MT + s;
+      const float* g2 = A.x2_in + ((size_t)row * H2 + half * 64 + q * 32) * ld + c;
+      const bool ok = tile < ntiles && c < A.n;
+      // volatile: the loads must be ISSUED here (the compiler would otherwise sink them to the pack, next to their use)
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        xm[e] = 0.f;
+        if (ok) asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(xm[e]) : "l"(g2 + (size_t)e * ld));
+      }
+    };
+    auto pack_x2 = [&]() {
+      unsigned int m = 0u;
+#pragma unroll
+      for (int e = 0; e < 32; ++e) m |= (xm[e] > 0.f ? 1u : 0u) << e;
+      return m;
+    };
+    load_x2(blockIdx.x, 1);
 
+    // rows of a staged tile (row r of S, MT floats) -> global rows by bulk-TMA stores, off the load/store pipe: the
+    // 64 + 64 KB of dPre3 / dPre2 a tile produces otherwise queue in front of every later global load of the SM
+    auto bulk_rows_out = [&](const float* src, float* dst, int nrows) {
+      if (tid < nrows) {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + (size_t)tid * ld),
+                     "r"(acx_smem_u32(src + tid * MS)), "r"(MT * 4)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    };
+    auto bulk_rows_read_done = [&]() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); };
 #ifdef ACX_CHAIN_PROF
     long long prof_[16] = {0}, last_ = clock64();
 #endif
@@ -163,6 +196,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       float* __restrict__ S = sm.S[buf];
       const bool live = s < valid;
       const size_t col = (size_t)n0 + s;
+      const bool bulk = tile_is_bulk(tile);         // full, 16-byte aligned rows: bulk-TMA in and out
       // the other buffer is idle since the end of the previous tile: fetch the next tile's X3 into it
       {
         const int next = tile + gridDim.x;
@@ -170,22 +204,17 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         if (next < ntiles && tid < MT && (next % tpr) * MT + tid < A.n)
           head_train_prefetch<HEAD>(A, nout, next / tpr, (size_t)(next % tpr) * MT + tid);
       }
-      // act'(X2) of this thread's 64 features straight from the cache (coalesced), as two 32-bit masks: the upper 32
-      // loads fly while the X3 tile lands, the lower 32 while the tensor cores form dX2
-      const float* g2 = A.x2_in + ((size_t)row * H2 + half * 64) * ld + col;
-      float xm[32];
       unsigned int m2[2];
-#pragma unroll
-      for (int e = 0; e < 32; ++e) xm[e] = live ? __ldg(g2 + (size_t)(32 + e) * ld) : 0.f;
-      if (tile_is_bulk(tile)) {
+      m2[1] = pack_x2();
+      load_x2(tile, 0);
+      PROF_MARK(12);
+      if (bulk) {
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[buf]), act_phase[buf] & 1u);
         ++act_phase[buf];
       } else {
         load_tile(S, A.x3_in + ((size_t)row * H3) * ld + n0, ld, H3, valid, vec_ok);
       }
-      m2[1] = 0u;
-#pragma unroll
-      for (int e = 0; e < 32; ++e) m2[1] |= (xm[e] > 0.f ? 1u : 0u) << e;
+      PROF_MARK(13);
       work_sync();
       PROF_MARK(0);
 
@@ -220,7 +249,8 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         }
       }
       PROF_MARK(2);
-      // ---------------------------------------------- dPre3: A operand + HBM stream (no barrier needed: reads only)
+      work_sync();                                  // head-layer gradients have read their X3 rows
+      // ---------------------------------------------- dPre3: A operand + HBM stream (staged in place over X3)
       {
         float dh[MAX_OUT];
 #pragma unroll
@@ -240,7 +270,10 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
             v[e] = acc * act_grad<LRELU>(v[e]);
           }
           a_store32_tt(tl, j0, v);
-          if (live) {
+          if (bulk) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) S[(j0 + e) * MS + s] = v[e];
+          } else if (live) {
             float* g = d3_out + ((size_t)row * H3 + j0) * ld + col;
 #pragma unroll
             for (int e = 0; e < 32; ++e) g[(size_t)e * ld] = v[e];
@@ -250,17 +283,19 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
-#pragma unroll
-      for (int e = 0; e < 32; ++e) xm[e] = live ? __ldg(g2 + (size_t)e * ld) : 0.f;
-      work_sync();                                  // every read of S as X3 is done: it may take the dPre1 blocks
+      if (bulk) fence_proxy_async();
+      work_sync();
+      if (bulk) bulk_rows_out(S, d3_out + ((size_t)row * H3) * ld + n0, H3);
       PROF_MARK(3);
       // ---------------------------------------------- dPre2 = dX2 * act'(X2): next A operand + HBM stream
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[0]), par);
       fence_after_sync();
       PROF_MARK(4);
-      m2[0] = 0u;
-#pragma unroll
-      for (int e = 0; e < 32; ++e) m2[0] |= (xm[e] > 0.f ? 1u : 0u) << e;
+      if (bulk) {                                   // dPre3 has left S: it takes dPre2 next
+        bulk_rows_read_done();
+        work_sync();
+      }
+      m2[0] = pack_x2();
 #pragma unroll 1
       for (int gq = 0; gq < 2; ++gq) {
         const unsigned int bits = m2[gq];
@@ -270,15 +305,26 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] *= ((bits >> e) & 1u) ? 1.0f : SLOPE;
         a_store32_tt(tl, k0, v);
-        if (live) {
+        if (bulk) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) S[(k0 + e) * MS + s] = v[e];
+        } else if (live) {
           float* g = d2_out + ((size_t)row * H2 + k0) * ld + col;
 #pragma unroll
           for (int e = 0; e < 32; ++e) g[(size_t)e * ld] = v[e];
         }
       }
+      PROF_MARK(14);
       tmem_wait_st();
       fence_before_sync();
       mbar_arrive1(&sm.a_ready);
+      if (bulk) {
+        fence_proxy_async();
+        work_sync();
+        bulk_rows_out(S, d2_out + ((size_t)row * H2) * ld + n0, H2);
+      }
+      PROF_MARK(15);
+      load_x2(tile + gridDim.x, 1);                 // next tile's upper 32 (zeros past the last tile)
       // this thread's observation (registers; also the shared copy layer1_grad reads), while dX1 is formed
       float ob_r[MAX_OB];
 #pragma unroll
@@ -292,6 +338,10 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       for (int h = 0; h < NB; ++h) {
         acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[1 + h]), par);
         fence_after_sync();
+        if (bulk && h == 0) {                       // dPre2 has left S: it takes the dPre1 blocks next
+          bulk_rows_read_done();
+          work_sync();
+        }
         PROF_MARK(6 + 3 * h);
 #pragma unroll 1
         for (int gq = 0; gq < 2; ++gq) {

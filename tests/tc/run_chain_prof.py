@@ -15,8 +15,9 @@ for _ in range(2):
     tr.iteration()
 torch.cuda.synchronize()
 lib = L.load()
-names = ["load+wait X3", "head", "head grads", "dPre3+sync", "wait MMA3", "dPre2", "wait MMA2 b0", "dPre1 b0", "l1grad b0",
-         "wait MMA2 b1", "dPre1 b1", "l1grad b1"]
+names = ["sync after X3 wait", "head", "head grads", "dPre3 + sync + row stores", "wait MMA3", "next-tile mask / obs loads",
+         "wait MMA2 b0", "dPre1 b0", "l1grad b0", "wait MMA2 b1", "dPre1 b1", "l1grad b1",
+         "tile start: X3 prefetch, mask pack + loads", "tile start: wait X3", "dPre2 loop", "dPre2: st-wait, arrive, row stores"]
 buf = (C.c_ulonglong * 16)()
 s = L.cur_stream()
 for which in ("actor", "critic"):
@@ -30,7 +31,7 @@ for which in ("actor", "critic"):
     torch.cuda.synchronize()
     lib.acx_chain_prof_read.argtypes = [C.c_void_p]
     lib.acx_chain_prof_read(buf)
-    tot = sum(buf[i] for i in range(12))
+    tot = sum(buf[i] for i in range(16))
     print(which, "total cycles", tot, "tiles ~", 20 * 512 / 148)
     for i, nm in enumerate(names):
-        print("  %-14s %9d  %5.1f%%  per tile %7.0f" % (nm, buf[i], 100.0 * buf[i] / tot, buf[i] / (20 * 512 / 148)))
+        print("  %-44s %9d  %5.1f%%  per tile %7.0f" % (nm, buf[i], 100.0 * buf[i] / tot, buf[i] / (20 * 512 / 148)))
