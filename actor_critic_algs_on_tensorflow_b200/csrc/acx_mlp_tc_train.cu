@@ -321,10 +321,22 @@ __global__ void __launch_bounds__(256) acx_grad_reduce_tc_kernel(const float* __
                                                                  float* __restrict__ grad,
                                                                  const double* __restrict__ loss_partial,
                                                                  float* __restrict__ stats, const float* __restrict__ opt,
-                                                                 int is_actor, double count) {
+                                                                 int is_actor, double count, int lane_major, int offW3,
+                                                                 int H3, int offW2, int H1) {
   for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < size; p += gridDim.x * blockDim.x) {
+    // lane_major: acx_wgrad_kernel keeps its dW3 / dW2 partials as it reads them from tensor memory (row r of a 128-row
+    // block = lane, column c): element (r, c) at ((c / 4) * 128 + r) * 4 + c % 4 of the region, so that its flushes are
+    // 512-byte coalesced
+    int q = p;
+    if (lane_major && p >= offW3 && p < offW3 + 128 * H3) {
+      const int r = (p - offW3) / H3, c = (p - offW3) % H3;
+      q = offW3 + ((c >> 2) * 128 + r) * 4 + (c & 3);
+    } else if (lane_major && p >= offW2 && p < offW2 + H1 * 128) {
+      const int k1 = (p - offW2) / 128, j = (p - offW2) % 128, r = k1 & 127, c = (k1 >> 7) * 128 + j;
+      q = offW2 + ((c >> 2) * 128 + r) * 4 + (c & 3);
+    }
     float acc = 0.f;
-    for (int cta = 0; cta < ncta; ++cta) acc += scratch[(size_t)cta * size + p];
+    for (int cta = 0; cta < ncta; ++cta) acc += scratch[(size_t)cta * size + q];
     grad[p] = acc;
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats != nullptr) {
@@ -412,7 +424,8 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
                   : launch_tt<128, 64, true, HEAD_CAT>(a, actor_packed, split, grid, st);
     if (rc) return rc;
     acx_grad_reduce_tc_kernel<<<(La.size + 255) / 256, 256, 0, st>>>(scr_a, grid, La.size, grad_actor, lossp_a, stats,
-                                                                    opt, 1, count);
+                                                                    opt, 1, count, split != nullptr, La.W3, ACX_A_H3,
+                                                                    La.W2, ACX_A_H1);
     ACX_LAUNCH_OK("acx_grad_reduce_tc_kernel(actor)");
   }
   if (critic) {
@@ -424,7 +437,8 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
     int rc = launch_tt<256, 128, false, HEAD_VALUE>(a, critic_packed, split, grid, st);
     if (rc) return rc;
     acx_grad_reduce_tc_kernel<<<(Lc.size + 255) / 256, 256, 0, st>>>(scr_c, grid, Lc.size, grad_critic, lossp_c, stats,
-                                                                    opt, 0, count);
+                                                                    opt, 0, count, split != nullptr, Lc.W3, ACX_C_H3,
+                                                                    Lc.W2, ACX_C_H1);
     ACX_LAUNCH_OK("acx_grad_reduce_tc_kernel(critic)");
   }
   return ACX_OK;

@@ -6,8 +6,11 @@
 // dPre2) and the activation cache (X2): the sample index is contiguous, i.e. both operands are K-major as they lie
 // in HBM.  X1 = act(obs W1 + b1) is not read but recomputed (ob_dim <= 8 FMAs per element) straight into the swizzled
 // operand layout.  Each persistent CTA owns the 128-sample tiles  blockIdx.x, +gridDim.x, ...  and keeps
-// its partial dW3 / dW2 in tensor memory (fp32, 128 + H1 columns) for the whole kernel; at the end they go to the CTA's
-// scratch row, which acx_grad_reduce sums in fixed order (bit-reproducible run to run).
+// its partial dW3 / dW2 in tensor memory (fp32).  The tensor core's accumulate truncates: over the ~3,300 accumulating
+// MMAs of a CTA's whole share the error reached 7.7e-5 of the result (measured against an fp64 product of the same
+// operands, tests/tc/run_wgrad_accuracy.py).  So the accumulators are double-buffered and flushed every WG_FLUSH
+// tiles: while the MMAs fill one buffer, warps 2-5 add the other into the CTA's scratch row with ordinary fp32
+// (round-to-nearest) adds; acx_grad_reduce then sums the rows in fixed order (bit-reproducible run to run).
 //   warp 0     producer: TMA tensor loads of [features x 32 samples] boxes, 128-byte swizzle, NSTAGE-deep ring
 //   warp 1     issuer:   per box 4 K-steps x 3 kind::tf32 MMAs (lo*hi, hi*lo, hi*hi) per 128-row block
 //   warps 2-9  splitters: lo = rna(x - trunc(x)) of every landed word into the stage's second buffer (the MMA itself
@@ -27,9 +30,13 @@ namespace {
 constexpr int WG_THREADS = 320;
 constexpr int BOX = 32;                    // samples per box row (128 bytes)
 constexpr int BLK = 128 * BOX;             // floats of a 128-row box
+#ifndef ACX_WG_FLUSH
+#define ACX_WG_FLUSH 8
+#endif
+constexpr int WG_FLUSH = ACX_WG_FLUSH;                // tiles (1,024 samples, 384 accumulating MMAs) per tensor-memory accumulation
 
 struct WgBars {
-  unsigned long long full[3], split[3], empty[3], done;
+  unsigned long long full[3], split[3], empty[3], dfull[2], dfree[2];
   unsigned int tmem_base;
   float W1[acxmlp::MAX_OB * 256];
   float b1[256];
@@ -79,7 +86,10 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       acx_mbar_init(reinterpret_cast<uint64_t*>(&B.split[i]), 256);
       acx_mbar_init(reinterpret_cast<uint64_t*>(&B.empty[i]), 1);
     }
-    acx_mbar_init(reinterpret_cast<uint64_t*>(&B.done), 1);
+    for (int i = 0; i < 2; ++i) {
+      acx_mbar_init(reinterpret_cast<uint64_t*>(&B.dfull[i]), 1);
+      acx_mbar_init(reinterpret_cast<uint64_t*>(&B.dfree[i]), 128);
+    }
     acx_mbar_fence_init();
   }
   fence_before_sync();
@@ -113,42 +123,97 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      unsigned int it = 0;
+      unsigned int it = 0, group = 0, used[2] = {0u, 0u};
       for (int phase = 0; phase < 2; ++phase) {
         const int nblk = phase == 0 ? 1 : NB;
         const uint32_t idesc = idesc_tf32(128, phase == 0 ? H3 : 128, false, false);
-        bool fresh = true;
+        if (phase == 1)                              // phase-1 buffers overlap phase-0's: every flush must be through
+          for (int b = 0; b < 2; ++b)
+            if (used[b]) acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.dfree[b]), (used[b] - 1u) & 1u);
+        int in_group = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
           const int n0 = (tile % tpr) * 128;
           const int nsub = (min(128, n - n0) + BOX - 1) / BOX;
+          const unsigned int buf = group & 1u;
+          const uint32_t dbase = tmem + (phase == 0 ? buf * 128u : buf * 256u);
+          if (in_group == 0 && used[buf]) {          // the buffer's previous contents have been added to the scratch row
+            acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.dfree[buf]), (used[buf] - 1u) & 1u);
+            fence_after_sync();
+          }
           for (int kk = 0; kk < nsub; ++kk, ++it) {
             const unsigned int slot = it % NSTAGE;
             acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.split[slot]), (it / NSTAGE) & 1u);
             fence_after_sync();
             const float* r = raw + (size_t)slot * Cfg::STAGE;
             const float* l = lo + (size_t)slot * Cfg::STAGE;
+            const bool fresh = in_group == 0 && kk == 0;
 #pragma unroll
             for (int ks = 0; ks < BOX / 8; ++ks) {
               const uint64_t bh = smem_desc_sw128(r + NB * BLK + ks * 8), bl = smem_desc_sw128(l + NB * BLK + ks * 8);
               for (int b = 0; b < nblk; ++b) {
                 const uint64_t ah = smem_desc_sw128(r + b * BLK + ks * 8), al = smem_desc_sw128(l + b * BLK + ks * 8);
-                const uint32_t d = tmem + (phase == 0 ? 0u : 128u + 128u * (uint32_t)b);
+                const uint32_t d = dbase + 128u * (uint32_t)b;
                 mma_tf32(d, al, bh, idesc, !(fresh && ks == 0));
                 mma_tf32(d, ah, bl, idesc, true);
                 mma_tf32(d, ah, bh, idesc, true);
               }
             }
-            fresh = false;
             commit(reinterpret_cast<uint64_t*>(&B.empty[slot]));
+          }
+          if (++in_group == WG_FLUSH || tile + (int)gridDim.x >= ntiles) {       // group complete: hand the buffer over
+            commit(reinterpret_cast<uint64_t*>(&B.dfull[buf]));
+            ++used[buf];
+            ++group;
+            in_group = 0;
           }
         }
       }
-      commit(reinterpret_cast<uint64_t*>(&B.done));
     }
   } else {
     const int t = tid - 64;                       // 0..255
     const int c4 = t & 7, r0 = t >> 3;            // this thread's 16-byte chunk and its rows r0 + 32 m of every box
     unsigned int it = 0;
+    // warps 2-5 also flush completed accumulation groups: tensor memory -> (+)= this CTA's scratch row
+    unsigned int group = 0, fl_used[2] = {0u, 0u};
+    int pend_phase = -1, pend_first = 0;
+    unsigned int pend_buf = 0;
+    float* scr_row = scratch + (size_t)blockIdx.x * scr_stride;
+    // One 32-column slice per call (so that a flush is spread over the following boxes instead of stalling the ring);
+    // the partials are kept lane-major -- element (r, c) of the region at ((c / 4) * 128 + r) * 4 + c % 4 -- so that a
+    // warp's float4 accesses are 512 contiguous bytes.  Returns true when the group is through.
+    int pend_c0 = 0;
+    auto flush_slice = [&]() {
+      if (pend_c0 == 0) {
+        acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.dfull[pend_buf]), fl_used[pend_buf] & 1u);
+        ++fl_used[pend_buf];
+        fence_after_sync();
+      }
+      const int r = (warp & 3) * 32 + lane;                   // TMEM lane = row of the A block
+      const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (pend_phase == 0 ? pend_buf * 128u : pend_buf * 256u);
+      const int ncol = pend_phase == 0 ? H3 : NB * 128;
+      float v[32];
+      tmem_ld32(tl + (uint32_t)pend_c0, v);
+      float4* p = reinterpret_cast<float4*>(scr_row + (pend_phase == 0 ? offW3 : offW2)) + (pend_c0 >> 2) * 128 + r;
+      float4 o[8];
+      if (!pend_first) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = p[i * 128];
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float4 a = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        if (!pend_first) { a.x += o[i].x; a.y += o[i].y; a.z += o[i].z; a.w += o[i].w; }
+        p[i * 128] = a;
+      }
+      pend_c0 += 32;
+      if (pend_c0 < ncol) return false;
+      fence_before_sync();
+      mbar_arrive(&B.dfree[pend_buf]);
+      pend_phase = -1;
+      pend_c0 = 0;
+      return true;
+    };
+    auto flush = [&]() { while (!flush_slice()) {} };
     // observations of this thread's 4 samples of box (tile, kk); zeros beyond the batch
     auto load_obs = [&](int tile, int kk, float4 (&o)[OBM]) {
       const int row = tile / tpr, col = (tile % tpr) * 128 + kk * BOX + 4 * c4;
@@ -163,6 +228,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       float bacc[4] = {0.f, 0.f, 0.f, 0.f};       // bias-gradient partials of rows r0 + 32 m (chunk c4 of every box)
       float4 o[OBM], o_next[OBM];
       if (phase == 1) load_obs(blockIdx.x, 0, o_next);
+      int in_group = 0, groups_done = 0;          // within this phase
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int n0 = (tile % tpr) * 128;
         const int nsub = (min(128, n - n0) + BOX - 1) / BOX;
@@ -217,8 +283,21 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             }
           fence_proxy_async();
           mbar_arrive(&B.split[slot]);
+          if (warp < 6 && pend_phase >= 0) flush_slice();     // a slice of the previous group per box
+        }
+        if (++in_group == WG_FLUSH || tile + (int)gridDim.x >= ntiles) {
+          if (warp < 6) {
+            if (pend_phase >= 0) flush();
+            pend_phase = phase; pend_buf = group & 1u; pend_first = groups_done == 0 ? 1 : 0;
+          }
+          ++group;
+          ++groups_done;
+          in_group = 0;
         }
       }
+      // the phase's last group now (the next phase's accumulators overlap this phase's: the issuer waits for it, and the
+      // ring is too short to feed a sliced flush meanwhile)
+      if (warp < 6 && pend_phase >= 0) flush();
       // the 8 threads of a row (consecutive lanes) fold their partials; fixed order -> reproducible
       float* scr = scratch + (size_t)blockIdx.x * scr_stride + (phase == 0 ? offb3 : offb2);
 #pragma unroll
@@ -230,28 +309,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
         if (c4 == 0 && r0 + 32 * m < brows) scr[r0 + 32 * m] = v;
       }
     }
-    if (warp < 6) {
-      // ------------------------------------------------ epilogue: tensor memory -> this CTA's scratch row
-      acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.done), 0);
-      fence_after_sync();
-      const int r = (warp & 3) * 32 + lane;                   // TMEM lane = row of the A block
-      const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-      float* scr = scratch + (size_t)blockIdx.x * scr_stride;
-      float v[32];
-      for (int c0 = 0; c0 < H3; c0 += 32) {
-        tmem_ld32(tl + (uint32_t)c0, v);
-        float4* p = reinterpret_cast<float4*>(scr + offW3 + r * H3 + c0);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) p[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-      }
-      for (int b = 0; b < NB; ++b)
-        for (int c0 = 0; c0 < 128; c0 += 32) {
-          tmem_ld32(tl + 128u + 128u * (uint32_t)b + (uint32_t)c0, v);
-          float4* p = reinterpret_cast<float4*>(scr + offW2 + (b * 128 + r) * 128 + c0);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) p[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-        }
-    }
+    if (warp < 6 && pend_phase >= 0) flush();                 // the last group
   }
   fence_before_sync();
   __syncthreads();

@@ -189,3 +189,43 @@ def test_tc_backward_rejects_bad_arguments(lib, dev):
     assert call(k.pa.data_ptr(), k.ax2.data_ptr(), nbytes=1024) == -1 and b"workspace" in lib.load().acx_last_error()
     assert call(k.pa.data_ptr(), k.ax2.data_ptr()) == 0
     torch.cuda.synchronize()
+
+
+def test_tc_backward_at_the_bench_size_is_linear_in_the_batch_and_agrees_with_ffma(lib, dev):
+    """BASELINE configs[2] size (20 x 65,536 samples), where the oracle is too slow: (i) the mean gradient of the batch is
+    the mean of the mean gradients of its two column halves (each run separately through the same entry point), (ii) the
+    all-FFMA cached kernel gives the same gradients.  The bar is looser than at oracle sizes on purpose: with random-sign
+    advantages the mean gradient of 1.3 M samples is a residual ~ 1/sqrt(B) of its terms, so the ~1e-6 relative rounding of
+    the terms (fp32 FMA chains in one kernel, 3xTF32 products in the other) shows up ~1e-3 x larger relative to the
+    result; 3e-4 of each tensor's max."""
+    BAR_FULL = 3e-4
+    rows, n = 20, 65536
+    full = Case(lib, dev, True, 3, 1, rows, n, 77)
+    ga, gc, st = full.run("tc")
+    fa, fc, fs = full.run("ffma")
+    halves = []
+    for h in range(2):
+        sl = slice(h * n // 2, (h + 1) * n // 2)
+        k = Case.__new__(Case)
+        k.__dict__.update(full.__dict__)
+        k.n, k.B = n // 2, rows * n // 2
+        cut = lambda t: t[..., sl].contiguous()
+        k.o, k.acs_d, k.adv_d, k.lp_d, k.tg_d = (cut(t) for t in (full.o, full.acs_d, full.adv_d, full.lp_d, full.tg_d))
+        k.ax2, k.ax3, k.cx2, k.cx3 = (cut(t) for t in (full.ax2, full.ax3, full.cx2, full.cx3))
+        k.nbytes = lib.load().acx_loss_backward_tc_workspace_bytes(3, 1, 1, rows, n // 2)
+        k.ws = torch.empty(k.nbytes, device=dev, dtype=torch.uint8)
+        halves.append(k.run("tc"))
+    worst = {}
+    for name, lay, got, ffma, i in (("actor", full.lay, ga, fa, 0), ("critic", full.clay, gc, fc, 1)):
+        mean_halves = 0.5 * (halves[0][i].astype(np.float64) + halves[1][i].astype(np.float64))
+        for key, o, s in P.items(lay):
+            sz = int(np.prod(s))
+            scale = np.abs(ffma[o:o + sz]).max()
+            worst[(name, key)] = (np.abs(got[o:o + sz] - ffma[o:o + sz]).max() / scale,
+                                  np.abs(got[o:o + sz] - mean_halves[o:o + sz]).max() / scale)
+    print({k: "%.2e %.2e" % v for k, v in worst.items()})
+    for k, (e_ffma, e_lin) in worst.items():
+        assert e_ffma <= BAR_FULL and e_lin <= BAR_FULL, (k, e_ffma, e_lin)
+    np.testing.assert_array_equal(st, fs)
+    np.testing.assert_allclose(st[3], 0.5 * (halves[0][2][3] + halves[1][2][3]), rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(st[4], 0.5 * (halves[0][2][4] + halves[1][2][4]), rtol=1e-5)
