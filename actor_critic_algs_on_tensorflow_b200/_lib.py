@@ -61,6 +61,7 @@ SIGNATURES = {
     "acx_loss_backward_gauss_cached": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_loss_backward_cat_cached": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_frame_push": (_i, [_i, _i, _i, _p, _p, _p, _p, _p]),
+    "acx_activation_cache_floats": (_sz, [_i, _i, _i]),
     "acx_tc_packed_bwd_floats": (_sz, [_i, _i, _i, _i]),
     "acx_loss_backward_tc_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "acx_tc_pack_weights_bwd": (_i, [_i, _p, _i, _i, _i, _p, _p]),

@@ -69,20 +69,20 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
     const bool vec_ok = (A.n & 3) == 0;          // tile rows start on 16-byte boundaries of the cache
     if (REUSE) {
       // ---------------------------------------------- layers 2 and 3 come from the activation cache
-      const float* g2 = A.x2_in + ((size_t)row * H2) * A.n + n0;
-      const float* g3 = A.x3_in + ((size_t)row * H3) * A.n + n0;
-      if (vec_ok && valid == MT) {
+      const float* g2 = A.x2_in + cache_tile_off(tile, H2);
+      const float* g3 = A.x3_in + cache_tile_off(tile, H3);
+      if (valid == MT) {
         // full tile: every row is 512 contiguous, 16-byte aligned bytes -> one bulk-TMA copy per row, all in flight
         uint64_t* bar = reinterpret_cast<uint64_t*>(&sm.bar_act);
         if (tid == 0) acx_mbar_expect_tx(bar, (uint32_t)((H2 + H3) * MT * 4));
         __syncthreads();      // the expect_tx is registered before any copy can complete; X2/X3 are idle by now
-        if (tid < H2) acx_bulk_g2s(sm.X2 + tid * MS, g2 + (size_t)tid * A.n, MT * 4, bar);
-        else if (tid - H2 < H3) acx_bulk_g2s(sm.X3 + (tid - H2) * MS, g3 + (size_t)(tid - H2) * A.n, MT * 4, bar);
+        if (tid < H2) acx_bulk_g2s(sm.X2 + tid * MS, g2 + (size_t)tid * MT, MT * 4, bar);
+        else if (tid - H2 < H3) acx_bulk_g2s(sm.X3 + (tid - H2) * MS, g3 + (size_t)(tid - H2) * MT, MT * 4, bar);
         acx_mbar_wait(bar, act_phase & 1u);
         ++act_phase;
       } else {
-        load_tile(sm.X2, g2, (size_t)A.n, H2, valid, vec_ok);
-        load_tile(sm.X3, g3, (size_t)A.n, H3, valid, vec_ok);
+        load_tile(sm.X2, g2, (size_t)MT, H2, valid, true);
+        load_tile(sm.X3, g3, (size_t)MT, H3, valid, true);
       }
       __syncthreads();
     } else {
@@ -99,8 +99,8 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
           __syncthreads();
         }
       }
-      f_store<8, LRELU>(sm.X2, sm.b2, acc, c, A.x2_out ? A.x2_out + ((size_t)row * H2) * A.n + n0 : nullptr,
-                        (size_t)A.n, valid, vec_ok);
+      f_store<8, LRELU>(sm.X2, sm.b2, acc, c, A.x2_out ? A.x2_out + cache_tile_off(tile, H2) : nullptr, (size_t)MT, valid,
+                        true);
     }
     __syncthreads();
     // ------------------------------------------------ forward: layer 3
@@ -112,8 +112,8 @@ __global__ void __launch_bounds__(NT, 1) acx_mlp_kernel(const Args A) {
         f_stage<TJ3>(slot, sm.X2 + c3 * CH * MS, acc, c);
         __syncthreads();
       }
-      f_store<TJ3, LRELU>(sm.X3, sm.b3, acc, c, A.x3_out ? A.x3_out + ((size_t)row * H3) * A.n + n0 : nullptr,
-                          (size_t)A.n, valid, vec_ok);
+      f_store<TJ3, LRELU>(sm.X3, sm.b3, acc, c, A.x3_out ? A.x3_out + cache_tile_off(tile, H3) : nullptr, (size_t)MT,
+                          valid, true);
     }
     __syncthreads();
     }

@@ -69,8 +69,10 @@ struct Args {
   float* scratch;            // per-CTA gradient partials [grid][L.size]
   double* loss_partial;      // per-CTA loss sums [grid][4]
   const float* wT;           // transposed weights: W3T [H3][128] then W2T [H1/128][128][128]
-  // activation cache (SoA like obs): x2[rows][128][n], x3[rows][H3][n].  Forward kernels may write it, the
-  // training kernel may read it instead of recomputing layers 2 and 3 (valid while the weights are unchanged).
+  // activation cache, tile-blocked: x2[rows][tiles][128][128], x3[rows][tiles][H3][128] (tiles = ceil(n / 128) blocks of
+  // 128 samples, a block is one contiguous F x 512-byte region; samples beyond n hold zeros).  Forward kernels may
+  // write it, the training kernels may read it instead of recomputing layers 2 and 3 (valid while the weights are
+  // unchanged).  A tile's rows lie 512 bytes apart instead of 4 n bytes: one DRAM page / TLB entry per tile.
   float* x2_out;
   float* x3_out;
   const float* x2_in;
@@ -94,6 +96,12 @@ struct Smem {
   unsigned long long bar[NSLOT];
   unsigned long long bar_act;      // arrival of a cached activation tile (bulk-TMA row copies)
 };
+
+// float offset of tile `tile` (= row * tiles_per_row + tile_in_row) of a tile-blocked [..][F][128] array
+__host__ __device__ inline size_t cache_tile_off(int tile, int F) { return (size_t)tile * F * MT; }
+__host__ __device__ inline size_t cache_floats(int rows, int F, int n) {
+  return (size_t)(rows > 0 ? rows : 0) * (size_t)((n + MT - 1) / MT) * F * MT;
+}
 
 template <bool LRELU> __device__ inline float act_fn(float x) {
   // lrelu exactly as A3C/policies.py:9-10: 0.8*relu(x) + 0.2*x
@@ -228,16 +236,14 @@ __device__ inline void f_store(float* __restrict__ OUT, const float* __restrict_
       o.w = act_fn<LRELU>(__fadd_rn(acc[jj][4 * h + 3], bj));
       const int m = 4 * c.b + 64 * h;
       *reinterpret_cast<float4*>(OUT + j * MS + m) = o;
-      if (gout != nullptr) {
-        float* g = gout + (size_t)j * gld + m;
-        if (vec_ok && m + 3 < valid) {
-          *reinterpret_cast<float4*>(g) = o;
-        } else {
-          if (m + 0 < valid) g[0] = o.x;
-          if (m + 1 < valid) g[1] = o.y;
-          if (m + 2 < valid) g[2] = o.z;
-          if (m + 3 < valid) g[3] = o.w;
-        }
+      if (gout != nullptr) {          // cache tile (always whole and 16-byte aligned): zeros beyond the batch
+        (void)vec_ok;
+        float4 z = o;
+        if (m + 0 >= valid) z.x = 0.f;
+        if (m + 1 >= valid) z.y = 0.f;
+        if (m + 2 >= valid) z.z = 0.f;
+        if (m + 3 >= valid) z.w = 0.f;
+        *reinterpret_cast<float4*>(gout + (size_t)j * gld + m) = z;
       }
     }
   }

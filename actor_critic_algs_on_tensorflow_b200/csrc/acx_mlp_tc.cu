@@ -253,10 +253,10 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         tmem_ld32(tl + TC_D2 + (uint32_t)j0, v);
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b2[j0 + e]));
-        if (A.x2_out != nullptr && live) {
-          float* g2 = A.x2_out + ((size_t)row * H2 + j0) * A.n + col;
+        if (A.x2_out != nullptr) {                 // tile-blocked cache; zeros beyond the batch
+          float* g2 = A.x2_out + cache_tile_off(tile, H2) + (size_t)j0 * MT + s;
 #pragma unroll
-          for (int e = 0; e < 32; ++e) g2[(size_t)e * A.n] = v[e];
+          for (int e = 0; e < 32; ++e) g2[e * MT] = live ? v[e] : 0.f;
         }
         if (basic) {
 #pragma unroll
@@ -277,10 +277,10 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         tmem_ld32(tl + TC_D3 + (uint32_t)j0, v);
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b3[j0 + e]));
-        if (A.x3_out != nullptr && live) {
-          float* g3 = A.x3_out + ((size_t)row * H3 + j0) * A.n + col;
+        if (A.x3_out != nullptr) {
+          float* g3 = A.x3_out + cache_tile_off(tile, H3) + (size_t)j0 * MT + s;
 #pragma unroll
-          for (int e = 0; e < 32; ++e) g3[(size_t)e * A.n] = v[e];
+          for (int e = 0; e < 32; ++e) g3[e * MT] = live ? v[e] : 0.f;
         }
         if (!basic) {
 #pragma unroll

@@ -133,26 +133,26 @@ __global__ void __launch_bounds__(TT_NT, 1) acx_mlp_tc_train_kernel(const Args A
       const int row = tile / tpr, n0 = (tile % tpr) * MT;
       const int valid = min(MT, A.n - n0);
       const unsigned int par = tiles_done & 1u;
-      const bool bulk = vec_ok && valid == MT;       // full, 16-byte aligned rows: bulk-TMA loads and stores
+      const bool bulk = valid == MT;                 // full tile: bulk-TMA row copies (the cache is tile-blocked)
       work_sync();                                   // previous tile is done with every shared buffer
       for (int idx = tid; idx < ob * MT; idx += TT_WORK) {
         const int i = idx / MT, m = idx % MT;
         sm.obs[idx] = (m < valid) ? A.obs[((size_t)row * ob + i) * A.n + n0 + m] : 0.f;
       }
       {
-        const float* g2 = A.x2_in + ((size_t)row * H2) * A.n + n0;
-        const float* g3 = A.x3_in + ((size_t)row * H3) * A.n + n0;
+        const float* g2 = A.x2_in + cache_tile_off(tile, H2);
+        const float* g3 = A.x3_in + cache_tile_off(tile, H3);
         if (bulk) {
           uint64_t* bar = reinterpret_cast<uint64_t*>(&sm.bar_act);
           if (tid == 0) acx_mbar_expect_tx(bar, (uint32_t)((H2 + H3) * MT * 4));
           work_sync();
-          if (tid < H2) acx_bulk_g2s(sm.X2 + tid * MS, g2 + (size_t)tid * A.n, MT * 4, bar);
-          else if (tid - H2 < H3) acx_bulk_g2s(sm.X3 + (tid - H2) * MS, g3 + (size_t)(tid - H2) * A.n, MT * 4, bar);
+          if (tid < H2) acx_bulk_g2s(sm.X2 + tid * MS, g2 + (size_t)tid * MT, MT * 4, bar);
+          else if (tid - H2 < H3) acx_bulk_g2s(sm.X3 + (tid - H2) * MS, g3 + (size_t)(tid - H2) * MT, MT * 4, bar);
           acx_mbar_wait(bar, act_phase & 1u);
           ++act_phase;
         } else {
-          load_tile(sm.X2, g2, (size_t)A.n, H2, valid, vec_ok);
-          load_tile(sm.X3, g3, (size_t)A.n, H3, valid, vec_ok);
+          load_tile(sm.X2, g2, (size_t)MT, H2, valid, true);
+          load_tile(sm.X3, g3, (size_t)MT, H3, valid, true);
         }
       }
       work_sync();
@@ -366,9 +366,8 @@ int launch_tt(const Args& a, const float* packed, float* split, int grid, cudaSt
     ACX_LAUNCH_OK("acx_mlp_tc_train_kernel");
     return ACX_OK;
   }
-  const size_t bn = (size_t)a.rows * (size_t)a.n;
-  float* d3 = split;
-  float* d2 = d3 + bn * H3;
+  float* d3 = split;                                   // tile-blocked like the activation cache
+  float* d2 = d3 + cache_floats(a.rows, H3, a.n);
   int rc = acx_tc_chain_launch(a, packed, d3, d2, HEAD, grid, st);
   if (rc) return rc;
   AcxWgradArgs w;
@@ -446,10 +445,14 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
 
 }  // namespace
 
+extern "C" size_t acx_activation_cache_floats(int rows, int features, int n) {
+  return cache_floats(rows, features > 0 ? features : 0, n > 0 ? n : 0);
+}
+
 extern "C" size_t acx_loss_backward_tc_workspace_bytes(int ob_dim, int num_ac, int cont, int rows, int n) {
   const size_t base_bytes = (acx_loss_backward_workspace_bytes(ob_dim, num_ac, cont) + 255) & ~(size_t)255;
   const size_t feat = (size_t)(ACX_C_H3 > ACX_A_H3 ? ACX_C_H3 : ACX_A_H3) + H2;      // dPre3 + dPre2 of one network
-  return base_bytes + feat * (size_t)(rows > 0 ? rows : 0) * (size_t)(n > 0 ? n : 0) * sizeof(float);
+  return base_bytes + cache_floats(rows, (int)feat, n) * sizeof(float);
 }
 
 extern "C" size_t acx_tc_packed_bwd_floats(int net, int ob_dim, int num_ac, int cont) {

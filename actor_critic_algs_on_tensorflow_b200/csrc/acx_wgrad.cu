@@ -115,8 +115,9 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             uint64_t* full = reinterpret_cast<uint64_t*>(&B.full[slot]);
             acx_mbar_expect_tx(full, (uint32_t)(((phase == 0 ? 128 : 0) + brows) * BOX * 4));
             float* dst = raw + (size_t)slot * Cfg::STAGE;
-            if (phase == 0) tma_load_2d(dst, &mapX2, n0 + kk * BOX, row * 128, full);      // phase 1: X1 is generated
-            tma_load_2d(dst + NB * BLK, mB, n0 + kk * BOX, row * brows, full);
+            (void)row;
+            if (phase == 0) tma_load_2d(dst, &mapX2, kk * BOX, tile * 128, full);          // phase 1: X1 is generated
+            tma_load_2d(dst + NB * BLK, mB, kk * BOX, tile * brows, full);
           }
         }
       }
@@ -319,10 +320,11 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
 template <int H1, int H3, bool LRELU, int OBM>
 int launch_wgrad(const AcxWgradArgs& a, cudaStream_t st) {
   CUtensorMap mX2, mD3, mD2;
-  const uint64_t pitch = (uint64_t)a.n * 4;
-  int rc = acx_tmap_2d(&mX2, a.x2, (uint64_t)a.n, (uint64_t)a.rows * 128, pitch, BOX, 128);
-  if (!rc) rc = acx_tmap_2d(&mD3, a.d3, (uint64_t)a.n, (uint64_t)a.rows * H3, pitch, BOX, H3);
-  if (!rc) rc = acx_tmap_2d(&mD2, a.d2, (uint64_t)a.n, (uint64_t)a.rows * 128, pitch, BOX, 128);
+  // tile-blocked arrays (activation cache, dPre streams): [tiles * F rows][128 samples]
+  const uint64_t tiles = (uint64_t)a.rows * (uint64_t)((a.n + 127) / 128);
+  int rc = acx_tmap_2d(&mX2, a.x2, 128, tiles * 128, 512, BOX, 128);
+  if (!rc) rc = acx_tmap_2d(&mD3, a.d3, 128, tiles * H3, 512, BOX, H3);
+  if (!rc) rc = acx_tmap_2d(&mD2, a.d2, 128, tiles * 128, 512, BOX, 128);
   ACX_REQUIRE(rc == 0, "acx_wgrad: cuTensorMapEncodeTiled failed (%d) for rows=%d n=%d", rc, a.rows, a.n);
   auto kern = acx_wgrad_kernel<H1, H3, LRELU, OBM>;
   ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgCfg<H1>::SMEM));

@@ -134,11 +134,12 @@ class A2CTrainer:
         self.ws_bwd = torch.empty(self.ws_bwd_bytes, device=d, dtype=torch.uint8)
         self.kl_part = torch.zeros(L.load().acx_kl_workspace_bytes() // 8, device=d, dtype=torch.float64)
         self.kl_blocks = ctypes.c_int(0)
-        if self.cache:
-            self.ax2 = torch.empty((T, 128, N), device=d, dtype=f32)
-            self.ax3 = torch.empty((T, 64, N), device=d, dtype=f32)
-            self.cx2 = torch.empty((T + 1, 128, N), device=d, dtype=f32)
-            self.cx3 = torch.empty((T + 1, 128, N), device=d, dtype=f32)
+        if self.cache:      # tile-blocked [rows][ceil(N/128)][features][128]; one row of the 2-D tensor = one time step
+            per = lambda feat: L.load().acx_activation_cache_floats(1, feat, N)
+            self.ax2 = torch.empty((T, per(128)), device=d, dtype=f32)
+            self.ax3 = torch.empty((T, per(64)), device=d, dtype=f32)
+            self.cx2 = torch.empty((T + 1, per(128)), device=d, dtype=f32)
+            self.cx3 = torch.empty((T + 1, per(128)), device=d, dtype=f32)
         self.packed_a = torch.zeros(L.load().acx_tc_packed_floats(0, self.ob, self.num_ac, int(self.cont)), device=d)
         self.packed_c = torch.zeros(L.load().acx_tc_packed_floats(1, self.ob, 1, 0), device=d)
         self.packed_bwd_a = torch.zeros(L.load().acx_tc_packed_bwd_floats(0, self.ob, self.num_ac, int(self.cont)), device=d)

@@ -150,10 +150,16 @@ int acx_value_forward(const float* critic, int ob_dim, int rows, int n, const fl
 
 /* Activation cache.  The reference makes ONE update per batch, on the weights that produced the batch
  * (A3C/process.py:221-258), so the hidden activations the rollout and value passes compute are exactly what
- * the update's forward pass would recompute.  The *_cached forwards also write them -- x2_out[rows][128][n]
- * (second hidden layer) and x3_out[rows][64 actor | 128 critic][n] -- and acx_loss_backward_*_cached reads
- * them instead of re-running those two GEMMs (650 k -> 500 k FLOP per env-step).  Results are
- * bit-identical to the recomputing entry points. */
+ * the update's forward pass would recompute.  The *_cached forwards also write them -- x2_out (second hidden
+ * layer, 128 features) and x3_out (third, 64 actor | 128 critic) -- and acx_loss_backward_*_cached reads them
+ * instead of re-running those two GEMMs (650 k -> 500 k FLOP per env-step).  Results are
+ * bit-identical to the recomputing entry points.
+ * Layout: tile-blocked, [rows][ceil(n / 128)][features][128] fp32 -- the 128-sample tile the kernels work on is one
+ * contiguous features x 512-byte block (one DRAM page / TLB entry per tile instead of `features` rows 4 n bytes
+ * apart); samples beyond n are written as zeros.  Size: acx_activation_cache_floats(rows, features, n) floats,
+ * 16-byte aligned.  A forward call with rows = 1 on row r of a [R]-row cache writes at
+ * cache + r * acx_activation_cache_floats(1, features, n). */
+size_t acx_activation_cache_floats(int rows, int features, int n);
 int acx_policy_forward_sample_gauss_cached(const float* actor, int ob_dim, int ac_dim, float ac_scale, int rows,
                                            int n, const float* obs, const float* eps, uint64_t seed,
                                            uint64_t index0, uint32_t step0, const uint32_t* step_base,
@@ -275,9 +281,9 @@ int acx_loss_backward_cat_cached(const float* actor, const float* critic, int ob
  * acx_tc_pack_weights_bwd() and re-filled whenever the parameters change.  The activation cache is required.
  * Gradients agree with acx_loss_backward_*_cached to 3xTF32 accuracy, not bit for bit.
  * Workspace: with at least acx_loss_backward_workspace_bytes() the weight-gradient products run as fp32 FFMA
- * inside the same kernel; with at least acx_loss_backward_tc_workspace_bytes(rows, n) (room for dPre3, dPre2 and the
- * layer-1 activations of one network, [rows][feature][n] fp32) and n % 4 == 0 they run on the tensor cores too, in a
- * second kernel per network (acx_wgrad_kernel: TMA tensor loads, 128-byte swizzle, accumulators in tensor memory). */
+ * inside the same kernel; with at least acx_loss_backward_tc_workspace_bytes(rows, n) (room for dPre3 and dPre2 of
+ * one network, tile-blocked like the cache) and n % 4 == 0 they run on the tensor cores too, in a second kernel
+ * per network (acx_wgrad_kernel: TMA tensor loads, 128-byte swizzle, accumulators in tensor memory). */
 size_t acx_loss_backward_tc_workspace_bytes(int ob_dim, int num_ac, int cont, int rows, int n);
 size_t acx_tc_packed_bwd_floats(int net, int ob_dim, int num_ac, int cont);
 int acx_tc_pack_weights_bwd(int net, const float* params, int ob_dim, int num_ac, int cont, float* packed,

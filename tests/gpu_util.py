@@ -52,3 +52,11 @@ def dev_t(x, dev, dtype=None):
 def rel_err(a, b):
     a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
     return np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
+
+
+def act_cache(lib, dev, rows, features, n):
+    """Zeroed activation-cache array in the library's tile-blocked layout, viewed [rows][tiles][features][128]."""
+    total = lib.load().acx_activation_cache_floats(rows, features, n)
+    tiles = (n + 127) // 128
+    assert total == rows * tiles * features * 128
+    return torch.zeros(total, device=dev).view(rows, tiles, features, 128)

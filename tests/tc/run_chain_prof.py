@@ -7,7 +7,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspa
 import torch  # noqa: E402
 from actor_critic_algs_on_tensorflow_b200 import _lib as L  # noqa: E402
 
-L.LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libacx_prof.so")
+L.LIB_PATH = os.environ.get("ACX_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libacx_prof.so")
 from actor_critic_algs_on_tensorflow_b200.trainer import A2CTrainer  # noqa: E402
 
 tr = A2CTrainer("Pendulum-v0", n_envs=65536, horizon=20, seed=12321, use_graph=False)

@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import policies as P
-from gpu_util import dev_t, random_weights, rel_err, soa
+from gpu_util import act_cache, dev_t, random_weights, rel_err, soa
 from test_gpu_backward import make_opt
 
 pytestmark = pytest.mark.gpu
@@ -49,8 +49,8 @@ class Case:
         self.a, self.c = dev_t(self.actor, dev), dev_t(self.critic, dev)
         self.o = dev_t(np.stack([soa(x) for x in self.obs]), dev)
         H3a = 64
-        self.ax2, self.ax3 = torch.zeros((rows, 128, n), device=dev), torch.zeros((rows, H3a, n), device=dev)
-        self.cx2, self.cx3 = torch.zeros((rows, 128, n), device=dev), torch.zeros((rows, 128, n), device=dev)
+        self.ax2, self.ax3 = act_cache(lib, dev, rows, 128, n), act_cache(lib, dev, rows, H3a, n)
+        self.cx2, self.cx3 = act_cache(lib, dev, rows, 128, n), act_cache(lib, dev, rows, 128, n)
         s = lib.cur_stream()
         lp = torch.empty((rows, n), device=dev)
         if cont:
@@ -194,11 +194,11 @@ def test_tc_backward_rejects_bad_arguments(lib, dev):
 def test_tc_backward_at_the_bench_size_is_linear_in_the_batch_and_agrees_with_ffma(lib, dev):
     """BASELINE configs[2] size (20 x 65,536 samples), where the oracle is too slow: (i) the mean gradient of the batch is
     the mean of the mean gradients of its two column halves (each run separately through the same entry point), (ii) the
-    all-FFMA cached kernel gives the same gradients.  The bar is looser than at oracle sizes on purpose: with random-sign
-    advantages the mean gradient of 1.3 M samples is a residual ~ 1/sqrt(B) of its terms, so the ~1e-6 relative rounding of
-    the terms (fp32 FMA chains in one kernel, 3xTF32 products in the other) shows up ~1e-3 x larger relative to the
-    result; 3e-4 of each tensor's max."""
-    BAR_FULL = 3e-4
+    all-FFMA cached kernel gives the same gradients.  Bar: 3e-5 of each tensor's max -- with random-sign advantages the
+    mean gradient of 1.3 M samples is a residual ~ 1/sqrt(B) of its terms, so the ~1e-6 rounding of the terms (fp32 FMA
+    chains in one kernel, 3xTF32 products with periodically flushed accumulators in the other) is amplified relative
+    to the result.  Measured: <= 1e-5 (before the flushes were added: 9e-5 on dW2 / dW3)."""
+    BAR_FULL = 3e-5
     rows, n = 20, 65536
     full = Case(lib, dev, True, 3, 1, rows, n, 77)
     ga, gc, st = full.run("tc")
@@ -211,7 +211,9 @@ def test_tc_backward_at_the_bench_size_is_linear_in_the_batch_and_agrees_with_ff
         k.n, k.B = n // 2, rows * n // 2
         cut = lambda t: t[..., sl].contiguous()
         k.o, k.acs_d, k.adv_d, k.lp_d, k.tg_d = (cut(t) for t in (full.o, full.acs_d, full.adv_d, full.lp_d, full.tg_d))
-        k.ax2, k.ax3, k.cx2, k.cx3 = (cut(t) for t in (full.ax2, full.ax3, full.cx2, full.cx3))
+        tiles = n // 128                                # the caches are tile-blocked: halve them by tiles
+        tsl = slice(h * tiles // 2, (h + 1) * tiles // 2)
+        k.ax2, k.ax3, k.cx2, k.cx3 = (t[:, tsl].contiguous() for t in (full.ax2, full.ax3, full.cx2, full.cx3))
         k.nbytes = lib.load().acx_loss_backward_tc_workspace_bytes(3, 1, 1, rows, n // 2)
         k.ws = torch.empty(k.nbytes, device=dev, dtype=torch.uint8)
         halves.append(k.run("tc"))

@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import policies as P
-from gpu_util import demo_weights, dev_t, random_weights, rel_err, soa
+from gpu_util import act_cache, demo_weights, dev_t, random_weights, rel_err, soa
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
@@ -133,8 +133,8 @@ def test_tc_forward_fills_the_activation_cache_like_the_ffma_forward(lib, dev):
     for tag in ("tc", "ffma"):
         ac, lp = torch.empty((rows, 1, n), device=dev), torch.empty((rows, n), device=dev)
         v = torch.empty((rows, n), device=dev)
-        ax2, ax3 = torch.zeros((rows, 128, n), device=dev), torch.zeros((rows, 64, n), device=dev)
-        cx2, cx3 = torch.zeros((rows, 128, n), device=dev), torch.zeros((rows, 128, n), device=dev)
+        ax2, ax3 = act_cache(lib, dev, rows, 128, n), act_cache(lib, dev, rows, 64, n)
+        cx2, cx3 = act_cache(lib, dev, rows, 128, n), act_cache(lib, dev, rows, 128, n)
         if tag == "tc":
             lib.call("acx_policy_forward_sample_gauss_tc", lib.ptr(a), lib.ptr(pa), 3, 1, 2.0, rows, n, lib.ptr(o), lib.ptr(e),
                      0, 0, 0, None, lib.ptr(ac), lib.ptr(lp), None, None, lib.ptr(ax2), lib.ptr(ax3), lib.cur_stream())
@@ -150,3 +150,13 @@ def test_tc_forward_fills_the_activation_cache_like_the_ffma_forward(lib, dev):
     for x, y in zip(res["tc"], res["ffma"]):
         assert rel_err(x, y) < 2 * TOL
     assert np.abs(res["tc"][0]).max() > 0
+    # layout: tile-blocked [rows][tiles][features][128], zeros beyond n; values = the critic's second hidden layer
+    lay = P.critic_layout(3)
+    W = {k: critic[o:o + int(np.prod(sh))].reshape(sh).astype(np.float64) for k, o, sh in P.items(lay)}
+    x1 = np.maximum(obs.astype(np.float64) @ W["W1"] + W["b1"], 0.0)
+    x2 = np.maximum(x1 @ W["W2"] + W["b2"], 0.0)                              # [rows, n, 128]
+    for tag in ("tc", "ffma"):
+        blk = res[tag][2]                                                     # [rows, tiles, 128, 128]
+        flat = blk.transpose(0, 2, 1, 3).reshape(rows, 128, -1)               # [rows, feature, tiles * 128]
+        np.testing.assert_allclose(flat[:, :, :n], x2.transpose(0, 2, 1), rtol=2e-5, atol=2e-5)
+        assert not flat[:, :, n:].any()
