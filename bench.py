@@ -378,8 +378,8 @@ def run_ours(args, rank, local_rank, world):
                     "frac_of_fp32_ffma_peak": dom["achieved"] / FP32_PEAK_TFLOPS,
                     "share_of_step": dom["ms"] / step_ms,
                     # dram__bytes_read.sum + dram__bytes_write.sum of the two kernels, one ncu --set full capture of this
-                    # workload (profiles/r01_ncu_tc_backward.md): chain 1.366 + 1.301 GB, wgrad 2.029 + 0.004 GB
-                    "traffic": 4.700e9 if (N_ENVS, HORIZON) == (65536, 20) else None, "traffic_unit": "bytes per launch",
+                    # workload (profiles/r01_ncu_tc_backward.md): chain 1.366 + 1.299 GB, wgrad 2.187 + 0.213 GB
+                    "traffic": 5.065e9 if (N_ENVS, HORIZON) == (65536, 20) else None, "traffic_unit": "bytes per launch",
                     "algorithmic_bytes": 4.697e9 if (N_ENVS, HORIZON) == (65536, 20) else None,
                     "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
         else:
