@@ -351,7 +351,7 @@ def run_ours(args, rank, local_rank, world):
             .acx_loss_backward_workspace_bytes(tr.ob, tr.num_ac, int(tr.cont))
         if getattr(tr, "tc_bwd", False) and tr.ws_bwd_bytes > base_bytes_:
             dom_name = "loss_backward_critic_tc, chain + wgrad kernels (K4, tcgen05 3xTF32)"
-            dom_kernel = ("acx_mlp_tc_train_kernel<critic, split> + acx_wgrad_kernel<critic> (fused loss+backward on "
+            dom_kernel = ("acx_mlp_tc_chain_kernel<critic> + acx_wgrad_kernel<critic> (fused loss+backward on "
                           "cached activations, K4)")
             note = "every product of the pair runs on tcgen05 as 3xTF32"
         elif getattr(tr, "tc_bwd", False):
