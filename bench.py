@@ -237,6 +237,13 @@ def kernel_table(tr, flush, hbm_peak):
     ks["returns_adv_scan, 1M columns (K3)"] = (lambda: L.call(
         "acx_returns_adv_scan", T, NB, L.ptr(rB), L.ptr(dB), L.ptr(vB), tr.gamma, tr.look_ahead, L.ptr(gB), L.ptr(aB),
         L.ptr(tr.stats), L.ptr(wsB), wsB.numel(), 0, s), None, 17.0 * T * NB + 4.0 * NB)
+    NB8 = 8 << 20
+    r8, d8 = torch.randn((T, NB8), device="cuda"), torch.zeros((T, NB8), device="cuda", dtype=torch.uint8)
+    v8, g8, a8 = torch.randn((T + 1, NB8), device="cuda"), torch.empty((T, NB8), device="cuda"), torch.empty((T, NB8), device="cuda")
+    ws8 = torch.zeros(L.load().acx_returns_adv_workspace_bytes(T, NB8), device="cuda", dtype=torch.uint8)
+    ks["returns_adv_scan, 8M columns (K3)"] = (lambda: L.call(
+        "acx_returns_adv_scan", T, NB8, L.ptr(r8), L.ptr(d8), L.ptr(v8), tr.gamma, tr.look_ahead, L.ptr(g8), L.ptr(a8),
+        L.ptr(tr.stats), L.ptr(ws8), ws8.numel(), 0, s), None, 17.0 * T * NB8 + 4.0 * NB8)
     out = {}
     for name, (fn, flops, nbytes) in ks.items():
         sec = time_kernel(fn, flush)
