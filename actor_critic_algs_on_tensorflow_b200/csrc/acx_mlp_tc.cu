@@ -24,6 +24,13 @@
 using namespace acxmlp;
 using namespace acxumma;
 
+#ifdef ACX_FWD_PROF
+__device__ unsigned long long acx_fwd_prof[16];
+#define FPROF(i) do { if (tid == 0) { const long long now_ = clock64(); prof_[i] += now_ - last_; last_ = now_; } } while (0)
+#else
+#define FPROF(i) do { } while (0)
+#endif
+
 namespace {
 
 constexpr int TC_EPI = 256;                      // epilogue threads (warps 0-7)
@@ -46,7 +53,7 @@ struct TcSmem {
   float pre[MAX_OUT * MT];                       // partial head sums of the second warpgroup
   float4 W1p[256];                               // ob_dim <= 3: {W1[0][k], W1[1][k], W1[2][k], b1[k]}
   double red[8];
-  unsigned long long full[TC_NSLOT], empty[TC_NSLOT], a_ready, stage_done;
+  unsigned long long full[TC_NSLOT], empty[TC_NSLOT], a_ready[2], stage_done;
   unsigned int tmem_base;
 };
 
@@ -141,7 +148,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
       acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.full[i]), 1);
       acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.empty[i]), 1);
     }
-    acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.a_ready), TC_EPI);
+    for (int i = 0; i < 2; ++i) acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.a_ready[i]), TC_EPI);
     acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.stage_done), 1);
     acx_mbar_fence_init();
   }
@@ -164,15 +171,24 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
       unsigned int ready = 0;
       for (unsigned int t = 0; t < mine; ++t) {
         for (int blk = 0; blk < NB; ++blk) {                     // layer 2, one 128-feature block of X1 at a time
-          acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready), ready & 1u); ++ready;
-          fence_after_sync();
-          for (int kc = 0; kc < 128 / TC_KC2; ++kc)
-            pipe.mma_chunk(tmem, kc * TC_KC2, TC_KC2, 128, tmem + TC_D2, blk == 0 && kc == 0);
+          // the A operand arrives in two halves of 64 features (a_ready[0], then [1]): the MMAs over the first half
+          // run while the epilogue warps still produce the second
+          for (int sub = 0; sub < 2; ++sub) {
+            acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready[sub]), ready & 1u);
+            fence_after_sync();
+            for (int kc = sub * (64 / TC_KC2); kc < (sub + 1) * (64 / TC_KC2); ++kc)
+              pipe.mma_chunk(tmem, kc * TC_KC2, TC_KC2, 128, tmem + TC_D2, blk == 0 && kc == 0);
+          }
+          ++ready;
           commit(reinterpret_cast<uint64_t*>(&sm.stage_done));
         }
-        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready), ready & 1u); ++ready;      // X2 is in place
-        fence_after_sync();
-        for (int kc = 0; kc < N3C; ++kc) pipe.mma_chunk(tmem, kc * KC3, KC3, H3, tmem + TC_D3, kc == 0);
+        for (int sub = 0; sub < 2; ++sub) {                                                   // X2 likewise
+          acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready[sub]), ready & 1u);
+          fence_after_sync();
+          for (int kc = sub * (N3C / 2); kc < (sub + 1) * (N3C / 2); ++kc)
+            pipe.mma_chunk(tmem, kc * KC3, KC3, H3, tmem + TC_D3, kc == 0);
+        }
+        ++ready;
         commit(reinterpret_cast<uint64_t*>(&sm.stage_done));
       }
     }
@@ -195,6 +211,9 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
     };
     float o_next[MAX_OB];
     load_obs(blockIdx.x, o_next);
+#ifdef ACX_FWD_PROF
+    long long prof_[16] = {0}, last_ = clock64();
+#endif
 
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int row = tile / tpr, n0 = (tile % tpr) * MT;
@@ -209,9 +228,9 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
       // ---------------------------------------------- layer 1 -> A operand, one 128-feature block per stage
       for (int blk = 0; blk < NB; ++blk) {
 #pragma unroll 1
-        for (int gq = 0; gq < 2; ++gq) {           // this thread: features half*64 + gq*32 .. +31 of the block
+        for (int gq = 0; gq < 2; ++gq) {           // this thread: features gq*64 + half*32 .. +31 of the block
           float v[32];
-          const int j0 = half * 64 + gq * 32;
+          const int j0 = gq * 64 + half * 32;
           if (ob <= 3) {
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
@@ -233,23 +252,27 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
             }
           }
           if (blk > 0 && gq == 0) {                // the MMAs reading the previous block must be done
+            FPROF(1);
             acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
             fence_after_sync();
+            FPROF(2);
           }
           a_store32(tl, j0, v);
+          tmem_wait_st();
+          fence_before_sync();
+          mbar_arrive(&sm.a_ready[gq]);            // features gq*64 .. +63 of the A operand are in place
         }
-        tmem_wait_st();
-        fence_before_sync();
-        mbar_arrive(&sm.a_ready);
+        FPROF(blk == 0 ? 0 : 3);
       }
       // ---------------------------------------------- layer-2 epilogue: X2 = act(D2 + b2) -> A operand (+ cache)
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
       fence_after_sync();
+      FPROF(4);
       float pre[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
       for (int gq = 0; gq < 2; ++gq) {
         float v[32];
-        const int j0 = half * 64 + gq * 32;
+        const int j0 = gq * 64 + half * 32;
         tmem_ld32(tl + TC_D2 + (uint32_t)j0, v);
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b2[j0 + e]));
@@ -263,13 +286,15 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
           for (int e = 0; e < 32; ++e) pre[0] = fmaf(v[e], sm.Wh[j0 + e], pre[0]);
         }
         a_store32(tl, j0, v);
+        tmem_wait_st();
+        fence_before_sync();
+        mbar_arrive(&sm.a_ready[gq]);
       }
-      tmem_wait_st();
-      fence_before_sync();
-      mbar_arrive(&sm.a_ready);
+      FPROF(5);
       // ---------------------------------------------- layer-3 epilogue + head
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
       fence_after_sync();
+      FPROF(6);
 #pragma unroll 1
       for (int gq = 0; gq < H3 / 64; ++gq) {       // this thread: H3/2 features
         float v[32];
@@ -296,7 +321,9 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         for (int a = 0; a < MAX_OUT; ++a)
           if (a < nout) sm.pre[a * MT + s] = pre[a];
       }
+      FPROF(7);
       epi_sync();
+      FPROF(8);
       if (half == 0) {
 #pragma unroll
         for (int a = 0; a < MAX_OUT; ++a)
@@ -402,7 +429,12 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         }
       }
       fence_before_sync();       // this tile's tcgen05.ld are ordered before the next a_ready arrive
+      FPROF(9);
     }
+#ifdef ACX_FWD_PROF
+    if (tid == 0 && blockIdx.x == 0)
+      for (int i = 0; i < 16; ++i) acx_fwd_prof[i] = (unsigned long long)prof_[i];
+#endif
     if (MODE == MODE_EVAL && HEAD != HEAD_VALUE && A.kl_partial != nullptr) {
       const double v = acx_warp_sum_d(kl_sum);
       if (lane == 0) sm.red[warp] = v;
@@ -571,3 +603,9 @@ extern "C" int acx_value_forward_tc(const float* critic, const float* packed, in
   a.v_out = v_out; a.basic_head = basic_head; a.x2_out = x2_out; a.x3_out = x3_out;
   return launch_tc<256, 128, false, HEAD_VALUE, MODE_EVAL>(a, packed, tc_grid(rows, n), (cudaStream_t)stream);
 }
+
+#ifdef ACX_FWD_PROF
+extern "C" int acx_fwd_prof_read(unsigned long long* out16) {
+  return (int)cudaMemcpyFromSymbol(out16, acx_fwd_prof, sizeof(unsigned long long) * 16);
+}
+#endif
