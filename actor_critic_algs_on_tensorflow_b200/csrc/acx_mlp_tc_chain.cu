@@ -2,17 +2,18 @@
 // per 128-sample tile the head (loss terms, seed gradients, head-layer gradients), then back-propagation
 //     dPre3 = (Wh dHead) * act'(X3)          dPre2 = (dPre3 W3^T) * act'(X2)          dPre1 = (dPre2 W2^T) * act'(X1)
 // with both products on tcgen05 (3xTF32, A operand = dPre in tensor memory, B = packed weight chunks through a bulk-TMA
-// ring, accumulators in tensor memory) and the first-layer gradients dW1 / db1.  dPre3 and dPre2 leave as coalesced
-// stores ([rows][feature][n]) for acx_wgrad_kernel, which forms dW3 / dW2 / db3 / db2 from them.
+// ring, accumulators in tensor memory) and the first-layer gradients dW1 / db1.  dPre3 and dPre2 are streamed to HBM
+// (tile-blocked like the activation cache) for acx_wgrad_kernel, which forms dW3 / dW2 / db3 / db2 from them.
 //
-// One persistent CTA per SM; warps 0-7 workers (thread = sample x half of the feature range = TMEM lane), warp 8 issuer.
+// One persistent CTA per SM; warps 0-7 workers (thread = sample x half of the feature range = TMEM lane), warp 8 issues
+// the MMAs, warp 9 feeds the weight-chunk ring.
 //  * The activation cache and the dPre streams are tile-blocked ([tile][feature][128]): a tile is one contiguous block,
 //    one DRAM page and TLB entry instead of `feature` rows 4 n bytes apart (worth 17 % of this kernel).  X3 tiles
 //    arrive by bulk-TMA one tile ahead (two staging buffers); dPre3 and dPre2 are staged in the tile's buffer and
 //    leave as bulk-TMA row stores, off the load/store pipe; after dPre2 the buffer is the transposition staging of the
 //    dPre1 blocks (thread = sample writes columns, thread = neuron reads rows).
 //  * X2 is needed only as act'(X2): each thread reads its 64 values straight from the cache (coalesced) into two
-//    32-bit masks at the start of the tile, long before the product they gate is done.
+//    32-bit masks, the loads issued a phase ahead of their use.
 //  * act'(X1) is recomputed per element from the thread's own observation (ob_dim FMAs, layer1_block's arithmetic).
 #include "acx_head.cuh"
 #include "acx_tc_bwd.cuh"

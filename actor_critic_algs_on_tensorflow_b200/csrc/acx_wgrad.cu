@@ -2,9 +2,9 @@
 //     dW3[k][j] = sum_s X2[k][s] * dPre3[j][s]          (A3C/policies.py:82,155: compute_gradients of the
 //     dW2[k][j] = sum_s X1[k][s] * dPre2[j][s]           third / second dense layer's kernel and bias)
 //     db3[j] = sum_s dPre3[j][s],   db2[j] = sum_s dPre2[j][s]
-// summed over the whole [rows x n] batch.  Operands are the [rows][feature][n] arrays the chain kernel wrote (dPre3,
-// dPre2) and the activation cache (X2): the sample index is contiguous, i.e. both operands are K-major as they lie
-// in HBM.  X1 = act(obs W1 + b1) is not read but recomputed (ob_dim <= 8 FMAs per element) straight into the swizzled
+// summed over the whole [rows x n] batch.  Operands are the tile-blocked [tile][feature][128] arrays the chain kernel
+// wrote (dPre3, dPre2) and the activation cache (X2): the sample index is contiguous, i.e. both operands are K-major
+// as they lie in HBM.  X1 = act(obs W1 + b1) is not read but recomputed (ob_dim <= 8 FMAs per element) straight into the swizzled
 // operand layout.  Each persistent CTA owns the 128-sample tiles  blockIdx.x, +gridDim.x, ...  and keeps
 // its partial dW3 / dW2 in tensor memory (fp32).  The tensor core's accumulate truncates: over the ~3,300 accumulating
 // MMAs of a CTA's whole share the error reached 7.7e-5 of the result (measured against an fp64 product of the same
