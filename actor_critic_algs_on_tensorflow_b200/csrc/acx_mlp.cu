@@ -267,8 +267,17 @@ __global__ void __launch_bounds__(256) acx_grad_reduce_kernel(const float* __res
                                                               float* __restrict__ stats, const float* __restrict__ opt,
                                                               int is_actor, double count) {
   for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < size; p += gridDim.x * blockDim.x) {
+    // fixed order cta = 0, 1, ...; the loads of eight rows are issued ahead of the dependent adds
     float s = 0.f;
-    for (int cta = 0; cta < ncta; ++cta) s += scratch[(size_t)cta * size + p];
+    int cta = 0;
+    for (; cta + 8 <= ncta; cta += 8) {
+      float x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) x[u] = scratch[(size_t)(cta + u) * size + p];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) s += x[u];
+    }
+    for (; cta < ncta; ++cta) s += scratch[(size_t)cta * size + p];
     grad[p] = s;
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats != nullptr) {

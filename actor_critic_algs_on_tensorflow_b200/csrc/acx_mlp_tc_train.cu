@@ -335,8 +335,17 @@ __global__ void __launch_bounds__(256) acx_grad_reduce_tc_kernel(const float* __
       const int k1 = (p - offW2) / 128, j = (p - offW2) % 128, r = k1 & 127, c = (k1 >> 7) * 128 + j;
       q = offW2 + ((c >> 2) * 128 + r) * 4 + (c & 3);
     }
+    // fixed order cta = 0, 1, ...; the loads of eight rows are issued ahead of the dependent adds
     float acc = 0.f;
-    for (int cta = 0; cta < ncta; ++cta) acc += scratch[(size_t)cta * size + q];
+    int cta = 0;
+    for (; cta + 8 <= ncta; cta += 8) {
+      float x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) x[u] = scratch[(size_t)(cta + u) * size + q];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc += x[u];
+    }
+    for (; cta < ncta; ++cta) acc += scratch[(size_t)cta * size + q];
     grad[p] = acc;
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats != nullptr) {
