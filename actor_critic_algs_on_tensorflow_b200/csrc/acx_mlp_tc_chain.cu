@@ -9,9 +9,10 @@
 // the MMAs, warp 9 feeds the weight-chunk ring.
 //  * The activation cache and the dPre streams are tile-blocked ([tile][feature][128]): a tile is one contiguous block,
 //    one DRAM page and TLB entry instead of `feature` rows 4 n bytes apart (worth 17 % of this kernel).  X3 tiles
-//    arrive by bulk-TMA one tile ahead (two staging buffers); dPre3 and dPre2 are staged in the tile's buffer and
-//    leave as bulk-TMA row stores, off the load/store pipe; after dPre2 the buffer is the transposition staging of the
-//    dPre1 blocks (thread = sample writes columns, thread = neuron reads rows).
+//    arrive one tile ahead as ONE bulk-TMA copy each (two dense staging buffers); dPre3 and dPre2 are staged dense in
+//    the tile's buffer and leave as one bulk-TMA store each, off the load/store pipe; after dPre2 the buffer is the
+//    transposition staging of the dPre1 blocks (thread = sample writes columns, thread = neuron reads rows; padded
+//    [feature][132] layout).  The A operand reaches the issuer in two halves of 64 reduction features.
 //  * X2 is needed only as act'(X2): each thread reads its 64 values straight from the cache (coalesced) into two
 //    32-bit masks, the loads issued a phase ahead of their use.
 //  * act'(X1) is recomputed per element from the thread's own observation (ob_dim FMAs, layer1_block's arithmetic).
@@ -45,7 +46,7 @@ struct TcSmem {
   float4 W1p[256];             // ob_dim <= 3: {W1[0][k], W1[1][k], W1[2][k], b1[k]} -- one 16-byte load per neuron
   float l1p[128 * (MAX_OB + 1)];   // layer1 gradient partials of the second half of the samples
   double red[8][4];
-  unsigned long long full[TT_NSLOT], empty[TT_NSLOT], a_ready, stage_done[3], bar_act[2];
+  unsigned long long full[TT_NSLOT], empty[TT_NSLOT], a_ready[2], stage_done[3], bar_act[2];
   unsigned int tmem_base;
 };
 
@@ -80,7 +81,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.full[i]), 1);
       acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.empty[i]), 1);
     }
-    acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.a_ready), TT_WORK);
+    for (int i = 0; i < 2; ++i) acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.a_ready[i]), TT_WORK);
     for (int i = 0; i < 3; ++i) acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.stage_done[i]), 1);
     for (int i = 0; i < 2; ++i) acx_mbar_init(reinterpret_cast<uint64_t*>(&sm.bar_act[i]), 1);
     acx_mbar_fence_init();
@@ -100,16 +101,26 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
   } else if (warp == 8) {
     // ================================================================ issuer
     if (lane == 0) {
-      unsigned int ready = 0;
+      // The A operand (dPre3, then dPre2) is handed over in halves of 64 reduction features, a_ready[0] then [1]: the
+      // MMAs over the first half run while the workers still produce the second (H3 = 64: a single hand-over)
+      unsigned int cnt[2] = {0u, 0u};
+      constexpr int SUB3 = H3 / 64;
       for (unsigned int t = 0; t < mine; ++t) {
-        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready), ready & 1u); ++ready;       // dPre3 is the A operand
-        fence_after_sync();
-        for (int cc = 0; cc < N3C; ++cc) pipe.mma_chunk(tmem, cc * 16, tmem + TT_D0, cc == 0);
+        for (int sub = 0; sub < SUB3; ++sub) {
+          acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready[sub]), cnt[sub] & 1u); ++cnt[sub];
+          fence_after_sync();
+          for (int cc = sub * 4; cc < sub * 4 + 4; ++cc) pipe.mma_chunk(tmem, cc * 16, tmem + TT_D0, cc == 0);
+        }
         commit(reinterpret_cast<uint64_t*>(&sm.stage_done[0]));
-        acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready), ready & 1u); ++ready;       // dPre2 is the A operand
-        fence_after_sync();
-        for (int h = 0; h < NB; ++h) {
-          for (int cc = 0; cc < 8; ++cc) pipe.mma_chunk(tmem, cc * 16, tmem + (h == 0 ? TT_D0 : TT_D1), cc == 0);
+        // dX1 block 0 goes to D1: D0 still holds the half of dX2 the workers are turning into dPre2
+        for (int sub = 0; sub < 2; ++sub) {
+          acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready[sub]), cnt[sub] & 1u); ++cnt[sub];
+          fence_after_sync();
+          for (int cc = sub * 4; cc < sub * 4 + 4; ++cc) pipe.mma_chunk(tmem, cc * 16, tmem + TT_D1, cc == 0);
+        }
+        commit(reinterpret_cast<uint64_t*>(&sm.stage_done[1]));
+        for (int h = 1; h < NB; ++h) {
+          for (int cc = 0; cc < 8; ++cc) pipe.mma_chunk(tmem, cc * 16, tmem + TT_D0, cc == 0);
           commit(reinterpret_cast<uint64_t*>(&sm.stage_done[1 + h]));
         }
       }
@@ -147,11 +158,14 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
     // X3 tile -> staging buffer `buf` by bulk-TMA (full, 16-byte aligned tiles only)
     // the activation cache and the dPre streams are tile-blocked ([tile][feature][128], zeros beyond the batch): every
     // tile is whole, its rows 512 bytes apart
+    // X3, dPre3 and dPre2 are staged DENSE ([feature][128], exactly the tile's block in HBM), so each moves with ONE
+    // bulk copy (128 per-row copies cost 2-3 k cycles of TMA issue per tile and direction); only the dPre1 blocks,
+    // which are read back by rows, use the padded [feature][132] layout in the same buffer
     auto issue_x3 = [&](int tile, int buf) {
-      const float* g3 = A.x3_in + cache_tile_off(tile, H3);
+      if (tid != 0) return;
       uint64_t* bar = reinterpret_cast<uint64_t*>(&sm.bar_act[buf]);
-      if (tid == 0) acx_mbar_expect_tx(bar, (uint32_t)(H3 * MT * 4));
-      if (tid < H3) acx_bulk_g2s(sm.S[buf] + tid * MS, g3 + (size_t)tid * MT, MT * 4, bar);
+      acx_mbar_expect_tx(bar, (uint32_t)(H3 * MT * 4));
+      acx_bulk_g2s(sm.S[buf], A.x3_in + cache_tile_off(tile, H3), H3 * MT * 4, bar);
     };
     if ((int)blockIdx.x < ntiles) issue_x3(blockIdx.x, 0);
     // act'(X2) of this thread's 64 features comes straight from the cache (coalesced loads) as two 32-bit masks.  The
@@ -159,7 +173,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
     // tile's layer-1 phase, the lower 32 at the start of the tile (they have until dX2 is done).
     float xm[32];
     auto load_x2 = [&](int tile, int q) {
-      const float* g2 = A.x2_in + cache_tile_off(tile, H2) + (size_t)(half * 64 + q * 32) * MT + s;
+      const float* g2 = A.x2_in + cache_tile_off(tile, H2) + (size_t)(q * 64 + half * 32) * MT + s;
       const bool ok = tile < ntiles;                 // (the cache holds zeros beyond the batch)
       // volatile: the loads must be ISSUED here (the compiler would otherwise sink them to the pack, next to their use)
 #pragma unroll
@@ -176,12 +190,12 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
     };
     load_x2(blockIdx.x, 1);
 
-    // rows of a staged tile (row r of S, MT floats) -> global rows by bulk-TMA stores, off the load/store pipe: the
-    // 64 + 64 KB of dPre3 / dPre2 a tile produces otherwise queue in front of every later global load of the SM
+    // staged dense tile (nrows x 128 floats) -> its block in HBM: one bulk-TMA store, off the load/store pipe (as plain
+    // stores the 64 + 64 KB per tile queued in front of every later global load of the SM)
     auto bulk_rows_out = [&](const float* src, float* dst, int nrows) {
-      if (tid < nrows) {
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + (size_t)tid * MT),
-                     "r"(acx_smem_u32(src + tid * MS)), "r"(MT * 4)
+      if (tid == 0) {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(acx_smem_u32(src)),
+                     "r"(nrows * MT * 4)
                      : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
@@ -218,7 +232,21 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       // ---------------------------------------------- head
       if (tid < MT) {
         float pre[MAX_OUT];
-        head_pre<H3>(sm, S, tid, nout, pre);
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a) pre[a] = 0.f;
+        for (int k0 = 0; k0 < H3; k0 += 8) {        // head_pre's k-ascending FMA chain over the dense tile
+          float x[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) x[u] = S[(k0 + u) * MT + tid];
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) pre[a] = fmaf(x[u], sm.Wh[(k0 + u) * nout + a], pre[a]);
+        }
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a)
+          if (a < nout) pre[a] = __fadd_rn(pre[a], sm.bh[a]);
         float dh[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
         head_apply<HEAD, MODE_TRAIN>(A, sm.log_std, nout, pre, live, row, col, hs, lsum, dls, dh);
 #pragma unroll
@@ -227,13 +255,16 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       }
       work_sync();
       PROF_MARK(1);
-      {   // head weights and bias
+      {   // head weights and bias.  Thread k < H3 owns row k of the dense tile; rows are 512 bytes apart, so every thread
+          // starts at its own 16-byte column (k mod 32) and wraps: a warp's accesses are then 512 distinct bytes
         if (tid < H3) {
           for (int a = 0; a < nout; ++a) {
             float acc = 0.f;
+#pragma unroll 8
             for (int m4 = 0; m4 < MT / 4; ++m4) {
-              const float4 x = *reinterpret_cast<const float4*>(&S[tid * MS + 4 * m4]);
-              const float4 d = *reinterpret_cast<const float4*>(&sm.dHead[a * MT + 4 * m4]);
+              const int mm = (m4 + tid) & 31;
+              const float4 x = *reinterpret_cast<const float4*>(&S[tid * MT + 4 * mm]);
+              const float4 d = *reinterpret_cast<const float4*>(&sm.dHead[a * MT + 4 * mm]);
               acc = fmaf(x.x, d.x, acc); acc = fmaf(x.y, d.y, acc); acc = fmaf(x.z, d.z, acc); acc = fmaf(x.w, d.w, acc);
             }
             gWh[a] += acc;
@@ -254,10 +285,10 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         for (int a = 0; a < MAX_OUT; ++a) dh[a] = a < nout ? sm.dHead[a * MT + s] : 0.f;
 #pragma unroll 1
         for (int gq = 0; gq < H3 / 64; ++gq) {
-          const int j0 = half * (H3 / 2) + gq * 32;
+          const int j0 = gq * 64 + half * 32;
           float v[32];
 #pragma unroll
-          for (int e = 0; e < 32; ++e) v[e] = S[(j0 + e) * MS + s];
+          for (int e = 0; e < 32; ++e) v[e] = S[(j0 + e) * MT + s];
 #pragma unroll
           for (int e = 0; e < 32; ++e) {
             float acc = 0.f;
@@ -268,12 +299,12 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
           }
           a_store32_tt(tl, j0, v);
 #pragma unroll
-          for (int e = 0; e < 32; ++e) S[(j0 + e) * MS + s] = v[e];
+          for (int e = 0; e < 32; ++e) S[(j0 + e) * MT + s] = v[e];
+          tmem_wait_st();
+          fence_before_sync();
+          mbar_arrive1(&sm.a_ready[gq]);           // reduction features gq*64 .. +63 of the A operand are in place
         }
       }
-      tmem_wait_st();
-      fence_before_sync();
-      mbar_arrive1(&sm.a_ready);
       fence_proxy_async();
       work_sync();
       bulk_rows_out(S, d3_out + cache_tile_off(tile, H3), H3);
@@ -289,18 +320,18 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       for (int gq = 0; gq < 2; ++gq) {
         const unsigned int bits = m2[gq];
         float v[32];
-        const int k0 = half * 64 + gq * 32;
+        const int k0 = gq * 64 + half * 32;
         tmem_ld32(tl + TT_D0 + (uint32_t)k0, v);
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] *= ((bits >> e) & 1u) ? 1.0f : SLOPE;
         a_store32_tt(tl, k0, v);
 #pragma unroll
-        for (int e = 0; e < 32; ++e) S[(k0 + e) * MS + s] = v[e];
+        for (int e = 0; e < 32; ++e) S[(k0 + e) * MT + s] = v[e];
+        tmem_wait_st();
+        fence_before_sync();
+        mbar_arrive1(&sm.a_ready[gq]);
       }
       PROF_MARK(14);
-      tmem_wait_st();
-      fence_before_sync();
-      mbar_arrive1(&sm.a_ready);
       fence_proxy_async();
       work_sync();
       bulk_rows_out(S, d2_out + cache_tile_off(tile, H2), H2);
@@ -328,7 +359,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         for (int gq = 0; gq < 2; ++gq) {
           float v[32];
           const int k0 = half * 64 + gq * 32;
-          tmem_ld32(tl + (h == 0 ? TT_D0 : TT_D1) + (uint32_t)k0, v);
+          tmem_ld32(tl + (h == 0 ? TT_D1 : TT_D0) + (uint32_t)k0, v);
           if (ob <= 3) {
 #pragma unroll
             for (int e = 0; e < 32; ++e) {

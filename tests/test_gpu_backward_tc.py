@@ -150,12 +150,16 @@ def test_tc_backward_agrees_with_the_ffma_kernel(lib, dev, cont, ob, num_ac, spl
         for name, o, s in P.items(lay):
             sz = int(np.prod(s))
             assert rel_err(got[o:o + sz], want[o:o + sz]) < 2e-5, name
-    # the head, its gradients and the loss sums never touch the tensor cores: identical
+    # the head, its gradients and the loss sums never touch the tensor cores: the loss sums are identical, and so are
+    # the head gradients in the one-kernel form; the chain kernel sums them warp-wide in another order (fp32 rounding)
     for lay, got, want in ((k.lay, ta, fa), (k.clay, tcg, fc)):
         for name in ("Wh", "bh") if "Wh" in lay else ("Wv", "bv"):
             o, s = lay[name]
             sz = int(np.prod(s))
-            np.testing.assert_array_equal(got[o:o + sz], want[o:o + sz])
+            if split:
+                assert rel_err(got[o:o + sz], want[o:o + sz]) < 2e-6, name
+            else:
+                np.testing.assert_array_equal(got[o:o + sz], want[o:o + sz])
     np.testing.assert_array_equal(ts, fs)
 
 
