@@ -71,6 +71,7 @@ SIGNATURES = {
     "acx_tc_pack_weights": (_i, [_i, _p, _i, _i, _i, _p, _p]),
     "acx_policy_forward_sample_gauss_tc": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _u64, _u64, _u32, _p, _p, _p, _p, _p, _p, _p, _p]),
     "acx_policy_forward_sample_cat_tc": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _u64, _u64, _u32, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "acx_rollout_tc": (_i, [_i, _p, _p, _f, _i, _i, _p, _p, _p, _p, _p, _u64, _u64, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
     "acx_policy_logp_gauss_tc": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _ip, _p]),
     "acx_policy_logp_cat_tc": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _ip, _p]),
     "acx_value_forward_tc": (_i, [_p, _p, _i, _i, _i, _p, _p, _i, _p, _p, _p]),

@@ -77,6 +77,14 @@ struct Args {
   float* x3_out;
   const float* x2_in;
   const float* x3_in;
+  // persistent rollout (acx_rollout_tc): the env step runs in the sampling head, rows = T time steps of the same envs
+  float* env_state;          // [S][n], read before the first step, written after the last
+  int* env_elapsed;          // [n]
+  float* obs_rw;             // = obs, [rows + 1][ob][n]: row 0 is read, rows 1..rows are written
+  float* rew_out;            // [rows][n]
+  unsigned char* done_out;   // [rows][n]
+  const float* reset_u;      // [rows][S][n] uniforms for resets, or NULL (Philox)
+  int max_steps;
 };
 
 struct Smem {

@@ -20,6 +20,7 @@
 // (tests/tc/run_tc_test.py), which is why the weight-gradient GEMMs stay on the FFMA engine.
 #include "acx_mlp.cuh"
 #include "acx_umma.cuh"
+#include "acx_env_dev.cuh"
 
 using namespace acxmlp;
 using namespace acxumma;
@@ -52,6 +53,7 @@ struct TcSmem {
   float log_std[MAX_OUT];
   float pre[MAX_OUT * MT];                       // partial head sums of the second warpgroup
   float4 W1p[256];                               // ob_dim <= 3: {W1[0][k], W1[1][k], W1[2][k], b1[k]}
+  float obs_x[MAX_OB * MT];                      // rollout: the observations the env step just produced
   double red[8];
   unsigned long long full[TC_NSLOT], empty[TC_NSLOT], a_ready[2], stage_done;
   unsigned int tmem_base;
@@ -115,7 +117,10 @@ __device__ inline void a_store32(uint32_t tmem_lane, int j0, const float (&v)[32
   tmem_st32(tmem_lane + TC_A_LO + (uint32_t)j0, lo);
 }
 
-template <int H1, int H3, bool LRELU, int HEAD, int MODE>
+// ENVR >= 0 (MODE_SAMPLE only): persistent rollout of environment ENVR.  A.rows = T time steps; a CTA keeps its column
+// tiles for all T steps, the sampling head steps the environment (acx_env_dev.cuh, the arithmetic of acx_env_step) with
+// the state in registers, and the next step's observation reaches layer 1 through shared memory instead of HBM.
+template <int H1, int H3, bool LRELU, int HEAD, int MODE, int ENVR = -1>
 __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, const float* __restrict__ packed) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   TcSmem& sm = *reinterpret_cast<TcSmem*>(smem_raw);
@@ -138,9 +143,13 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
     sm.bh[tid] = P[L.bh + tid];
     if (HEAD == HEAD_GAUSS) sm.log_std[tid] = P[L.log_std + tid];
   }
+  constexpr bool ROLL = ENVR >= 0;
   const int tpr = (A.n + MT - 1) / MT;
   const int ntiles = A.rows * tpr;
-  const unsigned int mine = ((int)blockIdx.x < ntiles) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const int nouter = ROLL ? tpr : ntiles;         // what a CTA iterates over: column tiles (x T steps each) or tiles
+  const int T = ROLL ? A.rows : 1;
+  const unsigned int mine =
+      ((int)blockIdx.x < nouter) ? (unsigned)((nouter - blockIdx.x + gridDim.x - 1) / gridDim.x) * (unsigned)T : 0u;
 
   if (warp == 8) tmem_alloc(&sm.tmem_base, 512);
   if (tid == 0) {
@@ -210,20 +219,72 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         o[i] = (i < ob && tile < ntiles && c < A.n) ? __ldg(A.obs + ((size_t)row * ob + i) * A.n + c) : 0.f;
     };
     float o_next[MAX_OB];
-    load_obs(blockIdx.x, o_next);
+    if (!ROLL) load_obs(blockIdx.x, o_next);
 #ifdef ACX_FWD_PROF
     long long prof_[16] = {0}, last_ = clock64();
 #endif
+    // rollout: this sample's environment (first warpgroup), in registers for all T steps
+    constexpr int ES = AcxEnv<ROLL ? ENVR : 0>::S, EOB = AcxEnv<ROLL ? ENVR : 0>::OB;   // (unused unless ROLL)
+    float est[ES];
+    int eel = 0;
+    const int emax = ROLL ? (A.max_steps > 0 ? A.max_steps : AcxEnv<ROLL ? ENVR : 0>::MAX_STEPS) : 0;
+    // one environment transition after the action of step `row` (the arithmetic and order of acx_env_step_kernel)
+    auto env_step = [&](float act, int row, size_t col) {
+      if (!ROLL) return;
+      float rew;
+      bool term;
+      AcxEnv<ROLL ? ENVR : 0>::dynamics(est, act, rew, term);
+      int e = eel + 1;
+      const bool dn = term || (e >= emax);
+      if (dn) {
+        float ru[ES];
+        if (A.reset_u != nullptr) {
+#pragma unroll
+          for (int k = 0; k < ES; ++k) ru[k] = A.reset_u[((size_t)row * ES + k) * A.n + col];
+        } else {
+          const AcxRng4 g = acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_RESET, A.seed);
+          const float u4[4] = {acx_u01(g.x), acx_u01(g.y), acx_u01(g.z), acx_u01(g.w)};
+#pragma unroll
+          for (int k = 0; k < ES; ++k) ru[k] = u4[k];
+        }
+        AcxEnv<ROLL ? ENVR : 0>::reset(ru, est);
+        e = 0;
+      }
+      float ov[EOB];
+      AcxEnv<ROLL ? ENVR : 0>::observe(est, ov);
+      eel = e;
+      A.rew_out[(size_t)row * A.n + col] = rew;
+      A.done_out[(size_t)row * A.n + col] = dn ? 1 : 0;
+#pragma unroll
+      for (int k = 0; k < EOB; ++k) {
+        A.obs_rw[((size_t)(row + 1) * EOB + k) * A.n + col] = ov[k];
+        sm.obs_x[k * MT + s] = ov[k];
+      }
+    };
 
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int outer = blockIdx.x; outer < nouter; outer += gridDim.x)
+    for (int t = 0; t < T; ++t) {
+      const int tile = ROLL ? t * tpr + outer : outer;
       const int row = tile / tpr, n0 = (tile % tpr) * MT;
       const int valid = min(MT, A.n - n0);
       const bool live = s < valid;
       const size_t col = (size_t)n0 + s;
       float o[MAX_OB];
+      if (!ROLL) {
 #pragma unroll
-      for (int i = 0; i < MAX_OB; ++i) o[i] = o_next[i];
-      load_obs(tile + gridDim.x, o_next);
+        for (int i = 0; i < MAX_OB; ++i) o[i] = o_next[i];
+        load_obs(tile + gridDim.x, o_next);
+      } else if (t == 0) {
+        load_obs(tile, o);
+        if (half == 0 && live) {
+#pragma unroll
+          for (int k = 0; k < ES; ++k) est[k] = A.env_state[(size_t)k * A.n + col];
+          eel = A.env_elapsed[col];
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < MAX_OB; ++i) o[i] = i < ob ? sm.obs_x[i * MT + s] : 0.f;
+      }
 
       // ---------------------------------------------- layer 1 -> A operand, one 128-feature block per stage
       for (int blk = 0; blk < NB; ++blk) {
@@ -333,7 +394,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
           if (HEAD == HEAD_VALUE) {
             A.v_out[s_idx] = pre[0];
           } else if (HEAD == HEAD_GAUSS) {
-            float lp = 0.f, ent = 0.f;
+            float lp = 0.f, ent = 0.f, ac_env = 0.f;
             AcxRng4 g = {0u, 0u, 0u, 0u};
             if (MODE == MODE_SAMPLE && A.noise == nullptr)
               g = acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed);
@@ -351,6 +412,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
                   else eps = (d == 0) ? acx_normal(g.x, g.y) : ((d == 1) ? acx_normal(g.z, g.w) : 0.f);
                   ac = __fadd_rn(mu, __fmul_rn(sd, eps));
                   A.ac_out_f[a_idx] = ac;
+                  if (d == 0) ac_env = ac;
                 } else {
                   ac = A.ac_in_f[a_idx];
                 }
@@ -365,6 +427,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
               const double df = (double)A.logp_old[s_idx] - (double)lp;
               kl_sum += df * df;
             }
+            if (ROLL) env_step(ac_env, row, col);
           } else {   // HEAD_CAT
             float l1[MAX_OUT], logps[MAX_OUT], p[MAX_OUT];
             float mx1 = -INFINITY, mx2 = -INFINITY;
@@ -425,8 +488,20 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
               const double df = (double)A.logp_old[s_idx] - (double)lp;
               kl_sum += df * df;
             }
+            if (ROLL) env_step((float)ac, row, col);
           }
+        } else if (ROLL) {
+#pragma unroll
+          for (int k = 0; k < EOB; ++k) sm.obs_x[k * MT + s] = 0.f;
         }
+      }
+      if (ROLL) {
+        if (t == T - 1 && half == 0 && live) {
+#pragma unroll
+          for (int k = 0; k < ES; ++k) A.env_state[(size_t)k * A.n + col] = est[k];
+          A.env_elapsed[col] = eel;
+        }
+        epi_sync();              // the next step's observations (obs_x) are visible to both warpgroups
       }
       fence_before_sync();       // this tile's tcgen05.ld are ordered before the next a_ready arrive
       FPROF(9);
@@ -472,9 +547,9 @@ __global__ void __launch_bounds__(256) acx_tc_pack_kernel(const float* __restric
   }
 }
 
-template <int H1, int H3, bool LRELU, int HEAD, int MODE>
+template <int H1, int H3, bool LRELU, int HEAD, int MODE, int ENVR = -1>
 int launch_tc(const Args& a, const float* packed, int grid, cudaStream_t st) {
-  auto kern = acx_mlp_tc_kernel<H1, H3, LRELU, HEAD, MODE>;
+  auto kern = acx_mlp_tc_kernel<H1, H3, LRELU, HEAD, MODE, ENVR>;
   ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024));
   kern<<<grid, TC_NT, sizeof(TcSmem) + 1024, st>>>(a, packed);
   ACX_LAUNCH_OK("acx_mlp_tc_kernel");
@@ -602,6 +677,35 @@ extern "C" int acx_value_forward_tc(const float* critic, const float* packed, in
   a.params = critic; a.L = acx_critic_layout(ob_dim); a.rows = rows; a.n = n; a.obs = obs;
   a.v_out = v_out; a.basic_head = basic_head; a.x2_out = x2_out; a.x3_out = x3_out;
   return launch_tc<256, 128, false, HEAD_VALUE, MODE_EVAL>(a, packed, tc_grid(rows, n), (cudaStream_t)stream);
+}
+
+extern "C" int acx_rollout_tc(int env, const float* actor, const float* packed, float ac_scale, int T, int n, float* obs,
+                              float* state, int* elapsed, const float* noise, const float* reset_u, uint64_t seed,
+                              uint64_t index0, const uint32_t* step_base, int max_steps, void* ac_out, float* logp_out,
+                              float* ent_out, float* rew_out, unsigned char* done_out, float* x2_out, float* x3_out,
+                              void* stream) {
+  ACX_REQUIRE(env == ACX_ENV_PENDULUM || env == ACX_ENV_CARTPOLE || env == ACX_ENV_ACROBOT,
+              "acx_rollout_tc: unknown env id %d", env);
+  const int ob_dim = env == ACX_ENV_PENDULUM ? 3 : (env == ACX_ENV_CARTPOLE ? 4 : 6);
+  const int cont = env == ACX_ENV_PENDULUM, num_ac = cont ? 1 : (env == ACX_ENV_CARTPOLE ? 2 : 3);
+  int rc = tc_check("acx_rollout_tc", actor, packed, ob_dim, num_ac, T, n, obs);
+  if (rc) return rc;
+  if (T == 0 || n == 0) return ACX_OK;
+  ACX_REQUIRE(state && elapsed && ac_out && rew_out && done_out, "acx_rollout_tc: null state / elapsed / ac_out / rew_out / done_out");
+  ACX_REQUIRE((x2_out == nullptr) == (x3_out == nullptr), "acx_rollout_tc: give both caches or none");
+  Args a; memset(&a, 0, sizeof(a));
+  a.params = actor; a.L = acx_actor_layout(ob_dim, num_ac, cont); a.rows = T; a.n = n; a.obs = obs; a.obs_rw = obs;
+  a.ac_scale = ac_scale; a.noise = noise; a.seed = seed; a.index0 = index0; a.step0 = 0; a.step_base = step_base;
+  a.ac_out_f = cont ? reinterpret_cast<float*>(ac_out) : nullptr;
+  a.ac_out_i = cont ? nullptr : reinterpret_cast<int*>(ac_out);
+  a.logp_out = logp_out; a.ent_out = ent_out; a.x2_out = x2_out; a.x3_out = x3_out;
+  a.env_state = state; a.env_elapsed = elapsed; a.rew_out = rew_out; a.done_out = done_out; a.reset_u = reset_u;
+  a.max_steps = max_steps;
+  const int grid = tc_grid(1, n);                      // column tiles: a CTA keeps its tiles for all T steps
+  cudaStream_t st = (cudaStream_t)stream;
+  if (env == ACX_ENV_PENDULUM) return launch_tc<128, 64, true, HEAD_GAUSS, MODE_SAMPLE, ACX_ENV_PENDULUM>(a, packed, grid, st);
+  if (env == ACX_ENV_CARTPOLE) return launch_tc<128, 64, true, HEAD_CAT, MODE_SAMPLE, ACX_ENV_CARTPOLE>(a, packed, grid, st);
+  return launch_tc<128, 64, true, HEAD_CAT, MODE_SAMPLE, ACX_ENV_ACROBOT>(a, packed, grid, st);
 }
 
 #ifdef ACX_FWD_PROF

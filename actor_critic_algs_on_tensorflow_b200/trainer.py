@@ -58,7 +58,7 @@ class A2CTrainer:
                  desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1, actor_lr=0.005, critic_lr=0.001, beta=1.0,
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
                  critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=True,
-                 cache_activations=True, tensor_core_backward=True, frames=1):
+                 cache_activations=True, tensor_core_backward=True, frames=1, fused_rollout=True):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
@@ -91,6 +91,9 @@ class A2CTrainer:
         # back-propagation chain products on tcgen05 too (needs both of the above); the weight-gradient products stay
         # fp32 FFMA in the same kernel
         self.tc_bwd = bool(tensor_core_backward) and self.tc and self.cache
+        # the T-step rollout as ONE persistent kernel (policy forward + sampling + env step per step, env state in
+        # registers); bit-identical to the T x {sample, env step} launches it replaces
+        self.fused_rollout = bool(fused_rollout) and self.tc and int(frames) == 1
         d, f32 = self.dev, torch.float32
         N, T = self.N, self.T
 
@@ -181,6 +184,15 @@ class A2CTrainer:
 
     def _rollout(self, buffered_noise):
         s, N = L.cur_stream(), self.N
+        if self.fused_rollout:
+            L.call("acx_rollout_tc", self.env, L.ptr(self.actor), L.ptr(self.packed_a), self.ac_scale, self.T, N,
+                   L.ptr(self.obs_buf), L.ptr(self.state), L.ptr(self.elapsed),
+                   L.ptr(self.noise_buf) if buffered_noise else None, L.ptr(self.reset_u_buf) if buffered_noise else None,
+                   self.seed, self.index0, L.ptr(self.step_ctr), self.max_steps, L.ptr(self.acs), L.ptr(self.logps),
+                   L.ptr(self.ent), L.ptr(self.rew), L.ptr(self.done), L.ptr(self.ax2) if self.cache else None,
+                   L.ptr(self.ax3) if self.cache else None, s)
+            L.call("acx_counter_add", L.ptr(self.step_ctr), self.T, s)
+            return 2
         n = 0
         for t in range(self.T):
             noise = None if not buffered_noise else self._row(self.noise_buf, t)

@@ -186,6 +186,13 @@ def kernel_table(tr, flush, hbm_peak):
         L.ptr(tr.obs_buf), None, tr.seed, 0, 0, None, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent), None,
         L.ptr(tr.ax2) if tr.cache else None, L.ptr(tr.ax3) if tr.cache else None, s),
         FLOP_ACTOR_FWD * N, "tc")
+    if getattr(tr, "fused_rollout", False):
+        st3, el3 = tr.state.clone(), tr.elapsed.clone()
+        ks["rollout_tc, %d steps in one launch (K1 + K2, tcgen05 3xTF32)" % T] = (lambda: L.call(
+            "acx_rollout_tc", tr.env, L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ac_scale, T, N, L.ptr(tr.obs_buf), L.ptr(st3),
+            L.ptr(el3), None, None, tr.seed, 0, None, tr.max_steps, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent),
+            L.ptr(tr.rew), L.ptr(tr.done), L.ptr(tr.ax2) if tr.cache else None, L.ptr(tr.ax3) if tr.cache else None, s),
+            FLOP_ACTOR_FWD * B, "tc")
     ks["policy_logp_kl_tc (K2/K5, tcgen05 3xTF32)"] = (lambda: L.call(
         "acx_policy_logp_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, T, N,
         L.ptr(tr.obs_buf), L.ptr(tr.acs), None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part),

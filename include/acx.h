@@ -196,6 +196,21 @@ int acx_policy_forward_sample_cat_tc(const float* actor, const float* packed, in
                                      uint32_t step0, const uint32_t* step_base, int* ac_out, float* logp_out,
                                      float* ent_out, float* logits_out, float* x2_out, float* x3_out,
                                      void* stream);
+/* The whole rollout of A3C/process.py:73-98 for n environments and T steps in ONE launch: per step the policy forward +
+ * sampling of acx_policy_forward_sample_*_tc and the transition of acx_env_step (same arithmetic, same Philox
+ * counters: action noise and reset uniforms of step t use step = *step_base + t), with each environment's state in
+ * registers and the next observation handed to layer 1 through shared memory.  A CTA keeps its 128-env tiles for all T
+ * steps (environments are independent).  env: ACX_ENV_*; the head follows the env (Pendulum: Gaussian with ac_scale,
+ * CartPole / Acrobot: categorical).  obs[T+1][ob][n]: row 0 is the current observation (input), rows 1..T are written;
+ * state[S][n] / elapsed[n] are updated in place; noise: eps[T][1][n] (Gaussian) or u[T][n] (categorical) or NULL
+ * (Philox); reset_u[T][S][n] or NULL; outputs ac_out[T][1][n] float | [T][n] int32, logp_out / ent_out [T][n]
+ * (nullable), rew_out[T][n], done_out[T][n]; x2_out / x3_out: activation cache rows 0..T-1 (both or neither).
+ * Results are identical, bit for bit, to T x {acx_policy_forward_sample_*_tc; acx_env_step}. */
+int acx_rollout_tc(int env, const float* actor, const float* packed, float ac_scale, int T, int n, float* obs,
+                   float* state, int* elapsed, const float* noise, const float* reset_u, uint64_t seed,
+                   uint64_t index0, const uint32_t* step_base, int max_steps, void* ac_out, float* logp_out,
+                   float* ent_out, float* rew_out, unsigned char* done_out, float* x2_out, float* x3_out,
+                   void* stream);
 int acx_policy_logp_gauss_tc(const float* actor, const float* packed, int ob_dim, int ac_dim, float ac_scale,
                              int rows, int n, const float* obs, const float* acs, float* logp_out,
                              float* ent_out, float* mu_out, const float* logp_old, double* kl_partial,

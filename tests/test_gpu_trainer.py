@@ -81,6 +81,34 @@ def test_frames_beyond_the_kernel_input_width_are_refused():
         A2CTrainer("Pendulum-v0", n_envs=64, horizon=2, frames=3)
 
 
+@pytest.mark.parametrize("env_id,N,T,max_steps", [("Pendulum-v0", 1024, 6, 3), ("Pendulum-v0", 200, 5, 0),
+                                                  ("CartPole-v0", 640, 9, 4), ("Acrobot-v1", 384, 5, 3)])
+@pytest.mark.parametrize("buffered", [False, True])
+def test_persistent_rollout_kernel_equals_the_per_step_launches(env_id, N, T, max_steps, buffered):
+    """acx_rollout_tc (one launch: T x {policy forward + sampling + env step}, env state in registers) against the
+    T x {acx_policy_forward_sample_*_tc; acx_env_step} launches it replaces: every buffer bit-identical, over two
+    iterations (so resets, the step counter and the carried observation row are exercised), with the device Philox
+    streams and with caller-supplied noise / reset uniforms."""
+    trs = [A2CTrainer(env_id, n_envs=N, horizon=T, seed=11, use_graph=False, max_episode_steps=max_steps, fused_rollout=f)
+           for f in (True, False)]
+    assert trs[0].fused_rollout and not trs[1].fused_rollout
+    gen = torch.Generator().manual_seed(5)
+    for it in range(2):
+        kw = {}
+        if buffered:
+            cont = trs[0].cont
+            kw = dict(noise=torch.randn((T, 1, N), generator=gen) if cont else torch.rand((T, N), generator=gen),
+                      reset_u=torch.rand((T, trs[0].S, N), generator=gen))
+        for tr in trs:
+            tr.iteration(**kw)
+        torch.cuda.synchronize()
+        a, b = trs
+        for name in ("obs_buf", "acs", "logps", "ent", "rew", "done", "state", "elapsed", "ax2", "ax3", "V", "G", "params"):
+            np.testing.assert_array_equal(getattr(a, name).cpu().numpy(), getattr(b, name).cpu().numpy(), err_msg=name)
+    assert trs[0].done.sum().item() > 0 or max_steps == 0
+    assert trs[0].step_ctr.item() == 2 * T
+
+
 def test_graph_replay_equals_eager_launches():
     outs = []
     for use_graph in (False, True):
