@@ -169,8 +169,8 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
     };
     if ((int)blockIdx.x < ntiles) issue_x3(blockIdx.x, 0);
     // act'(X2) of this thread's 64 features comes straight from the cache (coalesced loads) as two 32-bit masks.  The
-    // loads are software-pipelined so that none is waited for: the upper 32 of a tile are issued during the previous
-    // tile's layer-1 phase, the lower 32 at the start of the tile (they have until dX2 is done).
+    // loads are software-pipelined: the upper 32 of a tile are issued during the previous tile's layer-1 phase, the
+    // lower 32 once dPre3 is handed over (they have until dX2 is done).
     float xm[32];
     auto load_x2 = [&](int tile, int q) {
       const float* g2 = A.x2_in + cache_tile_off(tile, H2) + (size_t)(q * 64 + half * 32) * MT + s;
@@ -221,7 +221,6 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       }
       unsigned int m2[2];
       m2[1] = pack_x2();
-      load_x2(tile, 0);
       PROF_MARK(12);
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[buf]), act_phase[buf] & 1u);
       ++act_phase[buf];
@@ -305,6 +304,8 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
           mbar_arrive1(&sm.a_ready[gq]);           // reduction features gq*64 .. +63 of the A operand are in place
         }
       }
+      load_x2(tile, 0);                             // lower 32 act'(X2) values: in flight while dX2 is formed (not earlier:
+                                                    // 32 more live registers across the head spill in the Gaussian kernel)
       fence_proxy_async();
       work_sync();
       bulk_rows_out(S, d3_out + cache_tile_off(tile, H3), H3);
