@@ -11,7 +11,9 @@ ki, vi, ui = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Met
 last = rows[1:][-int(sys.argv[2]):]
 agg = collections.OrderedDict()
 for r in last:
-    name = r[ki].split("(")[0].replace("void ", "").replace("<unnamed>::", "")
+    name = r[ki]
+    name = name[:name.find(">(") + 1] if ">(" in name else name.split("(")[0]
+    name = name.replace("void ", "").replace("<unnamed>::", "").replace("(int)", "")
     v = float(r[vi].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0}[r[ui]]
     agg.setdefault(name, [0, 0.0])
     agg[name][0] += 1
