@@ -62,19 +62,20 @@ SIGNATURES = {
     "acx_loss_backward_cat_cached": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_frame_push": (_i, [_i, _i, _i, _p, _p, _p, _p, _p]),
     "acx_activation_cache_floats": (_sz, [_i, _i, _i]),
+    "acx_act_mask_words": (_sz, [_i, _i, _i]),
     "acx_tc_packed_bwd_floats": (_sz, [_i, _i, _i, _i]),
     "acx_loss_backward_tc_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "acx_tc_pack_weights_bwd": (_i, [_i, _p, _i, _i, _i, _p, _p]),
-    "acx_loss_backward_gauss_tc": (_i, [_p, _p, _p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
-    "acx_loss_backward_cat_tc": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "acx_loss_backward_gauss_tc": (_i, [_p, _p, _p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "acx_loss_backward_cat_tc": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_tc_packed_floats": (_sz, [_i, _i, _i, _i]),
     "acx_tc_pack_weights": (_i, [_i, _p, _i, _i, _i, _p, _p]),
     "acx_policy_forward_sample_gauss_tc": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _u64, _u64, _u32, _p, _p, _p, _p, _p, _p, _p, _p]),
     "acx_policy_forward_sample_cat_tc": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _u64, _u64, _u32, _p, _p, _p, _p, _p, _p, _p, _p]),
-    "acx_rollout_tc": (_i, [_i, _p, _p, _f, _i, _i, _p, _p, _p, _p, _p, _u64, _u64, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "acx_rollout_tc": (_i, [_i, _p, _p, _f, _i, _i, _p, _p, _p, _p, _p, _u64, _u64, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "acx_policy_logp_gauss_tc": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _ip, _p]),
     "acx_policy_logp_cat_tc": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _ip, _p]),
-    "acx_value_forward_tc": (_i, [_p, _p, _i, _i, _i, _p, _p, _i, _p, _p, _p]),
+    "acx_value_forward_tc": (_i, [_p, _p, _i, _i, _i, _p, _p, _i, _p, _p, _p, _p]),
     "acx_returns_adv_workspace_bytes": (_sz, [_i, _i]),
     "acx_returns_adv_scan": (_i, [_i, _i, _p, _p, _p, _d, _i, _p, _p, _p, _p, _sz, _i, _p]),
     "acx_returns_adv_scan_static": (_i, [_i, _i, _p, _p, _p, _d, _i, _p, _p, _p, _i, _p]),

@@ -77,6 +77,11 @@ struct Args {
   float* x3_out;
   const float* x2_in;
   const float* x3_in;
+  // activation sign masks (tensor-core path, optional): per tile NW = H1/32 + 4 words x 128 samples, u32; word w < H1/32:
+  // bit e = X1[32 w + e] > 0, word H1/32 + w: bit e = X2[32 w + e] > 0.  Written by the forward kernels, read by the
+  // chain kernel instead of re-deriving act'(X2) from the cache and act'(X1) from the observations.
+  unsigned int* mask_out;
+  const unsigned int* mask_in;
   // persistent rollout (acx_rollout_tc): the env step runs in the sampling head, rows = T time steps of the same envs
   float* env_state;          // [S][n], read before the first step, written after the last
   int* env_elapsed;          // [n]
@@ -107,6 +112,7 @@ struct Smem {
 
 // float offset of tile `tile` (= row * tiles_per_row + tile_in_row) of a tile-blocked [..][F][128] array
 __host__ __device__ inline size_t cache_tile_off(int tile, int F) { return (size_t)tile * F * MT; }
+__host__ __device__ inline size_t mask_tile_off(int tile, int H1) { return (size_t)tile * (H1 / 32 + 4) * MT; }
 __host__ __device__ inline size_t cache_floats(int rows, int F, int n) {
   return (size_t)(rows > 0 ? rows : 0) * (size_t)((n + MT - 1) / MT) * F * MT;
 }

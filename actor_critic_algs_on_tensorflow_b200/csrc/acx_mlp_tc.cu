@@ -312,6 +312,12 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
               v[e] = act_fn<LRELU>(__fadd_rn(acc, sm.b1[k]));
             }
           }
+          if (A.mask_out != nullptr) {             // act'(X1) for the chain kernel
+            unsigned int bits = 0u;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
+            A.mask_out[mask_tile_off(tile, H1) + (size_t)(blk * 4 + gq * 2 + half) * MT + s] = bits;
+          }
           if (blk > 0 && gq == 0) {                // the MMAs reading the previous block must be done
             FPROF(1);
             acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
@@ -337,6 +343,12 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         tmem_ld32(tl + TC_D2 + (uint32_t)j0, v);
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b2[j0 + e]));
+        if (A.mask_out != nullptr) {               // act'(X2)
+          unsigned int bits = 0u;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
+          A.mask_out[mask_tile_off(tile, H1) + (size_t)(H1 / 32 + gq * 2 + half) * MT + s] = bits;
+        }
         if (A.x2_out != nullptr) {                 // tile-blocked cache; zeros beyond the batch
           float* g2 = A.x2_out + cache_tile_off(tile, H2) + (size_t)j0 * MT + s;
 #pragma unroll
@@ -667,6 +679,7 @@ extern "C" int acx_policy_logp_cat_tc(const float* actor, const float* packed, i
 
 extern "C" int acx_value_forward_tc(const float* critic, const float* packed, int ob_dim, int rows, int n,
                                     const float* obs, float* v_out, int basic_head, float* x2_out, float* x3_out,
+                                    unsigned int* mask_out,
                                     void* stream) {
   int rc = tc_check("acx_value_forward_tc", critic, packed, ob_dim, 1, rows, n, obs);
   if (rc) return rc;
@@ -675,7 +688,7 @@ extern "C" int acx_value_forward_tc(const float* critic, const float* packed, in
   ACX_REQUIRE((x2_out == nullptr) == (x3_out == nullptr), "acx_value_forward_tc: give both caches or none");
   Args a; memset(&a, 0, sizeof(a));
   a.params = critic; a.L = acx_critic_layout(ob_dim); a.rows = rows; a.n = n; a.obs = obs;
-  a.v_out = v_out; a.basic_head = basic_head; a.x2_out = x2_out; a.x3_out = x3_out;
+  a.v_out = v_out; a.basic_head = basic_head; a.x2_out = x2_out; a.x3_out = x3_out; a.mask_out = mask_out;
   return launch_tc<256, 128, false, HEAD_VALUE, MODE_EVAL>(a, packed, tc_grid(rows, n), (cudaStream_t)stream);
 }
 
@@ -683,6 +696,7 @@ extern "C" int acx_rollout_tc(int env, const float* actor, const float* packed, 
                               float* state, int* elapsed, const float* noise, const float* reset_u, uint64_t seed,
                               uint64_t index0, const uint32_t* step_base, int max_steps, void* ac_out, float* logp_out,
                               float* ent_out, float* rew_out, unsigned char* done_out, float* x2_out, float* x3_out,
+                              unsigned int* mask_out,
                               void* stream) {
   ACX_REQUIRE(env == ACX_ENV_PENDULUM || env == ACX_ENV_CARTPOLE || env == ACX_ENV_ACROBOT,
               "acx_rollout_tc: unknown env id %d", env);
@@ -698,7 +712,7 @@ extern "C" int acx_rollout_tc(int env, const float* actor, const float* packed, 
   a.ac_scale = ac_scale; a.noise = noise; a.seed = seed; a.index0 = index0; a.step0 = 0; a.step_base = step_base;
   a.ac_out_f = cont ? reinterpret_cast<float*>(ac_out) : nullptr;
   a.ac_out_i = cont ? nullptr : reinterpret_cast<int*>(ac_out);
-  a.logp_out = logp_out; a.ent_out = ent_out; a.x2_out = x2_out; a.x3_out = x3_out;
+  a.logp_out = logp_out; a.ent_out = ent_out; a.x2_out = x2_out; a.x3_out = x3_out; a.mask_out = mask_out;
   a.env_state = state; a.env_elapsed = elapsed; a.rew_out = rew_out; a.done_out = done_out; a.reset_u = reset_u;
   a.max_steps = max_steps;
   const int grid = tc_grid(1, n);                      // column tiles: a CTA keeps its tiles for all T steps

@@ -50,7 +50,9 @@ struct TcSmem {
   unsigned int tmem_base;
 };
 
-template <int H1, int H3, bool LRELU, int HEAD>
+// MASKS: act'(X2) / act'(X1) come as the sign-mask words the forward kernels stored (A.mask_in) instead of being
+// re-derived from the X2 cache (64 loads per thread) and the observations (ob_dim FMAs per element).
+template <int H1, int H3, bool LRELU, int HEAD, bool MASKS>
 __global__ void __launch_bounds__(TT_NT, 1)
 acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* __restrict__ d3_out,
                         float* __restrict__ d2_out) {
@@ -188,7 +190,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       for (int e = 0; e < 32; ++e) m |= (xm[e] > 0.f ? 1u : 0u) << e;
       return m;
     };
-    load_x2(blockIdx.x, 1);
+    if (!MASKS) load_x2(blockIdx.x, 1);
 
     // staged dense tile (nrows x 128 floats) -> its block in HBM: one bulk-TMA store, off the load/store pipe (as plain
     // stores the 64 + 64 KB per tile queued in front of every later global load of the SM)
@@ -219,8 +221,18 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         if (next < ntiles && tid < MT && (next % tpr) * MT + tid < A.n)
           head_train_prefetch<HEAD>(A, nout, next / tpr, (size_t)(next % tpr) * MT + tid);
       }
-      unsigned int m2[2];
-      m2[1] = pack_x2();
+      unsigned int m2[2], m1[NB][2];
+      if (MASKS) {      // this thread's mask words of the tile: X2 features gq*64 + half*32.., X1 features half*64 + gq*32..
+        const unsigned int* mk = A.mask_in + mask_tile_off(tile, H1) + s;
+#pragma unroll
+        for (int gq = 0; gq < 2; ++gq) {
+          m2[gq] = __ldg(mk + (H1 / 32 + gq * 2 + half) * MT);
+#pragma unroll
+          for (int h = 0; h < NB; ++h) m1[h][gq] = __ldg(mk + (h * 4 + half * 2 + gq) * MT);
+        }
+      } else {
+        m2[1] = pack_x2();
+      }
       PROF_MARK(12);
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[buf]), act_phase[buf] & 1u);
       ++act_phase[buf];
@@ -304,7 +316,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
           mbar_arrive1(&sm.a_ready[gq]);           // reduction features gq*64 .. +63 of the A operand are in place
         }
       }
-      load_x2(tile, 0);                             // lower 32 act'(X2) values: in flight while dX2 is formed (not earlier:
+      if (!MASKS) load_x2(tile, 0);                 // lower 32 act'(X2) values: in flight while dX2 is formed (not earlier:
                                                     // 32 more live registers across the head spill in the Gaussian kernel)
       fence_proxy_async();
       work_sync();
@@ -316,7 +328,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       PROF_MARK(4);
       bulk_rows_read_done();                        // dPre3 has left S: it takes dPre2 next
       work_sync();
-      m2[0] = pack_x2();
+      if (!MASKS) m2[0] = pack_x2();
 #pragma unroll 1
       for (int gq = 0; gq < 2; ++gq) {
         const unsigned int bits = m2[gq];
@@ -337,7 +349,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       work_sync();
       bulk_rows_out(S, d2_out + cache_tile_off(tile, H2), H2);
       PROF_MARK(15);
-      load_x2(tile + gridDim.x, 1);                 // next tile's upper 32 (zeros past the last tile)
+      if (!MASKS) load_x2(tile + gridDim.x, 1);     // next tile's upper 32 (zeros past the last tile)
       // this thread's observation (registers; also the shared copy layer1_grad reads), while dX1 is formed
       float ob_r[MAX_OB];
 #pragma unroll
@@ -361,7 +373,11 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
           float v[32];
           const int k0 = half * 64 + gq * 32;
           tmem_ld32(tl + (h == 0 ? TT_D1 : TT_D0) + (uint32_t)k0, v);
-          if (ob <= 3) {
+          if (MASKS) {
+            const unsigned int bits = m1[h][gq];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[e] *= ((bits >> e) & 1u) ? 1.0f : SLOPE;
+          } else if (ob <= 3) {
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
               const float4 w = sm.W1p[h * 128 + k0 + e];
@@ -478,13 +494,19 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
   if (warp == 8) tmem_dealloc(tmem, 512);
 }
 
-template <int H1, int H3, bool LRELU, int HEAD>
-int launch_chain(const Args& a, const float* packed, float* d3, float* d2, int grid, cudaStream_t st) {
-  auto kern = acx_mlp_tc_chain_kernel<H1, H3, LRELU, HEAD>;
+template <int H1, int H3, bool LRELU, int HEAD, bool MASKS>
+int launch_chain1(const Args& a, const float* packed, float* d3, float* d2, int grid, cudaStream_t st) {
+  auto kern = acx_mlp_tc_chain_kernel<H1, H3, LRELU, HEAD, MASKS>;
   ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem) + 1024));
   kern<<<grid, TT_NT, sizeof(TcSmem) + 1024, st>>>(a, packed, d3, d2);
   ACX_LAUNCH_OK("acx_mlp_tc_chain_kernel");
   return ACX_OK;
+}
+
+template <int H1, int H3, bool LRELU, int HEAD>
+int launch_chain(const Args& a, const float* packed, float* d3, float* d2, int grid, cudaStream_t st) {
+  return a.mask_in != nullptr ? launch_chain1<H1, H3, LRELU, HEAD, true>(a, packed, d3, d2, grid, st)
+                              : launch_chain1<H1, H3, LRELU, HEAD, false>(a, packed, d3, d2, grid, st);
 }
 
 }  // namespace

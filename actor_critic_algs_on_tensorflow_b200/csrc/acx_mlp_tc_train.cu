@@ -392,7 +392,8 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
                      const float* obs, const void* acs, const float* adv, const float* adv_stats,
                      const float* logp_old, const float* targets, const float* opt, float* grad_actor,
                      float* grad_critic, float* stats, const float* ax2, const float* ax3, const float* cx2,
-                     const float* cx3, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+                     const float* cx3, const unsigned int* amask, const unsigned int* cmask, void* workspace,
+                     size_t workspace_bytes, cudaStream_t st) {
   const char* fn = cont ? "acx_loss_backward_gauss_tc" : "acx_loss_backward_cat_tc";
   ACX_REQUIRE(actor || critic, "%s: neither actor nor critic given", fn);
   ACX_REQUIRE(rows >= 1 && n >= 1, "%s: empty batch (rows=%d, n=%d): the mean loss is undefined", fn, rows, n);
@@ -427,7 +428,7 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
     a.ac_in_f = cont ? reinterpret_cast<const float*>(acs) : nullptr;
     a.ac_in_i = cont ? nullptr : reinterpret_cast<const int*>(acs);
     a.adv = adv; a.adv_stats = adv_stats; a.logp_old = logp_old; a.opt = opt;
-    a.scratch = scr_a; a.loss_partial = lossp_a; a.x2_in = ax2; a.x3_in = ax3;
+    a.scratch = scr_a; a.loss_partial = lossp_a; a.x2_in = ax2; a.x3_in = ax3; a.mask_in = amask;
     int rc = cont ? launch_tt<128, 64, true, HEAD_GAUSS>(a, actor_packed, split, grid, st)
                   : launch_tt<128, 64, true, HEAD_CAT>(a, actor_packed, split, grid, st);
     if (rc) return rc;
@@ -441,7 +442,7 @@ int loss_backward_tc(int cont, const float* actor, const float* critic, const fl
                 "%s: null / misaligned critic-side buffer (packed weights and the activation cache are required)", fn);
     Args a; memset(&a, 0, sizeof(a));
     a.params = critic; a.L = Lc; a.rows = rows; a.n = n; a.obs = obs;
-    a.targets = targets; a.scratch = scr_c; a.loss_partial = lossp_c; a.x2_in = cx2; a.x3_in = cx3;
+    a.targets = targets; a.scratch = scr_c; a.loss_partial = lossp_c; a.x2_in = cx2; a.x3_in = cx3; a.mask_in = cmask;
     int rc = launch_tt<256, 128, false, HEAD_VALUE>(a, critic_packed, split, grid, st);
     if (rc) return rc;
     acx_grad_reduce_tc_kernel<<<(Lc.size + 255) / 256, 256, 0, st>>>(scr_c, grid, Lc.size, grad_critic, lossp_c, stats,
@@ -462,6 +463,11 @@ extern "C" size_t acx_loss_backward_tc_workspace_bytes(int ob_dim, int num_ac, i
   const size_t base_bytes = (acx_loss_backward_workspace_bytes(ob_dim, num_ac, cont) + 255) & ~(size_t)255;
   const size_t feat = (size_t)(ACX_C_H3 > ACX_A_H3 ? ACX_C_H3 : ACX_A_H3) + H2;      // dPre3 + dPre2 of one network
   return base_bytes + cache_floats(rows, (int)feat, n) * sizeof(float);
+}
+
+extern "C" size_t acx_act_mask_words(int net, int rows, int n) {
+  const int h1 = net == 0 ? ACX_A_H1 : ACX_C_H1;
+  return (size_t)(rows > 0 ? rows : 0) * (size_t)(((n > 0 ? n : 0) + MT - 1) / MT) * (size_t)(h1 / 32 + 4) * MT;
 }
 
 extern "C" size_t acx_tc_packed_bwd_floats(int net, int ob_dim, int num_ac, int cont) {
@@ -486,11 +492,13 @@ extern "C" int acx_loss_backward_gauss_tc(const float* actor, const float* criti
                                           const float* adv_stats, const float* logp_old, const float* targets,
                                           const float* opt, float* grad_actor, float* grad_critic, float* stats,
                                           const float* actor_x2, const float* actor_x3, const float* critic_x2,
-                                          const float* critic_x3, void* workspace, size_t workspace_bytes,
+                                          const float* critic_x3, const unsigned int* actor_masks,
+                                          const unsigned int* critic_masks, void* workspace, size_t workspace_bytes,
                                           void* stream) {
   return loss_backward_tc(1, actor, critic, actor_packed_bwd, critic_packed_bwd, ob_dim, ac_dim, ac_scale, rows, n, obs,
                           acs, adv, adv_stats, logp_old, targets, opt, grad_actor, grad_critic, stats, actor_x2,
-                          actor_x3, critic_x2, critic_x3, workspace, workspace_bytes, (cudaStream_t)stream);
+                          actor_x3, critic_x2, critic_x3, actor_masks, critic_masks, workspace, workspace_bytes,
+                          (cudaStream_t)stream);
 }
 
 extern "C" int acx_loss_backward_cat_tc(const float* actor, const float* critic, const float* actor_packed_bwd,
@@ -499,8 +507,10 @@ extern "C" int acx_loss_backward_cat_tc(const float* actor, const float* critic,
                                         const float* logp_old, const float* targets, const float* opt,
                                         float* grad_actor, float* grad_critic, float* stats, const float* actor_x2,
                                         const float* actor_x3, const float* critic_x2, const float* critic_x3,
+                                        const unsigned int* actor_masks, const unsigned int* critic_masks,
                                         void* workspace, size_t workspace_bytes, void* stream) {
   return loss_backward_tc(0, actor, critic, actor_packed_bwd, critic_packed_bwd, ob_dim, n_act, 0.f, rows, n, obs, acs,
                           adv, adv_stats, logp_old, targets, opt, grad_actor, grad_critic, stats, actor_x2, actor_x3,
-                          critic_x2, critic_x3, workspace, workspace_bytes, (cudaStream_t)stream);
+                          critic_x2, critic_x3, actor_masks, critic_masks, workspace, workspace_bytes,
+                          (cudaStream_t)stream);
 }

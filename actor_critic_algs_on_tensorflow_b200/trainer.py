@@ -143,6 +143,12 @@ class A2CTrainer:
             self.ax3 = torch.empty((T, per(64)), device=d, dtype=f32)
             self.cx2 = torch.empty((T + 1, per(128)), device=d, dtype=f32)
             self.cx3 = torch.empty((T + 1, per(128)), device=d, dtype=f32)
+        # activation sign masks for the tensor-core backward (written by the value pass and the fused rollout)
+        self.amask = self.cmask = None
+        if self.tc_bwd:
+            self.cmask = torch.empty(L.load().acx_act_mask_words(1, T + 1, N), device=d, dtype=torch.int32)
+            if self.fused_rollout:
+                self.amask = torch.empty(L.load().acx_act_mask_words(0, T, N), device=d, dtype=torch.int32)
         self.packed_a = torch.zeros(L.load().acx_tc_packed_floats(0, self.ob, self.num_ac, int(self.cont)), device=d)
         self.packed_c = torch.zeros(L.load().acx_tc_packed_floats(1, self.ob, 1, 0), device=d)
         self.packed_bwd_a = torch.zeros(L.load().acx_tc_packed_bwd_floats(0, self.ob, self.num_ac, int(self.cont)), device=d)
@@ -190,7 +196,7 @@ class A2CTrainer:
                    L.ptr(self.noise_buf) if buffered_noise else None, L.ptr(self.reset_u_buf) if buffered_noise else None,
                    self.seed, self.index0, L.ptr(self.step_ctr), self.max_steps, L.ptr(self.acs), L.ptr(self.logps),
                    L.ptr(self.ent), L.ptr(self.rew), L.ptr(self.done), L.ptr(self.ax2) if self.cache else None,
-                   L.ptr(self.ax3) if self.cache else None, s)
+                   L.ptr(self.ax3) if self.cache else None, L.ptr(self.amask), s)
             L.call("acx_counter_add", L.ptr(self.step_ctr), self.T, s)
             return 2
         n = 0
@@ -233,7 +239,7 @@ class A2CTrainer:
         if self.tc:
             L.call("acx_value_forward_tc", L.ptr(self.critic), L.ptr(self.packed_c), self.ob, T + 1, N,
                    L.ptr(self.obs_buf), L.ptr(self.V), 0, L.ptr(self.cx2) if self.cache else None,
-                   L.ptr(self.cx3) if self.cache else None, s)
+                   L.ptr(self.cx3) if self.cache else None, L.ptr(self.cmask), s)
         elif self.cache:
             L.call("acx_value_forward_cached", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V),
                    0, L.ptr(self.cx2), L.ptr(self.cx3), s)
@@ -247,7 +253,8 @@ class A2CTrainer:
                   L.ptr(self.G), L.ptr(self.opt), L.ptr(ga), L.ptr(gc), L.ptr(self.stats), L.ptr(self.ws_bwd),
                   self.ws_bwd_bytes, s)
         if self.tc_bwd:
-            cached = common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3)) + common[-3:]
+            cached = (common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3), L.ptr(self.amask),
+                                     L.ptr(self.cmask)) + common[-3:])
             head = (L.ptr(self.actor), L.ptr(self.critic), L.ptr(self.packed_bwd_a), L.ptr(self.packed_bwd_c), self.ob)
             if self.cont:
                 L.call("acx_loss_backward_gauss_tc", *head, self.num_ac, self.ac_scale, T, N, *cached)

@@ -179,7 +179,7 @@ def kernel_table(tr, flush, hbm_peak):
             L.ptr(tr.ax2), L.ptr(tr.ax3), s), FLOP_ACTOR_FWD * N, None)
     ks["value_forward_tc (K2, tcgen05 3xTF32)"] = (lambda: L.call(
         "acx_value_forward_tc", L.ptr(tr.critic), L.ptr(tr.packed_c), tr.ob, T + 1, N, L.ptr(tr.obs_buf), L.ptr(tr.V), 0,
-        L.ptr(tr.cx2) if tr.cache else None, L.ptr(tr.cx3) if tr.cache else None, s),
+        L.ptr(tr.cx2) if tr.cache else None, L.ptr(tr.cx3) if tr.cache else None, L.ptr(getattr(tr, "cmask", None)), s),
         FLOP_CRITIC_FWD * (T + 1) * N, "tc")
     ks["policy_forward_sample_tc (K2, tcgen05 3xTF32)"] = (lambda: L.call(
         "acx_policy_forward_sample_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, 1, N,
@@ -191,8 +191,8 @@ def kernel_table(tr, flush, hbm_peak):
         ks["rollout_tc, %d steps in one launch (K1 + K2, tcgen05 3xTF32)" % T] = (lambda: L.call(
             "acx_rollout_tc", tr.env, L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ac_scale, T, N, L.ptr(tr.obs_buf), L.ptr(st3),
             L.ptr(el3), None, None, tr.seed, 0, None, tr.max_steps, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent),
-            L.ptr(tr.rew), L.ptr(tr.done), L.ptr(tr.ax2) if tr.cache else None, L.ptr(tr.ax3) if tr.cache else None, s),
-            FLOP_ACTOR_FWD * B, "tc")
+            L.ptr(tr.rew), L.ptr(tr.done), L.ptr(tr.ax2) if tr.cache else None, L.ptr(tr.ax3) if tr.cache else None,
+            L.ptr(getattr(tr, "amask", None)), s), FLOP_ACTOR_FWD * B, "tc")
     ks["policy_logp_kl_tc (K2/K5, tcgen05 3xTF32)"] = (lambda: L.call(
         "acx_policy_logp_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, T, N,
         L.ptr(tr.obs_buf), L.ptr(tr.acs), None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part),
@@ -201,7 +201,7 @@ def kernel_table(tr, flush, hbm_peak):
         base_bytes = L.load().acx_loss_backward_workspace_bytes(tr.ob, tr.num_ac, int(tr.cont))
 
         def bwd_t(actor, critic, nbytes):
-            args = cached[:-2] + (nbytes, s)
+            args = cached[:-3] + (L.ptr(getattr(tr, "amask", None)), L.ptr(getattr(tr, "cmask", None))) + (cached[-3], nbytes, s)
             return lambda: L.call("acx_loss_backward_gauss_tc", actor, critic, L.ptr(tr.packed_bwd_a),
                                   L.ptr(tr.packed_bwd_c), tr.ob, tr.num_ac, tr.ac_scale, T, N, *args)
         # one kernel: chain products on tcgen05, weight-gradient products FFMA (small workspace)

@@ -209,7 +209,7 @@ int acx_policy_forward_sample_cat_tc(const float* actor, const float* packed, in
 int acx_rollout_tc(int env, const float* actor, const float* packed, float ac_scale, int T, int n, float* obs,
                    float* state, int* elapsed, const float* noise, const float* reset_u, uint64_t seed,
                    uint64_t index0, const uint32_t* step_base, int max_steps, void* ac_out, float* logp_out,
-                   float* ent_out, float* rew_out, unsigned char* done_out, float* x2_out, float* x3_out,
+                   float* ent_out, float* rew_out, unsigned char* done_out, float* x2_out, float* x3_out, unsigned int* mask_out,
                    void* stream);
 int acx_policy_logp_gauss_tc(const float* actor, const float* packed, int ob_dim, int ac_dim, float ac_scale,
                              int rows, int n, const float* obs, const float* acs, float* logp_out,
@@ -220,7 +220,7 @@ int acx_policy_logp_cat_tc(const float* actor, const float* packed, int ob_dim, 
                            float* logits_out, const float* logp_old, double* kl_partial,
                            int* kl_blocks /*host*/, void* stream);
 int acx_value_forward_tc(const float* critic, const float* packed, int ob_dim, int rows, int n,
-                         const float* obs, float* v_out, int basic_head, float* x2_out, float* x3_out,
+                         const float* obs, float* v_out, int basic_head, float* x2_out, float* x3_out, unsigned int* mask_out,
                          void* stream);
 
 /* ---------------------------------------------------------------- K3: returns / advantages
@@ -300,6 +300,12 @@ int acx_loss_backward_cat_cached(const float* actor, const float* critic, int ob
  * one network, tile-blocked like the cache) and n % 4 == 0 they run on the tensor cores too, in a second kernel
  * per network (acx_wgrad_kernel: TMA tensor loads, 128-byte swizzle, accumulators in tensor memory). */
 size_t acx_loss_backward_tc_workspace_bytes(int ob_dim, int num_ac, int cont, int rows, int n);
+/* Activation sign masks (optional, nullable everywhere): acx_value_forward_tc / acx_rollout_tc can store, per 128-sample
+ * tile, one 32-bit word per 32 features and sample of "X1 > 0" and "X2 > 0" (acx_act_mask_words(net, rows, n) uint32
+ * words, 16-byte aligned; net 0 = actor, 1 = critic); acx_loss_backward_*_tc given the same array (actor_masks /
+ * critic_masks) reads act'(X1) / act'(X2) from it instead of re-deriving them from the X2 cache (64 loads per thread)
+ * and the observations.  Same results. */
+size_t acx_act_mask_words(int net, int rows, int n);
 size_t acx_tc_packed_bwd_floats(int net, int ob_dim, int num_ac, int cont);
 int acx_tc_pack_weights_bwd(int net, const float* params, int ob_dim, int num_ac, int cont, float* packed,
                             void* stream);
@@ -309,13 +315,15 @@ int acx_loss_backward_gauss_tc(const float* actor, const float* critic, const fl
                                const float* adv_stats, const float* logp_old, const float* targets,
                                const float* opt, float* grad_actor, float* grad_critic, float* stats,
                                const float* actor_x2, const float* actor_x3, const float* critic_x2,
-                               const float* critic_x3, void* workspace, size_t workspace_bytes, void* stream);
+                               const float* critic_x3, const unsigned int* actor_masks,
+                               const unsigned int* critic_masks, void* workspace, size_t workspace_bytes, void* stream);
 int acx_loss_backward_cat_tc(const float* actor, const float* critic, const float* actor_packed_bwd,
                              const float* critic_packed_bwd, int ob_dim, int n_act, int rows, int n,
                              const float* obs, const int* acs, const float* adv, const float* adv_stats,
                              const float* logp_old, const float* targets, const float* opt, float* grad_actor,
                              float* grad_critic, float* stats, const float* actor_x2, const float* actor_x3,
-                             const float* critic_x2, const float* critic_x3, void* workspace,
+                             const float* critic_x2, const float* critic_x3, const unsigned int* actor_masks,
+                               const unsigned int* critic_masks, void* workspace,
                              size_t workspace_bytes, void* stream);
 
 /* Critic loss + gradient for the Basic_AC network, whose value head reads the SECOND layer

@@ -24,7 +24,7 @@ for which in ("actor", "critic"):
     ga, gc = tr.grads[:tr.Pa], tr.grads[tr.Pa:]
     common = (L.ptr(tr.obs_buf), L.ptr(tr.acs), L.ptr(tr.adv), L.ptr(tr.stats), L.ptr(tr.logps), L.ptr(tr.G), L.ptr(tr.opt),
               L.ptr(ga), L.ptr(gc), L.ptr(tr.stats), L.ptr(tr.ax2), L.ptr(tr.ax3), L.ptr(tr.cx2), L.ptr(tr.cx3),
-              L.ptr(tr.ws_bwd), tr.ws_bwd_bytes, s)
+              L.ptr(tr.amask), L.ptr(tr.cmask), L.ptr(tr.ws_bwd), tr.ws_bwd_bytes, s)
     L.call("acx_loss_backward_gauss_tc", L.ptr(tr.actor) if which == "actor" else None,
            L.ptr(tr.critic) if which == "critic" else None, L.ptr(tr.packed_bwd_a), L.ptr(tr.packed_bwd_c), tr.ob,
            tr.num_ac, tr.ac_scale, tr.T, tr.N, *common)

@@ -24,7 +24,7 @@ T, N = tr.T, tr.N
 for which in ("value", "logp"):
     if which == "value":
         L.call("acx_value_forward_tc", L.ptr(tr.critic), L.ptr(tr.packed_c), tr.ob, T + 1, N, L.ptr(tr.obs_buf), L.ptr(tr.V),
-               0, L.ptr(tr.cx2), L.ptr(tr.cx3), s)
+               0, L.ptr(tr.cx2), L.ptr(tr.cx3), L.ptr(tr.cmask), s)
         tiles = (T + 1) * 512 / 148
     else:
         L.call("acx_policy_logp_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, T, N,

@@ -84,13 +84,26 @@ class Case:
         lib.call("acx_tc_pack_weights_bwd", 0, lib.ptr(self.a), ob, num_ac, int(cont), lib.ptr(self.pa), s)
         lib.call("acx_tc_pack_weights_bwd", 1, lib.ptr(self.c), ob, 1, 0, lib.ptr(self.pc), s)
 
-    def run(self, which, actor=True, critic=True):
+    def critic_forward_tc_with_masks(self):
+        """Refill the critic's caches with the tensor-core value pass, which also stores the activation sign masks."""
+        lib = self.lib
+        pf = torch.zeros(lib.load().acx_tc_packed_floats(1, self.ob, 1, 0), device=self.dev)
+        lib.call("acx_tc_pack_weights", 1, lib.ptr(self.c), self.ob, 1, 0, lib.ptr(pf), lib.cur_stream())
+        self.cmask = torch.zeros(lib.load().acx_act_mask_words(1, self.rows, self.n), device=self.dev, dtype=torch.int32)
+        v = torch.empty((self.rows, self.n), device=self.dev)
+        lib.call("acx_value_forward_tc", lib.ptr(self.c), lib.ptr(pf), self.ob, self.rows, self.n, lib.ptr(self.o),
+                 lib.ptr(v), 0, lib.ptr(self.cx2), lib.ptr(self.cx3), lib.ptr(self.cmask), lib.cur_stream())
+        torch.cuda.synchronize()
+
+    def run(self, which, actor=True, critic=True, critic_masks=False):
         lib = self.lib
         ga, gc = torch.full_like(self.a, 7.0), torch.full_like(self.c, 7.0)
         stats = torch.zeros(16, device=self.dev)
+        masks = (None, lib.ptr(self.cmask) if critic_masks else None) if which == "tc" else ()
         tail = (self.rows, self.n, lib.ptr(self.o), lib.ptr(self.acs_d), lib.ptr(self.adv_d), None, lib.ptr(self.lp_d),
                 lib.ptr(self.tg_d), lib.ptr(self.opt), lib.ptr(ga), lib.ptr(gc), lib.ptr(stats), lib.ptr(self.ax2),
-                lib.ptr(self.ax3), lib.ptr(self.cx2), lib.ptr(self.cx3), lib.ptr(self.ws), self.nbytes, lib.cur_stream())
+                lib.ptr(self.ax3), lib.ptr(self.cx2), lib.ptr(self.cx3), *masks, lib.ptr(self.ws), self.nbytes,
+                lib.cur_stream())
         nets = (lib.ptr(self.a) if actor else None, lib.ptr(self.c) if critic else None)
         dims = (self.ob, self.num_ac, 2.0) if self.cont else (self.ob, self.num_ac)
         kind = "gauss" if self.cont else "cat"
@@ -175,6 +188,30 @@ def test_tc_backward_is_deterministic_and_takes_either_net(lib, dev, split):
     assert (only_a[1] == 7.0).all() and (only_c[0] == 7.0).all()      # the absent net's gradient is untouched
 
 
+@pytest.mark.parametrize("rows,n", [(2, 333), (20, 512), (3, 20000)])
+def test_tc_backward_with_the_forward_pass_sign_masks(lib, dev, rows, n):
+    """act'(X1) / act'(X2) from the mask words acx_value_forward_tc stores == re-derived from the cache and the
+    observations: the critic's gradients are identical bit for bit; the mask words are the signs of the cached X2."""
+    k = Case(lib, dev, True, 3, 1, rows, n, 41)
+    k.critic_forward_tc_with_masks()
+    plain = k.run("tc", actor=False)
+    masked = k.run("tc", actor=False, critic_masks=True)
+    np.testing.assert_array_equal(masked[1], plain[1])
+    np.testing.assert_array_equal(masked[2], plain[2])
+    # against the oracle with the bar of the trainer tests (2e-3 of each tensor's max): here the cached activations come
+    # from the 3xTF32 forward, and an activation within rounding of zero may land on the other side of the ReLU kink
+    _, wc = k.oracle(np.float64)
+    for name, o, sh in P.items(k.clay):
+        sz = int(np.prod(sh))
+        assert np.abs(masked[1][o:o + sz] - wc["grad"][o:o + sz]).max() <= 2e-3 * np.abs(wc["grad"][o:o + sz]).max(), name
+    words = k.cmask.cpu().numpy().view(np.uint32).reshape(rows, -1, 12, 128)      # [rows][tiles][8 X1 + 4 X2 words][128]
+    x2 = k.cx2.cpu().numpy()                                                        # [rows][tiles][128][128]
+    bits = (words[:, :, 8:, None, :] >> np.arange(32, dtype=np.uint32)[None, None, None, :, None]) & 1
+    got = bits.reshape(rows, -1, 128, 128).transpose(0, 2, 1, 3).reshape(rows, 128, -1)[:, :, :n]      # live samples only
+    want = (x2 > 0).transpose(0, 2, 1, 3).reshape(rows, 128, -1)[:, :, :n]
+    np.testing.assert_array_equal(got, want.astype(np.uint32))
+
+
 def test_tc_backward_rejects_bad_arguments(lib, dev):
     k = Case(lib, dev, True, 3, 1, 1, 128, 2)
     f = lib.load().acx_loss_backward_gauss_tc
@@ -184,7 +221,7 @@ def test_tc_backward_rejects_bad_arguments(lib, dev):
         return f(k.a.data_ptr(), k.c.data_ptr(), pa, k.pc.data_ptr(), 3, 1, 2.0, rows, 128, k.o.data_ptr(),
                  k.acs_d.data_ptr(), k.adv_d.data_ptr(), None, k.lp_d.data_ptr(), k.tg_d.data_ptr(), k.opt.data_ptr(),
                  ga.data_ptr(), gc.data_ptr(), st.data_ptr(), ax2, k.ax3.data_ptr(), k.cx2.data_ptr(), k.cx3.data_ptr(),
-                 k.ws.data_ptr(), nbytes, None)
+                 None, None, k.ws.data_ptr(), nbytes, None)
 
     assert call(None, k.ax2.data_ptr()) == -1 and b"packed" in lib.load().acx_last_error()
     assert call(k.pa.data_ptr(), None) == -1

@@ -37,7 +37,7 @@ def test_gauss_and_value_tc_match_oracle(lib, dev, rows, n, weights):
     v = torch.empty((rows, n), device=dev)
     lib.call("acx_policy_forward_sample_gauss_tc", lib.ptr(a), lib.ptr(pa), 3, 1, 2.0, rows, n, lib.ptr(o), lib.ptr(e), 0, 0,
              0, None, lib.ptr(ac), lib.ptr(lp), lib.ptr(ent), lib.ptr(mu), None, None, lib.cur_stream())
-    lib.call("acx_value_forward_tc", lib.ptr(c), lib.ptr(pc), 3, rows, n, lib.ptr(o), lib.ptr(v), 0, None, None, lib.cur_stream())
+    lib.call("acx_value_forward_tc", lib.ptr(c), lib.ptr(pc), 3, rows, n, lib.ptr(o), lib.ptr(v), 0, None, None, None, lib.cur_stream())
     # log-prob of the sampled actions must reproduce lp; KL partials against lp + 0.5
     lp2 = torch.empty((rows, n), device=dev)
     old = lp + 0.5
@@ -82,7 +82,7 @@ def test_cat_tc_matches_oracle_and_ffma(lib, dev, ob, n_act):
         if tag == "tc":
             lib.call("acx_policy_forward_sample_cat_tc", lib.ptr(a), lib.ptr(pa), ob, n_act, rows, n, lib.ptr(o), lib.ptr(uu), 0,
                      0, 0, None, lib.ptr(ac), lib.ptr(lp), lib.ptr(ent), lib.ptr(lg), None, None, lib.cur_stream())
-            lib.call("acx_value_forward_tc", lib.ptr(c), lib.ptr(pc), ob, rows, n, lib.ptr(o), lib.ptr(v), 0, None, None, lib.cur_stream())
+            lib.call("acx_value_forward_tc", lib.ptr(c), lib.ptr(pc), ob, rows, n, lib.ptr(o), lib.ptr(v), 0, None, None, None, lib.cur_stream())
         else:
             lib.call("acx_policy_forward_sample_cat", lib.ptr(a), ob, n_act, rows, n, lib.ptr(o), lib.ptr(uu), 0, 0, 0, None,
                      lib.ptr(ac), lib.ptr(lp), lib.ptr(ent), lib.ptr(lg), lib.cur_stream())
@@ -108,15 +108,15 @@ def test_tc_basic_head_and_argument_checks(lib, dev):
     obs = np.random.default_rng(0).normal(size=(1, 300, 4)).astype(np.float32)
     o = dev_t(soa(obs[0])[None], dev)
     v = torch.empty((1, 300), device=dev)
-    lib.call("acx_value_forward_tc", lib.ptr(c), lib.ptr(pc), 4, 1, 300, lib.ptr(o), lib.ptr(v), 1, None, None, lib.cur_stream())
+    lib.call("acx_value_forward_tc", lib.ptr(c), lib.ptr(pc), 4, 1, 300, lib.ptr(o), lib.ptr(v), 1, None, None, None, lib.cur_stream())
     torch.cuda.synchronize()
     want = P.critic_value(critic, P.critic_layout(4), obs[0], basic_head=True, dtype=np.float64)
     assert rel_err(v.cpu().numpy()[0], want) < 2 * TOL
     f = lib.load().acx_value_forward_tc
-    assert f(c.data_ptr(), None, 4, 1, 8, o.data_ptr(), v.data_ptr(), 0, None, None, None) == -1
+    assert f(c.data_ptr(), None, 4, 1, 8, o.data_ptr(), v.data_ptr(), 0, None, None, None, None) == -1
     assert b"null" in lib.load().acx_last_error()
-    assert f(c.data_ptr(), pc.data_ptr() + 4, 4, 1, 8, o.data_ptr(), v.data_ptr(), 0, None, None, None) == -1
-    assert f(c.data_ptr(), pc.data_ptr(), 4, 0, 8, o.data_ptr(), v.data_ptr(), 0, None, None, None) == 0
+    assert f(c.data_ptr(), pc.data_ptr() + 4, 4, 1, 8, o.data_ptr(), v.data_ptr(), 0, None, None, None, None) == -1
+    assert f(c.data_ptr(), pc.data_ptr(), 4, 0, 8, o.data_ptr(), v.data_ptr(), 0, None, None, None, None) == 0
 
 
 def test_tc_forward_fills_the_activation_cache_like_the_ffma_forward(lib, dev):
@@ -139,7 +139,7 @@ def test_tc_forward_fills_the_activation_cache_like_the_ffma_forward(lib, dev):
             lib.call("acx_policy_forward_sample_gauss_tc", lib.ptr(a), lib.ptr(pa), 3, 1, 2.0, rows, n, lib.ptr(o), lib.ptr(e),
                      0, 0, 0, None, lib.ptr(ac), lib.ptr(lp), None, None, lib.ptr(ax2), lib.ptr(ax3), lib.cur_stream())
             lib.call("acx_value_forward_tc", lib.ptr(c), lib.ptr(pc), 3, rows, n, lib.ptr(o), lib.ptr(v), 0, lib.ptr(cx2),
-                     lib.ptr(cx3), lib.cur_stream())
+                     lib.ptr(cx3), None, lib.cur_stream())
         else:
             lib.call("acx_policy_forward_sample_gauss_cached", lib.ptr(a), 3, 1, 2.0, rows, n, lib.ptr(o), lib.ptr(e), 0, 0,
                      0, None, lib.ptr(ac), lib.ptr(lp), None, None, lib.ptr(ax2), lib.ptr(ax3), lib.cur_stream())
