@@ -156,6 +156,9 @@ class A2CTrainer:
         # optional caller-supplied noise (parity / end-to-end mode), static so graphs can replay on them
         self.noise_buf = None
         self.reset_u_buf = None
+        # double-buffered input staging for prefetch(): [noise, reset_u, ready event] per buffer set
+        self._stage, self._stage_cur, self._stage_next_ready = [None, None], 0, 0
+        self._copy_stream, self._ev_iter, self._own = None, None, None
         self.index0 = self.rank * N
         self.iterations = 0
         self._graphs = {}
@@ -336,17 +339,58 @@ class A2CTrainer:
 
     iterations_started = False
 
-    def iteration(self, noise=None, reset_u=None):
-        """One rollout + update.  ``noise``/``reset_u``: optional DEVICE tensors [T, ac, N] (normals) or
-        [T, N] (uniforms) and [T, S, N]; default is the device Philox stream."""
-        buffered = noise is not None
-        if buffered:
-            if self.noise_buf is None:
-                self.noise_buf = torch.empty_like(noise, device=self.dev)
-                self.reset_u_buf = torch.empty((self.T, self.S, self.N), device=self.dev, dtype=torch.float32)
+    def prefetch(self, noise, reset_u):
+        """Start the host->device copy of the NEXT iteration's action noise / reset uniforms (pinned host tensors)
+        on a copy stream, into the staging set the running iteration does not read; ``iteration(prefetched=True)``
+        then consumes it.  The copy overlaps the kernels of the iteration enqueued before this call -- the loader
+        running one batch ahead, as a queue-fed ``sess.run`` would."""
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+        nxt = 1 - self._stage_cur
+        if self._stage[nxt] is None:
+            self._stage[nxt] = [torch.empty(noise.shape, device=self.dev, dtype=noise.dtype),
+                                torch.empty((self.T, self.S, self.N), device=self.dev, dtype=torch.float32),
+                                torch.cuda.Event()]
+        nb, rb, ev = self._stage[nxt]
+        cs = self._copy_stream
+        # the set was last read by the rollout of the iteration before the latest one: everything enqueued before the
+        # latest iteration's start marker has to be through
+        if self._ev_iter is not None:
+            cs.wait_event(self._ev_iter)
+        else:
+            cs.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(cs):
+            nb.copy_(noise, non_blocking=True)
+            rb.copy_(reset_u, non_blocking=True)
+            ev.record(cs)
+        self._stage_next_ready = nxt
+
+    def wait_prefetch(self):
+        """Make the current stream wait for the copy the last prefetch() started (iteration(prefetched=True) does so
+        itself; this is for callers that want the copy to end inside an interval they time)."""
+        torch.cuda.current_stream().wait_event(self._stage[self._stage_next_ready][2])
+
+    def iteration(self, noise=None, reset_u=None, prefetched=False):
+        """One rollout + update.  ``noise``/``reset_u``: optional tensors [T, ac, N] (normals) or [T, N]
+        (uniforms) and [T, S, N], copied to the device here; ``prefetched=True`` takes the set a preceding
+        ``prefetch()`` staged; default is the device Philox stream."""
+        if self._ev_iter is None:
+            self._ev_iter = torch.cuda.Event()
+        self._ev_iter.record()
+        buffered = noise is not None or prefetched
+        tag = "buf" if buffered else "rng"
+        if prefetched:
+            self._stage_cur = self._stage_next_ready
+            self.noise_buf, self.reset_u_buf, ev = self._stage[self._stage_cur]
+            torch.cuda.current_stream().wait_event(ev)
+            tag = "pre%d" % self._stage_cur            # one CUDA graph per staging set
+        elif buffered:
+            if self._own is None:
+                self._own = (torch.empty_like(noise, device=self.dev),
+                             torch.empty((self.T, self.S, self.N), device=self.dev, dtype=torch.float32))
+            self.noise_buf, self.reset_u_buf = self._own       # the "a_buf" graph is captured on this set
             self.noise_buf.copy_(noise, non_blocking=True)
             self.reset_u_buf.copy_(reset_u, non_blocking=True)
-        tag = "buf" if buffered else "rng"
         if not self.iterations_started:
             # first iteration: obs_buf[0] already holds the reset observations
             n = self._rollout(buffered) + self._gradients()

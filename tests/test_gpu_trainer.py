@@ -136,6 +136,26 @@ def test_caller_supplied_noise_matches_oracle_and_device_rng():
     np.testing.assert_allclose(b.params.cpu().numpy(), a.params.cpu().numpy(), rtol=1e-3, atol=1e-5)
 
 
+def test_prefetched_inputs_equal_inline_copies():
+    """prefetch() stages the next iteration's noise on a copy stream into alternating buffer sets (one CUDA graph per
+    set); six iterations must leave exactly the parameters of six iterations that copy their inputs in line."""
+    N, T, seed, iters = 1024, 5, 31, 6
+    g = torch.Generator().manual_seed(7)
+    eps = [torch.randn((T, 1, N), generator=g).pin_memory() for _ in range(iters)]
+    ru = [torch.rand((T, 2, N), generator=g).pin_memory() for _ in range(iters)]
+    a = A2CTrainer("Pendulum-v0", n_envs=N, horizon=T, seed=seed, max_episode_steps=7)
+    b = A2CTrainer("Pendulum-v0", n_envs=N, horizon=T, seed=seed, max_episode_steps=7)
+    b.prefetch(eps[0], ru[0])
+    for k in range(iters):
+        a.iteration(noise=eps[k], reset_u=ru[k])
+        b.iteration(prefetched=True)
+        if k + 1 < iters:
+            b.prefetch(eps[k + 1], ru[k + 1])
+    torch.cuda.synchronize()
+    for name in ("params", "acs", "rew", "done", "G", "stats"):
+        np.testing.assert_array_equal(getattr(b, name).cpu().numpy(), getattr(a, name).cpu().numpy(), err_msg=name)
+
+
 def test_many_iterations_stay_finite_and_lr_adapts():
     tr = A2CTrainer("CartPole-v0", n_envs=2048, horizon=20, seed=1)
     for _ in range(30):
