@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(256) acx_env_step_kernel(int n, float* __restr
 #pragma unroll
       for (int k = 0; k < S; ++k) sv[k] = s[k][v];
       bool term;
-      AcxEnv<ENV>::dynamics(sv, act[v], r[v], term);
+      acx_env_transition<ENV>(sv, act[v], r[v], term, ov);
       int e = el[v] + 1;
       bool dn = term || (e >= max_steps);
       if (dn) {
@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256) acx_env_step_kernel(int n, float* __restr
         AcxEnv<ENV>::reset(ru, sv);
         e = 0;
       }
-      AcxEnv<ENV>::observe(sv, ov);
+      acx_env_observe_after<ENV>(sv, dn, ov);
 #pragma unroll
       for (int k = 0; k < S; ++k) s[k][v] = sv[k];
 #pragma unroll

@@ -10,6 +10,16 @@
 
 template <int ENV> struct AcxEnv;
 
+// One transition + the observation that follows it, the sequence both env-stepping kernels run:
+//   acx_env_transition<ENV>(state, action, reward, terminated, obs)   then, if the episode ended,   reset + observe.
+// Environments with FUSED_OBS produce the observation inside the transition (Acrobot: the sines / cosines of the new
+// angles also decide termination); for the others `obs` is written by acx_env_observe_after() once the reset is known.
+template <int ENV>
+__device__ inline void acx_env_transition(float (&s)[AcxEnv<ENV>::S], float a, float& rew, bool& term,
+                                          float (&o)[AcxEnv<ENV>::OB]);
+template <int ENV>
+__device__ inline void acx_env_observe_after(const float (&s)[AcxEnv<ENV>::S], bool was_reset, float (&o)[AcxEnv<ENV>::OB]);
+
 // numpy float32 `%` (floored modulo): fmodf is exact, then fix the sign
 __device__ inline float acx_floored_mod(float a, float b) {
   float r = fmodf(a, b);
@@ -23,7 +33,7 @@ __device__ inline float acx_floored_mod(float a, float b) {
 
 template <> struct AcxEnv<ACX_ENV_PENDULUM> {
   static constexpr int S = 2, OB = 3, MAX_STEPS = 200, NACT = 0;
-  static constexpr bool CONT = true;
+  static constexpr bool CONT = true, FUSED_OBS = false;
   __device__ static inline void dynamics(float (&s)[S], float a, float& rew, bool& term) {
     const float th = s[0], thdot = s[1];
     const float u = fminf(fmaxf(a, -2.0f), 2.0f);
@@ -49,7 +59,7 @@ template <> struct AcxEnv<ACX_ENV_PENDULUM> {
 
 template <> struct AcxEnv<ACX_ENV_CARTPOLE> {
   static constexpr int S = 4, OB = 4, MAX_STEPS = 200, NACT = 2;
-  static constexpr bool CONT = false;
+  static constexpr bool CONT = false, FUSED_OBS = false;
   __device__ static inline void dynamics(float (&s)[S], float a, float& rew, bool& term) {
     const float gravity = 9.8f, masspole = 0.1f, total_mass = 1.1f, length = 0.5f, pml = 0.05f, tau = 0.02f;
     float x = s[0], x_dot = s[1], theta = s[2], theta_dot = s[3];
@@ -82,20 +92,25 @@ template <> struct AcxEnv<ACX_ENV_CARTPOLE> {
 
 template <> struct AcxEnv<ACX_ENV_ACROBOT> {
   static constexpr int S = 4, OB = 6, MAX_STEPS = 500, NACT = 3;
-  static constexpr bool CONT = false;
-  // "book" dynamics, all link constants 1 except lc = 0.5, g = 9.8
+  static constexpr bool CONT = false, FUSED_OBS = true;      // step_observe(): the transition also yields the observation
+  // "book" dynamics, all link constants 1 except lc = 0.5, g = 9.8.  gym's cos(th1 - pi/2) and cos(th1 + th2 - pi/2)
+  // are sin(th1) and sin(th1 + th2) = s1 c2 + c1 s2: two sincosf per evaluation instead of four trigonometric calls
+  // (RK4 makes this kernel ALU-bound), and the quotients by d1 share one reciprocal.  Differences from the literal
+  // expression are of rounding size (tests: 1e-5 against the fp32 restatement, 1e-4 against float64).
   __device__ static inline void dsdt(const float (&s)[4], float a, float (&d)[4]) {
     const float g = 9.8f;
-    const float th1 = s[0], th2 = s[1], dth1 = s[2], dth2 = s[3];
-    float s2, c2;
-    sincosf(th2, &s2, &c2);
+    const float dth1 = s[2], dth2 = s[3];
+    float s1, c1, s2, c2;
+    sincosf(s[0], &s1, &c1);
+    sincosf(s[1], &s2, &c2);
     const float d1 = 0.25f + (1.0f + 0.25f + c2) + 1.0f + 1.0f;
     const float d2 = (0.25f + 0.5f * c2) + 1.0f;
-    const float phi2 = 0.5f * g * cosf(th1 + th2 - 0.5f * ACX_PI_F);
-    const float phi1 = -0.5f * dth2 * dth2 * s2 - 2.0f * 0.5f * dth2 * dth1 * s2 +
-                       1.5f * g * cosf(th1 - 0.5f * ACX_PI_F) + phi2;
-    const float ddth2 = (a + d2 / d1 * phi1 - 0.5f * dth1 * dth1 * s2 - phi2) / (0.25f + 1.0f - d2 * d2 / d1);
-    const float ddth1 = -(d2 * ddth2 + phi1) / d1;
+    const float r1 = __frcp_rn(d1);
+    const float phi2 = 0.5f * g * (s1 * c2 + c1 * s2);
+    const float phi1 = -0.5f * dth2 * dth2 * s2 - 2.0f * 0.5f * dth2 * dth1 * s2 + 1.5f * g * s1 + phi2;
+    const float q = d2 * r1;
+    const float ddth2 = (a + q * phi1 - 0.5f * dth1 * dth1 * s2 - phi2) * __frcp_rn(0.25f + 1.0f - d2 * q);
+    const float ddth1 = -(d2 * ddth2 + phi1) * r1;
     d[0] = dth1; d[1] = dth2; d[2] = ddth1; d[3] = ddth2;
   }
   __device__ static inline float wrap(float x, float lo, float hi) {
@@ -104,7 +119,9 @@ template <> struct AcxEnv<ACX_ENV_ACROBOT> {
     for (int i = 0; i < 64 && x < lo; ++i) x += diff;
     return x;
   }
-  __device__ static inline void dynamics(float (&s)[S], float a, float& rew, bool& term) {
+  // one RK4 transition; also returns the observation of the new state (its sines / cosines decide `term` as well:
+  // cos(y0 + y1) = c0 c1 - s0 s1)
+  __device__ static inline void step_observe(float (&s)[S], float a, float& rew, bool& term, float (&o)[OB]) {
     const float dt = 0.2f, torque = a - 1.0f;
     float k1[4], k2[4], k3[4], k4[4], y[4];
     dsdt(s, torque, k1);
@@ -123,16 +140,40 @@ template <> struct AcxEnv<ACX_ENV_ACROBOT> {
     y[1] = wrap(y[1], -ACX_PI_F, ACX_PI_F);
     y[2] = fminf(fmaxf(y[2], -4.0f * ACX_PI_F), 4.0f * ACX_PI_F);
     y[3] = fminf(fmaxf(y[3], -9.0f * ACX_PI_F), 9.0f * ACX_PI_F);
-    term = (-cosf(y[0]) - cosf(y[1] + y[0])) > 1.0f;
+    sincosf(y[0], &o[1], &o[0]);
+    sincosf(y[1], &o[3], &o[2]);
+    o[4] = y[2]; o[5] = y[3];
+    term = (-o[0] - (o[0] * o[2] - o[1] * o[3])) > 1.0f;
     rew = term ? 0.0f : -1.0f;
 #pragma unroll
     for (int i = 0; i < 4; ++i) s[i] = y[i];
+  }
+  __device__ static inline void dynamics(float (&s)[S], float a, float& rew, bool& term) {
+    float o[OB];
+    step_observe(s, a, rew, term, o);
   }
   __device__ static inline void reset(const float (&u)[S], float (&s)[S]) {
 #pragma unroll
     for (int k = 0; k < S; ++k) s[k] = __fadd_rn(-0.1f, __fmul_rn(0.2f, u[k]));
   }
   __device__ static inline void observe(const float (&s)[S], float (&o)[OB]) {
-    o[0] = cosf(s[0]); o[1] = sinf(s[0]); o[2] = cosf(s[1]); o[3] = sinf(s[1]); o[4] = s[2]; o[5] = s[3];
+    sincosf(s[0], &o[1], &o[0]);
+    sincosf(s[1], &o[3], &o[2]);
+    o[4] = s[2]; o[5] = s[3];
   }
 };
+
+template <int ENV>
+__device__ inline void acx_env_transition(float (&s)[AcxEnv<ENV>::S], float a, float& rew, bool& term,
+                                          float (&o)[AcxEnv<ENV>::OB]) {
+  if constexpr (AcxEnv<ENV>::FUSED_OBS) AcxEnv<ENV>::step_observe(s, a, rew, term, o);
+  else AcxEnv<ENV>::dynamics(s, a, rew, term);
+}
+template <int ENV>
+__device__ inline void acx_env_observe_after(const float (&s)[AcxEnv<ENV>::S], bool was_reset, float (&o)[AcxEnv<ENV>::OB]) {
+  if constexpr (AcxEnv<ENV>::FUSED_OBS) {
+    if (was_reset) AcxEnv<ENV>::observe(s, o);
+  } else {
+    AcxEnv<ENV>::observe(s, o);
+  }
+}

@@ -233,7 +233,8 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
       if (!ROLL) return;
       float rew;
       bool term;
-      AcxEnv<ROLL ? ENVR : 0>::dynamics(est, act, rew, term);
+      float ov[EOB];
+      acx_env_transition<ROLL ? ENVR : 0>(est, act, rew, term, ov);
       int e = eel + 1;
       const bool dn = term || (e >= emax);
       if (dn) {
@@ -250,8 +251,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         AcxEnv<ROLL ? ENVR : 0>::reset(ru, est);
         e = 0;
       }
-      float ov[EOB];
-      AcxEnv<ROLL ? ENVR : 0>::observe(est, ov);
+      acx_env_observe_after<ROLL ? ENVR : 0>(est, dn, ov);
       eel = e;
       A.rew_out[(size_t)row * A.n + col] = rew;
       A.done_out[(size_t)row * A.n + col] = dn ? 1 : 0;
