@@ -162,10 +162,44 @@ def test_process(env_id, random_seed, stack_frames, model_path, num_episodes, an
     return avg_rew
 
 
-def evaluate_batched(env_id, model_path, num_episodes, greedy=True, seed=12321, actor_flat=None, chunk=1 << 20):
+def _evaluate_chunk_rollout(vec, params, num_ac, cont, greedy, seed, start, block=20):
+    """One chunk of evaluate_batched on the persistent rollout kernel (acx_rollout_tc): ``block`` steps of
+    {policy forward on the tensor cores, action, env transition} per launch, env state in registers; the first
+    episode's return is the reward sum up to the first ``done`` of each column."""
+    n, dev, s = vec.n, vec.dev, L.cur_stream()
+    ob, T, horizon = vec.obs_dim, int(block), vec.max_episode_steps
+    packed = torch.zeros(L.load().acx_tc_packed_floats(0, ob, num_ac, int(cont)), device=dev)
+    L.call("acx_tc_pack_weights", 0, L.ptr(params), ob, num_ac, int(cont), L.ptr(packed), s)
+    obs = torch.empty((T + 1, ob, n), device=dev)
+    obs[0].copy_(vec.reset())
+    noise = torch.zeros((T, 1, n), device=dev) if (greedy and cont) else None       # eps = 0: action = mu
+    acs = torch.empty((T, 1, n), device=dev) if cont else torch.empty((T, n), device=dev, dtype=torch.int32)
+    rew = torch.empty((T, n), device=dev)
+    done = torch.empty((T, n), device=dev, dtype=torch.uint8)
+    ctr = torch.zeros(1, device=dev, dtype=torch.int32)
+    ret = torch.zeros(n, device=dev)
+    alive = torch.ones(n, device=dev)
+    for t0 in range(0, horizon, T):
+        tc = min(T, horizon - t0)
+        L.call("acx_rollout_tc", vec.env, L.ptr(params), L.ptr(packed), 2.0, tc, n, L.ptr(obs), L.ptr(vec.state),
+               L.ptr(vec.elapsed), L.ptr(noise), None, seed, start, L.ptr(ctr), 0, L.ptr(acs), None, None, L.ptr(rew),
+               L.ptr(done), None, None, None, s)
+        L.call("acx_counter_add", L.ptr(ctr), tc, s)
+        d = done[:tc].to(torch.float32)
+        before = torch.cumsum(d, 0) - d                     # finished episodes before step t of this block
+        ret += (rew[:tc] * (before == 0)).sum(0) * alive
+        alive = alive * (d.sum(0) == 0)
+        obs[0].copy_(obs[tc])
+    return ret
+
+
+def evaluate_batched(env_id, model_path, num_episodes, greedy=True, seed=12321, actor_flat=None, chunk=1 << 20,
+                     tensor_cores=False):
     """Config 5: evaluate a checkpoint over ``num_episodes`` episodes stepped in lock-step on the GPU.
     ``greedy=True`` uses action = mu (the derived deterministic variant); ``False`` samples like the
-    reference's ``test_process``.  Returns the per-episode returns (numpy, first episode of each env)."""
+    reference's ``test_process``.  Returns the per-episode returns (numpy, first episode of each env).
+    ``tensor_cores=True`` runs each chunk on the persistent rollout kernel (3xTF32 forward, 20 steps per launch)
+    instead of one FFMA forward + one env-step launch per step."""
     env_code = envs_mod.ENV_IDS[env_id]
     dev = torch.device("cuda", torch.cuda.current_device())
     out = []
@@ -179,6 +213,9 @@ def evaluate_batched(env_id, model_path, num_episodes, greedy=True, seed=12321, 
             params = actor.net.params
         else:
             params = torch.as_tensor(np.asarray(actor_flat, dtype=np.float32), device=dev)
+        if tensor_cores:
+            out.append(_evaluate_chunk_rollout(vec, params, num_ac, cont, greedy, seed, start).cpu().numpy())
+            continue
         obs = vec.reset().clone()
         ret = torch.zeros(n, device=dev)
         alive = torch.ones(n, device=dev)

@@ -35,6 +35,15 @@ if ROOT not in sys.path:
 ENV_ID, N_ENVS, HORIZON, SEED = "Pendulum-v0", 65536, 20, 12321
 WORKLOAD = "Pendulum-v0 A2C, 65536 envs x 20-step horizon per GPU, fused rollout+update (BASELINE.json configs[2])"
 FLOP_ACTOR_FWD, FLOP_CRITIC_FWD = 50048.0, 100096.0       # per sample, 2 FLOP/MAC
+# --workload: the default line is configs[2]; the other two are extra, separately reported measurements
+WORKLOADS = {
+    "pendulum": dict(env_id="Pendulum-v0", n_envs=65536, horizon=20, name=WORKLOAD, flop_actor=50048.0,
+                     flop_critic=100096.0),
+    "cartpole": dict(env_id="CartPole-v0", n_envs=262144, horizon=20,
+                     name="CartPole-v0 A2C, 262144 envs x 20-step horizon per GPU, fused rollout+update, NCCL "
+                          "flat-gradient all-reduce (BASELINE.json configs[3]; the horizon is not given there: 20, as "
+                          "in configs[2])", flop_actor=50432.0, flop_critic=100608.0),
+}
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12         # FFMA peak at max boost clock (computed)
 
 
@@ -94,7 +103,7 @@ class ClockSampler(object):
 def cpu_baseline(steps=2, n_envs=2048, warmup=1):
     """Oracle A2C iteration (numpy, all host threads through BLAS) on a bounded sample."""
     from oracle import a2c, envs as E
-    S = a2c.A2CState(E.PENDULUM, n_envs, seed=SEED)
+    S = a2c.A2CState(E.ENV_IDS[ENV_ID], n_envs, seed=SEED)
     for _ in range(warmup):
         a2c.iteration(S, T=HORIZON)
     t0 = time.perf_counter()
@@ -273,6 +282,27 @@ def kernel_table(tr, flush, hbm_peak):
     return out
 
 
+def critic_pair_only(tr, flush, bf16_peak):
+    """Non-default workloads: only the dominant kernel pair (critic chain + weight-gradient kernels), timed alone."""
+    from actor_critic_algs_on_tensorflow_b200 import _lib as L
+    N, T = tr.N, tr.T
+    ga, gc = tr.grads[:tr.Pa], tr.grads[tr.Pa:]
+    tail = (T, N, L.ptr(tr.obs_buf), L.ptr(tr.acs), L.ptr(tr.adv), L.ptr(tr.stats), L.ptr(tr.logps), L.ptr(tr.G),
+            L.ptr(tr.opt), L.ptr(ga), L.ptr(gc), L.ptr(tr.stats), L.ptr(tr.ax2), L.ptr(tr.ax3), L.ptr(tr.cx2),
+            L.ptr(tr.cx3), L.ptr(tr.amask), L.ptr(tr.cmask), L.ptr(tr.ws_bwd), tr.ws_bwd_bytes, L.cur_stream())
+    head = (None, L.ptr(tr.critic), L.ptr(tr.packed_bwd_a), L.ptr(tr.packed_bwd_c), tr.ob)
+    if tr.cont:
+        fn = lambda: L.call("acx_loss_backward_gauss_tc", *head, tr.num_ac, tr.ac_scale, *tail)
+    else:
+        fn = lambda: L.call("acx_loss_backward_cat_tc", *head, tr.n_act, *tail)
+    sec = time_kernel(fn, flush)
+    ach = 2 * FLOP_CRITIC_FWD * N * T / sec / 1e12
+    peak = bf16_peak / 2.0 / 3.0
+    return {"loss_backward_critic_tc, chain + wgrad kernels (K4, tcgen05 3xTF32)": {
+        "bound": "tensor", "ms": sec * 1e3, "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+        "peak_note": "measured bf16 peak / 2 (tf32) / 3 (3xTF32 split)", "frac_of_fp32_ffma_peak": ach / FP32_PEAK_TFLOPS}}
+
+
 def run_ours(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -329,7 +359,8 @@ def run_ours(args, rank, local_rank, world):
     stats = tr.read_stats()
 
     # ---- end to end through the public API with host buffers
-    eps_h = torch.randn((HORIZON, 1, N_ENVS), dtype=torch.float32).pin_memory()
+    eps_h = (torch.randn((HORIZON, 1, N_ENVS), dtype=torch.float32) if tr.cont
+             else torch.rand((HORIZON, N_ENVS), dtype=torch.float32)).pin_memory()
     ru_h = torch.rand((HORIZON, tr.S, N_ENVS), dtype=torch.float32).pin_memory()
     stats_h = torch.empty(32, dtype=torch.float32).pin_memory()
     params_h = torch.empty(tr.Pa + tr.Pc, dtype=torch.float32).pin_memory()
@@ -367,7 +398,7 @@ def run_ours(args, rank, local_rank, world):
 
     if rank == 0:
         kernel_table.bf16_peak = bf16_peak
-        kernels = kernel_table(tr, flush, hbm_peak)
+        kernels = kernel_table(tr, flush, hbm_peak) if args.workload == "pendulum" else critic_pair_only(tr, flush, bf16_peak)
         base_bytes_ = __import__("actor_critic_algs_on_tensorflow_b200._lib", fromlist=["x"]).load() \
             .acx_loss_backward_workspace_bytes(tr.ob, tr.num_ac, int(tr.cont))
         if getattr(tr, "tc_bwd", False) and tr.ws_bwd_bytes > base_bytes_:
@@ -443,6 +474,116 @@ def run_ours(args, rank, local_rank, world):
         dist.destroy_process_group()
 
 
+def run_eval(args, rank, local_rank, world):
+    """BASELINE configs[4]: greedy evaluation of the shipped Pendulum checkpoint, 1,048,576 episodes x 200 steps per GPU
+    (episodes are independent: sharded by rank, no collective).  A step = one whole evaluation."""
+    n_ep, horizon = 1 << 20, 200
+    model = os.path.join(ROOT, "tests", "golden", "model-Pendulum_a3c")
+    name = ("test_model.py greedy evaluation of demos/model-Pendulum_a3c, %d episodes x %d steps per GPU "
+            "(BASELINE.json configs[4])" % (n_ep, horizon))
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        import numpy as np
+        from oracle import envs as E, policies as P, philox as R
+        from actor_critic_algs_on_tensorflow_b200.tf_bundle import read_bundle
+        t = read_bundle(model)
+        lay = P.actor_layout(3, 1, True)
+        g = "global_actor/"
+        actor = P.pack({"W1": t[g + "first_layer/kernel"], "b1": t[g + "first_layer/bias"],
+                        "W2": t[g + "second_layer/kernel"], "b2": t[g + "second_layer/bias"],
+                        "W3": t[g + "third_layer/kernel"], "b3": t[g + "third_layer/bias"],
+                        "Wh": t[g + "mu_layer/kernel"], "bh": t[g + "mu_layer/bias"], "log_std": t[g + "log_std"]}, lay)
+        n = 2048
+        u = R.uniforms(np.arange(n, dtype=np.uint64), 0xFFFFFFFF, R.STREAM_RESET, SEED).T[:2]
+
+        def one():
+            s_ = E.reset_from_uniforms(E.PENDULUM, u.astype(np.float32), dtype=np.float32)
+            tot = np.zeros(n, dtype=np.float32)
+            for _ in range(horizon):
+                _, _, _, mu = P.actor_act(actor, lay, E.observe(E.PENDULUM, s_, np.float32).T, np.zeros((n, 1), np.float32),
+                                          True, 2.0, dtype=np.float32)
+                s_, r, _ = E.dynamics(E.PENDULUM, s_, mu.T, dtype=np.float32)
+                tot += r
+            return tot
+        one()
+        t0 = time.perf_counter()
+        k = max(1, min(args.steps, 5))
+        for _ in range(k):
+            ret = one()
+        dt = time.perf_counter() - t0
+        v = n * horizon * k / dt
+        sample = "%d episodes x %d steps x %d evaluations" % (n, horizon, k)
+        print(json.dumps({"impl": "reference", "metric": "env-steps/sec (greedy evaluation)", "value": v,
+                          "unit": "env-steps/s", "n_gpus": args.gpus, "steps": k, "warmup": 1, "ms_per_step": dt / k * 1e3,
+                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32",
+                          "data": "synthetic", "config": {"workload": name, "sample": sample},
+                          "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": os.cpu_count(), "kind": "port",
+                                           "sample": sample},
+                          "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                          "gpu_launches": 0, "mean_return": float(ret.mean())}), flush=True)
+        return
+    import torch
+    import torch.distributed as dist
+    from actor_critic_algs_on_tensorflow_b200 import process, envs as envs_mod
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    actor = process.load_actor(model, 3, 1, 'cont', 2.0)
+    params = actor.net.params
+    start = rank * n_ep
+
+    def resident():          # parameters resident; returns stay on the device
+        vec = envs_mod.VecEnv("Pendulum-v0", n_ep, SEED, index0=start)
+        return process._evaluate_chunk_rollout(vec, params, 1, True, True, SEED, start)
+
+    def e2e():               # the public call: checkpoint file -> device, returns -> host
+        return process.evaluate_batched("Pendulum-v0", model, n_ep, greedy=True, seed=SEED, tensor_cores=True)
+    out = {}
+    for key, fn in (("value", resident), ("e2e", e2e)):
+        for _ in range(max(1, min(args.warmup, 3))):
+            ret = fn()
+        barrier()
+        tot = 0.0
+        steps = max(1, min(args.steps, 10))
+        for _ in range(steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            ret = fn()
+            b.record()
+            torch.cuda.synchronize()
+            tot += a.elapsed_time(b) * 1e-3
+        barrier()
+        t = torch.tensor([tot], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[key] = (world * n_ep * horizon * steps / float(t.item()), float(t.item()) / steps, ret)
+    if rank == 0:
+        ret = out["e2e"][2]
+        steps = max(1, min(args.steps, 10))
+        launches = (horizon // 20) * 2 + 3
+        print(json.dumps({
+            "metric": "env-steps/sec (greedy evaluation)", "value": out["value"][0], "unit": "env-steps/s",
+            "n_gpus": world, "steps": steps, "warmup": max(1, min(args.warmup, 3)), "ms_per_step": out["value"][1] * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": {"workload": name, "episodes_per_gpu": n_ep, "steps_per_episode": horizon,
+                       "engine": "acx_rollout_tc (tcgen05 3xTF32 forward + env step, 20 steps per launch)",
+                       "l2": "working set per launch (obs/reward rows of 1M envs x 20 steps, 0.4 GB) exceeds L2"},
+            "e2e": {"value": out["e2e"][0], "unit": "env-steps/s", "ms_per_step": out["e2e"][1] * 1e3,
+                    "h2d_bytes_per_step": 25352 * 4, "d2h_bytes_per_step": n_ep * 4},
+            "gpu_launches": launches * steps, "episodes_per_s": out["value"][0] / horizon,
+            "mean_return": float(ret.mean()), "std_return": float(ret.std())}), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -452,7 +593,14 @@ def main():
     ap.add_argument("--mode", choices=["sync", "async"], default="sync")
     ap.add_argument("--no_graph", action="store_true", help="launch kernels eagerly (for ncu launch lists)")
     ap.add_argument("--ffma_only", action="store_true", help="keep the forward passes on the FFMA engine as well")
+    ap.add_argument("--workload", choices=["pendulum", "cartpole", "eval"], default="pendulum",
+                    help="pendulum = BASELINE configs[2] (the bench line); cartpole = configs[3]; eval = configs[4]")
     args = ap.parse_args()
+    if args.workload in WORKLOADS:
+        global ENV_ID, N_ENVS, HORIZON, WORKLOAD, FLOP_ACTOR_FWD, FLOP_CRITIC_FWD
+        w = WORKLOADS[args.workload]
+        ENV_ID, N_ENVS, HORIZON, WORKLOAD = w["env_id"], w["n_envs"], w["horizon"], w["name"]
+        FLOP_ACTOR_FWD, FLOP_CRITIC_FWD = w["flop_actor"], w["flop_critic"]
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -461,7 +609,9 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
-    if args.impl == "reference":
+    if args.workload == "eval":
+        run_eval(args, rank, local_rank, world)
+    elif args.impl == "reference":
         run_reference(args, rank)
     else:
         run_ours(args, rank, local_rank, world)

@@ -144,6 +144,27 @@ def test_test_process_and_batched_greedy_evaluation(capsys):
     assert -190 < ret.mean() < -150                                          # Appendix B: -171.1 +- 107.4 over random starts
     sampled = process.evaluate_batched("Pendulum-v0", MODEL, n, greedy=False, seed=4)
     assert sampled.mean() < ret.mean() and -230 < sampled.mean() < -170      # Appendix B: -200.9 sampled
+    # the same evaluation on the persistent rollout kernel (3xTF32 forward, 20 steps per launch): same bar
+    ret_tc = process.evaluate_batched("Pendulum-v0", MODEL, n, greedy=True, seed=4, tensor_cores=True)
+    rel = np.abs(ret_tc - want) / np.maximum(np.abs(want), 1.0)
+    assert np.median(rel) < 1e-4 and np.quantile(rel, 0.95) < 1e-2
+    np.testing.assert_allclose(ret_tc.mean(), want.mean(), rtol=2e-3)
+    sampled_tc = process.evaluate_batched("Pendulum-v0", MODEL, n, greedy=False, seed=4, tensor_cores=True)
+    np.testing.assert_allclose(sampled_tc.mean(), sampled.mean(), rtol=2e-2)   # same Philox draws, chaotic episodes
+
+
+def test_batched_evaluation_with_early_termination_agrees_between_engines():
+    """CartPole episodes end early: the return is the reward sum up to the first done.  Random-init policy, sampled
+    actions from the same Philox counters on both engines: the per-step launches (FFMA forward) and the persistent
+    rollout kernel must agree episode by episode except where a 3xTF32-sized logit difference flips a draw."""
+    from actor_critic_algs_on_tensorflow_b200.trainer import glorot_flat
+    n = 8192
+    flat = glorot_flat(0, 4, 2, False, np.random.default_rng(3))
+    a = process.evaluate_batched("CartPole-v0", None, n, greedy=False, seed=9, actor_flat=flat)
+    b = process.evaluate_batched("CartPole-v0", None, n, greedy=False, seed=9, actor_flat=flat, tensor_cores=True)
+    assert a.min() >= 8 and a.max() <= 200 and 15 < a.mean() < 40          # random policy: ~22 steps
+    assert (a == b).mean() > 0.995
+    np.testing.assert_allclose(b.mean(), a.mean(), rtol=5e-3)
 
 
 def test_process_fn_and_run_ac_smoke(tmp_path, capsys):
