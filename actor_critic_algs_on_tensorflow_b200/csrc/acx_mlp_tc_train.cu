@@ -332,7 +332,9 @@ __global__ void __launch_bounds__(256) acx_grad_reduce_tc_kernel(const float* __
       const int r = (p - offW3) / H3, c = (p - offW3) % H3;
       q = offW3 + ((c >> 2) * 128 + r) * 4 + (c & 3);
     } else if (lane_major && p >= offW2 && p < offW2 + H1 * 128) {
-      const int k1 = (p - offW2) / 128, j = (p - offW2) % 128, r = k1 & 127, c = (k1 >> 7) * 128 + j;
+      // H1 = 128: lane = k, column = j; H1 = 256: the kernel accumulates dW2 transposed (lane = j, column = k)
+      const int k1 = (p - offW2) / 128, j = (p - offW2) % 128;
+      const int r = H1 == 256 ? j : k1, c = H1 == 256 ? k1 : j;
       q = offW2 + ((c >> 2) * 128 + r) * 4 + (c & 3);
     }
     // fixed order cta = 0, 1, ...; the loads of eight rows are issued ahead of the dependent adds

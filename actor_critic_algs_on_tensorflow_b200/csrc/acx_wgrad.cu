@@ -25,6 +25,12 @@
 
 using namespace acxumma;
 
+#ifdef ACX_WG_PROF
+// dev build (make prof): issuer of CTA 0 -- [0] phase-0 cycles, [1] phase-1 cycles, [2]/[3] of which waiting for split
+// boxes, [4]/[5] boxes per phase
+__device__ unsigned long long acx_wg_prof[8];
+#endif
+
 namespace {
 
 constexpr int WG_THREADS = 320;
@@ -125,9 +131,19 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
   } else if (warp == 1) {
     if (lane == 0) {
       unsigned int it = 0, group = 0, used[2] = {0u, 0u};
+#ifdef ACX_WG_PROF
+      long long pt_ = clock64(), pw_ = 0;
+      unsigned int pit_ = 0;
+#endif
       for (int phase = 0; phase < 2; ++phase) {
-        const int nblk = phase == 0 ? 1 : NB;
-        const uint32_t idesc = idesc_tf32(128, phase == 0 ? H3 : 128, false, false);
+        // phase 1 with two X1 blocks (critic): the roles are swapped -- A = the dPre2 box (128 rows), B = both X1 blocks
+        // (256 rows, contiguous under the 128-byte swizzle), ONE N = 256 instruction per split product; the accumulator
+        // holds dW2 transposed (lane = j, column = k).  Per K step the tensor core then reads 3 x (4 + 8) KB of shared
+        // memory instead of 6 x (4 + 4) (ncu: tensor-core reads 39 % + load/store wavefronts 37 % of the shared-memory
+        // data pipe's peak in this kernel).
+        const bool wide = phase == 1 && NB == 2;
+        const int nblk = (phase == 0 || wide) ? 1 : NB;
+        const uint32_t idesc = idesc_tf32(128, phase == 0 ? H3 : (wide ? 256 : 128), false, false);
         if (phase == 1)                              // phase-1 buffers overlap phase-0's: every flush must be through
           for (int b = 0; b < 2; ++b)
             if (used[b]) acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.dfree[b]), (used[b] - 1u) & 1u);
@@ -143,7 +159,13 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
           }
           for (int kk = 0; kk < nsub; ++kk, ++it) {
             const unsigned int slot = it % NSTAGE;
+#ifdef ACX_WG_PROF
+            const long long w0_ = clock64();
+#endif
             acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.split[slot]), (it / NSTAGE) & 1u);
+#ifdef ACX_WG_PROF
+            pw_ += clock64() - w0_;
+#endif
             fence_after_sync();
             const float* r = raw + (size_t)slot * Cfg::STAGE;
             const float* l = lo + (size_t)slot * Cfg::STAGE;
@@ -151,6 +173,13 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
 #pragma unroll
             for (int ks = 0; ks < BOX / 8; ++ks) {
               const uint64_t bh = smem_desc_sw128(r + NB * BLK + ks * 8), bl = smem_desc_sw128(l + NB * BLK + ks * 8);
+              if (wide) {
+                const uint64_t xh = smem_desc_sw128(r + ks * 8), xl = smem_desc_sw128(l + ks * 8);
+                mma_tf32(dbase, bl, xh, idesc, !(fresh && ks == 0));
+                mma_tf32(dbase, bh, xl, idesc, true);
+                mma_tf32(dbase, bh, xh, idesc, true);
+                continue;
+              }
               for (int b = 0; b < nblk; ++b) {
                 const uint64_t ah = smem_desc_sw128(r + b * BLK + ks * 8), al = smem_desc_sw128(l + b * BLK + ks * 8);
                 const uint32_t d = dbase + 128u * (uint32_t)b;
@@ -168,6 +197,13 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             in_group = 0;
           }
         }
+#ifdef ACX_WG_PROF
+        if (blockIdx.x == 0) {
+          const long long now_ = clock64();
+          acx_wg_prof[phase] = now_ - pt_; acx_wg_prof[2 + phase] = pw_; acx_wg_prof[4 + phase] = it - pit_;
+          pt_ = now_; pw_ = 0; pit_ = it;
+        }
+#endif
       }
     }
   } else {
@@ -349,3 +385,9 @@ int acx_wgrad_launch(const AcxWgradArgs& a, void* stream) {
   ACX_REQUIRE(false, "acx_wgrad: unsupported layer widths H1=%d H3=%d", a.H1, a.H3);
   return ACX_OK;
 }
+
+#ifdef ACX_WG_PROF
+extern "C" int acx_wg_prof_read(unsigned long long* out8) {
+  return (int)cudaMemcpyFromSymbol(out8, acx_wg_prof, sizeof(unsigned long long) * 8);
+}
+#endif

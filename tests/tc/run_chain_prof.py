@@ -31,6 +31,13 @@ for which in ("actor", "critic"):
     torch.cuda.synchronize()
     lib.acx_chain_prof_read.argtypes = [C.c_void_p]
     lib.acx_chain_prof_read(buf)
+    if hasattr(lib, "acx_wg_prof_read"):
+        wg = (C.c_ulonglong * 8)()
+        lib.acx_wg_prof_read.argtypes = [C.c_void_p]
+        lib.acx_wg_prof_read(wg)
+        for ph in (0, 1):
+            print("  wgrad %s phase %d: %d boxes, %.0f cycles per box, of which %.0f waiting for the split box"
+                  % (which, ph, wg[4 + ph], wg[ph] / max(wg[4 + ph], 1), wg[2 + ph] / max(wg[4 + ph], 1)))
     tot = sum(buf[i] for i in range(16))
     print(which, "total cycles", tot, "tiles ~", 20 * 512 / 148)
     for i, nm in enumerate(names):
