@@ -76,6 +76,10 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
   constexpr int NB = Cfg::NB, NSTAGE = Cfg::NSTAGE;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // NB: the round trip through uintptr_t drops the address space, so the splitters' accesses to the ring compile to
+  // generic LD / ST instead of LDS / STS.  Measured both ways (make prof): with LDS / STS the dW2 phase is SLOWER
+  // (critic 3,600 -> 4,040, actor 2,620 -> 3,220 cycles per box; the dW3 phase unchanged) -- the 16-byte stores of a
+  // whole X1 box then queue in the MIO pipe in front of the mbarrier operations; the generic path has its own queue.
   float* raw = reinterpret_cast<float*>(base);                         // [NSTAGE][STAGE]
   float* lo = raw + (size_t)NSTAGE * Cfg::STAGE;                       // [NSTAGE][STAGE]
   WgBars& B = *reinterpret_cast<WgBars*>(lo + (size_t)NSTAGE * Cfg::STAGE);
