@@ -90,6 +90,24 @@ template <> struct AcxEnv<ACX_ENV_CARTPOLE> {
   }
 };
 
+// sin and cos of a BOUNDED angle (|x| < ~100: Acrobot's angles are wrapped to [-pi, pi] and its velocities clipped, so an
+// RK4 stage never leaves |x| < 12): two-constant Cody-Waite reduction to [-pi/4, pi/4] and the single-precision minimax
+// polynomials of the Cephes library, 9.2e-8 absolute against float64 over |x| < 40.  sincosf() carries a slow path for
+// huge arguments and costs about twice the instructions; the RK4 step calls this ten times and is bound by its arithmetic.
+__device__ inline void acx_sincos_bounded(float x, float& sn, float& cs) {
+  const float k = rintf(x * 0.636619772367581343f);
+  float r = fmaf(k, -1.57079625129699707031f, x);
+  r = fmaf(k, -7.54978941586159635335e-8f, r);
+  const float z = r * r;
+  const float sp = fmaf(r * z, fmaf(z, fmaf(z, -1.9515295891e-4f, 8.3321608736e-3f), -1.6666654611e-1f), r);
+  const float cp = fmaf(z * z, fmaf(z, fmaf(z, 2.443315711809948e-5f, -1.388731625493765e-3f), 4.166664568298827e-2f),
+                        fmaf(z, -0.5f, 1.0f));
+  const int q = (int)k;
+  const float s0 = (q & 1) ? cp : sp, c0 = (q & 1) ? sp : cp;
+  sn = (q & 2) ? -s0 : s0;
+  cs = ((q + 1) & 2) ? -c0 : c0;
+}
+
 template <> struct AcxEnv<ACX_ENV_ACROBOT> {
   static constexpr int S = 4, OB = 6, MAX_STEPS = 500, NACT = 3;
   static constexpr bool CONT = false, FUSED_OBS = true;      // step_observe(): the transition also yields the observation
@@ -101,8 +119,8 @@ template <> struct AcxEnv<ACX_ENV_ACROBOT> {
     const float g = 9.8f;
     const float dth1 = s[2], dth2 = s[3];
     float s1, c1, s2, c2;
-    sincosf(s[0], &s1, &c1);
-    sincosf(s[1], &s2, &c2);
+    acx_sincos_bounded(s[0], s1, c1);
+    acx_sincos_bounded(s[1], s2, c2);
     const float d1 = 0.25f + (1.0f + 0.25f + c2) + 1.0f + 1.0f;
     const float d2 = (0.25f + 0.5f * c2) + 1.0f;
     const float r1 = __frcp_rn(d1);
@@ -115,7 +133,10 @@ template <> struct AcxEnv<ACX_ENV_ACROBOT> {
   }
   __device__ static inline float wrap(float x, float lo, float hi) {
     const float diff = hi - lo;
+    // gym's `while x > M: x -= diff`; one pass at most for in-range states -- kept as real loops (not unrolled)
+#pragma unroll 1
     for (int i = 0; i < 64 && x > hi; ++i) x -= diff;
+#pragma unroll 1
     for (int i = 0; i < 64 && x < lo; ++i) x += diff;
     return x;
   }
@@ -140,8 +161,8 @@ template <> struct AcxEnv<ACX_ENV_ACROBOT> {
     y[1] = wrap(y[1], -ACX_PI_F, ACX_PI_F);
     y[2] = fminf(fmaxf(y[2], -4.0f * ACX_PI_F), 4.0f * ACX_PI_F);
     y[3] = fminf(fmaxf(y[3], -9.0f * ACX_PI_F), 9.0f * ACX_PI_F);
-    sincosf(y[0], &o[1], &o[0]);
-    sincosf(y[1], &o[3], &o[2]);
+    acx_sincos_bounded(y[0], o[1], o[0]);
+    acx_sincos_bounded(y[1], o[3], o[2]);
     o[4] = y[2]; o[5] = y[3];
     term = (-o[0] - (o[0] * o[2] - o[1] * o[3])) > 1.0f;
     rew = term ? 0.0f : -1.0f;
@@ -157,8 +178,8 @@ template <> struct AcxEnv<ACX_ENV_ACROBOT> {
     for (int k = 0; k < S; ++k) s[k] = __fadd_rn(-0.1f, __fmul_rn(0.2f, u[k]));
   }
   __device__ static inline void observe(const float (&s)[S], float (&o)[OB]) {
-    sincosf(s[0], &o[1], &o[0]);
-    sincosf(s[1], &o[3], &o[2]);
+    acx_sincos_bounded(s[0], o[1], o[0]);
+    acx_sincos_bounded(s[1], o[3], o[2]);
     o[4] = s[2]; o[5] = s[3];
   }
 };
