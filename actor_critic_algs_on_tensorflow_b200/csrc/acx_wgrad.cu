@@ -27,8 +27,12 @@ using namespace acxumma;
 
 #ifdef ACX_WG_PROF
 // dev build (make prof): issuer of CTA 0 -- [0] phase-0 cycles, [1] phase-1 cycles, [2]/[3] of which waiting for split
-// boxes, [4]/[5] boxes per phase
-__device__ unsigned long long acx_wg_prof[8];
+// boxes, [4]/[5] boxes per phase; splitter warp 6 (no flush duty), thread 0, per phase p: [8+4p] wait for the free slot,
+// [9+4p] X1 generation, [10+4p] wait for the TMA box, [11+4p] split + arrive
+__device__ unsigned long long acx_wg_prof[16];
+#define WG_SPLIT_MARK(i) do { if (sprof_) { const long long n_ = clock64(); sp_[i] += n_ - sl_; sl_ = n_; } } while (0)
+#else
+#define WG_SPLIT_MARK(i) do { } while (0)
 #endif
 
 namespace {
@@ -193,6 +197,13 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
               }
             }
             commit(reinterpret_cast<uint64_t*>(&B.empty[slot]));
+#ifdef ACX_WG_PROF_DRAIN      // measurement only: block until this box's MMAs are through (serialises the ring)
+            {
+              const long long d0_ = clock64();
+              acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.empty[slot]), (it / NSTAGE) & 1u);
+              if (blockIdx.x == 0) acx_wg_prof[6 + phase] += clock64() - d0_;
+            }
+#endif
           }
           if (++in_group == WG_FLUSH || tile + (int)gridDim.x >= ntiles) {       // group complete: hand the buffer over
             commit(reinterpret_cast<uint64_t*>(&B.dfull[buf]));
@@ -268,6 +279,10 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       const int brows = phase == 0 ? H3 : 128;
       float bacc[4] = {0.f, 0.f, 0.f, 0.f};       // bias-gradient partials of rows r0 + 32 m (chunk c4 of every box)
       float4 o[OBM], o_next[OBM];
+#ifdef ACX_WG_PROF
+      const bool sprof_ = blockIdx.x == 0 && tid == 64 + 128;
+      long long sp_[4] = {0, 0, 0, 0}, sl_ = clock64();
+#endif
       if (phase == 1) load_obs(blockIdx.x, 0, o_next);
       int in_group = 0, groups_done = 0;          // within this phase
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -285,6 +300,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             if (kk + 1 < nsub) load_obs(tile, kk + 1, o_next); else load_obs(tile + gridDim.x, 0, o_next);
             if (it >= (unsigned)NSTAGE)
               acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.empty[slot]), ((it / NSTAGE) - 1u) & 1u);
+            WG_SPLIT_MARK(0);
 #pragma unroll
             for (int m = 0; m < H1 / 32; ++m) {
               const int k = r0 + 32 * m;
@@ -305,7 +321,9 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
               l4[idx] = lo_of(x);
             }
           }
+          WG_SPLIT_MARK(1);
           acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.full[slot]), (it / NSTAGE) & 1u);
+          WG_SPLIT_MARK(2);
           if (phase == 0) {
 #pragma unroll
             for (int m = 0; m < 4; ++m) {          // A = X2 box: rows r0 + 32 m, stored chunk c4 (any bijection works)
@@ -324,6 +342,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             }
           fence_proxy_async();
           mbar_arrive(&B.split[slot]);
+          WG_SPLIT_MARK(3);
           if (warp < 6 && pend_phase >= 0) flush_slice();     // a slice of the previous group per box
         }
         if (++in_group == WG_FLUSH || tile + (int)gridDim.x >= ntiles) {
@@ -339,6 +358,9 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       // the phase's last group now (the next phase's accumulators overlap this phase's: the issuer waits for it, and the
       // ring is too short to feed a sliced flush meanwhile)
       if (warp < 6 && pend_phase >= 0) flush();
+#ifdef ACX_WG_PROF
+      if (sprof_) for (int i = 0; i < 4; ++i) acx_wg_prof[8 + 4 * phase + i] = sp_[i];
+#endif
       // the 8 threads of a row (consecutive lanes) fold their partials; fixed order -> reproducible
       float* scr = scratch + (size_t)blockIdx.x * scr_stride + (phase == 0 ? offb3 : offb2);
 #pragma unroll
@@ -391,7 +413,7 @@ int acx_wgrad_launch(const AcxWgradArgs& a, void* stream) {
 }
 
 #ifdef ACX_WG_PROF
-extern "C" int acx_wg_prof_read(unsigned long long* out8) {
-  return (int)cudaMemcpyFromSymbol(out8, acx_wg_prof, sizeof(unsigned long long) * 8);
+extern "C" int acx_wg_prof_read(unsigned long long* out16) {
+  return (int)cudaMemcpyFromSymbol(out16, acx_wg_prof, sizeof(unsigned long long) * 16);
 }
 #endif
