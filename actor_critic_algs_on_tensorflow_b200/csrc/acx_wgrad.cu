@@ -29,7 +29,7 @@ using namespace acxumma;
 // dev build (make prof): issuer of CTA 0 -- [0] phase-0 cycles, [1] phase-1 cycles, [2]/[3] of which waiting for split
 // boxes, [4]/[5] boxes per phase; splitter warp 6 (no flush duty), thread 0, per phase p: [8+4p] wait for the free slot,
 // [9+4p] X1 generation, [10+4p] wait for the TMA box, [11+4p] split + arrive
-__device__ unsigned long long acx_wg_prof[16];
+__device__ unsigned long long acx_wg_prof[24];     // [16+p]: of "wait for the free slot", the part before the wait itself
 #define WG_SPLIT_MARK(i) do { if (sprof_) { const long long n_ = clock64(); sp_[i] += n_ - sl_; sl_ = n_; } } while (0)
 #else
 #define WG_SPLIT_MARK(i) do { } while (0)
@@ -281,7 +281,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       float4 o[OBM], o_next[OBM];
 #ifdef ACX_WG_PROF
       const bool sprof_ = blockIdx.x == 0 && tid == 64 + 128;
-      long long sp_[4] = {0, 0, 0, 0}, sl_ = clock64();
+      long long sp_[5] = {0, 0, 0, 0, 0}, sl_ = clock64();
 #endif
       if (phase == 1) load_obs(blockIdx.x, 0, o_next);
       int in_group = 0, groups_done = 0;          // within this phase
@@ -298,6 +298,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
 #pragma unroll
             for (int i = 0; i < OBM; ++i) o[i] = o_next[i];
             if (kk + 1 < nsub) load_obs(tile, kk + 1, o_next); else load_obs(tile + gridDim.x, 0, o_next);
+            WG_SPLIT_MARK(4);
             if (it >= (unsigned)NSTAGE)
               acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.empty[slot]), ((it / NSTAGE) - 1u) & 1u);
             WG_SPLIT_MARK(0);
@@ -359,7 +360,10 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       // ring is too short to feed a sliced flush meanwhile)
       if (warp < 6 && pend_phase >= 0) flush();
 #ifdef ACX_WG_PROF
-      if (sprof_) for (int i = 0; i < 4; ++i) acx_wg_prof[8 + 4 * phase + i] = sp_[i];
+      if (sprof_) {
+        for (int i = 0; i < 4; ++i) acx_wg_prof[8 + 4 * phase + i] = sp_[i];
+        acx_wg_prof[16 + phase] = sp_[4];
+      }
 #endif
       // the 8 threads of a row (consecutive lanes) fold their partials; fixed order -> reproducible
       float* scr = scratch + (size_t)blockIdx.x * scr_stride + (phase == 0 ? offb3 : offb2);
@@ -414,6 +418,6 @@ int acx_wgrad_launch(const AcxWgradArgs& a, void* stream) {
 
 #ifdef ACX_WG_PROF
 extern "C" int acx_wg_prof_read(unsigned long long* out16) {
-  return (int)cudaMemcpyFromSymbol(out16, acx_wg_prof, sizeof(unsigned long long) * 16);
+  return (int)cudaMemcpyFromSymbol(out16, acx_wg_prof, sizeof(unsigned long long) * 24);
 }
 #endif

@@ -32,7 +32,7 @@ for which in ("actor", "critic"):
     lib.acx_chain_prof_read.argtypes = [C.c_void_p]
     lib.acx_chain_prof_read(buf)
     if hasattr(lib, "acx_wg_prof_read"):
-        wg = (C.c_ulonglong * 16)()
+        wg = (C.c_ulonglong * 24)()
         lib.acx_wg_prof_read.argtypes = [C.c_void_p]
         lib.acx_wg_prof_read(wg)
         for ph in (0, 1):
@@ -41,8 +41,8 @@ for which in ("actor", "critic"):
             nb = max(wg[4 + ph], 1)
             if wg[6 + ph]:
                 print("        issuer: commit -> MMAs complete %.0f cycles per box (ACX_WG_PROF_DRAIN build)" % (wg[6 + ph] / nb))
-            print("        splitter warp 6 per box: wait slot %.0f, X1 generation %.0f, wait TMA box %.0f, split + arrive %.0f"
-                  % tuple(wg[8 + 4 * ph + i] / nb for i in range(4)))
+            print("        splitter warp 6 per box: loop + obs prefetch %.0f, wait slot %.0f, X1 generation %.0f, wait TMA box %.0f, "
+                  "split + arrive %.0f" % ((wg[16 + ph] / nb,) + tuple(wg[8 + 4 * ph + i] / nb for i in range(4))))
     tot = sum(buf[i] for i in range(16))
     print(which, "total cycles", tot, "tiles ~", 20 * 512 / 148)
     for i, nm in enumerate(names):
