@@ -206,6 +206,68 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
 #ifdef ACX_CHAIN_PROF
     long long prof_[16] = {0}, last_ = clock64();
 #endif
+    // Head of one tile: loss terms, seed gradients dHead (shared memory) and the head-layer gradients (registers) from the
+    // tile's X3 block in staging buffer Sx.  It needs nothing from the tensor cores, so it runs one tile AHEAD: the
+    // head of tile t+1 fills the wait for tile t's dX2 product (its X3 block was prefetched into the other buffer at the
+    // start of tile t, and dHead of tile t has been consumed by then); only the CTA's first tile pays for its head up front.
+    auto do_head = [&](const float* __restrict__ Sx, int row_h, size_t col_h, bool live_h) {
+      // ---------------------------------------------- head
+      if (tid < MT) {
+        float pre[MAX_OUT];
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a) pre[a] = 0.f;
+        for (int k0 = 0; k0 < H3; k0 += 8) {        // head_pre's k-ascending FMA chain over the dense tile
+          float x[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) x[u] = Sx[(k0 + u) * MT + tid];
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) pre[a] = fmaf(x[u], sm.Wh[(k0 + u) * nout + a], pre[a]);
+        }
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a)
+          if (a < nout) pre[a] = __fadd_rn(pre[a], sm.bh[a]);
+        float dh[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
+        head_apply<HEAD, MODE_TRAIN>(A, sm.log_std, nout, pre, live_h, row_h, col_h, hs, lsum, dls, dh);
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a)
+          if (a < nout) sm.dHead[a * MT + tid] = dh[a];
+      }
+      work_sync();
+      PROF_MARK(1);
+      {   // head weights and bias.  Thread k < H3 owns row k of the dense tile; rows are 512 bytes apart, so every thread
+          // starts at its own 16-byte column (k mod 32) and wraps: a warp's accesses are then 512 distinct bytes
+        if (tid < H3) {
+          for (int a = 0; a < nout; ++a) {
+            float acc = 0.f;
+#pragma unroll 8
+            for (int m4 = 0; m4 < MT / 4; ++m4) {
+              const int mm = (m4 + tid) & 31;
+              const float4 x = *reinterpret_cast<const float4*>(&Sx[tid * MT + 4 * mm]);
+              const float4 d = *reinterpret_cast<const float4*>(&sm.dHead[a * MT + 4 * mm]);
+              acc = fmaf(x.x, d.x, acc); acc = fmaf(x.y, d.y, acc); acc = fmaf(x.z, d.z, acc); acc = fmaf(x.w, d.w, acc);
+            }
+            gWh[a] += acc;
+          }
+        } else if (tid >= 128 && tid < 128 + nout) {
+          const int a = tid - 128;
+          float acc = 0.f;
+          for (int m = 0; m < MT; ++m) acc += sm.dHead[a * MT + m];
+          gbh += acc;
+        }
+      }
+      PROF_MARK(2);
+      work_sync();                                  // head-layer gradients have read their X3 rows
+    };
+    if ((int)blockIdx.x < ntiles) {                 // the first tile's head
+      const int t0 = blockIdx.x, n00 = (t0 % tpr) * MT;
+      acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[0]), act_phase[0] & 1u);
+      ++act_phase[0];
+      work_sync();
+      do_head(sm.S[0], t0 / tpr, (size_t)n00 + s, s < min(MT, A.n - n00));
+    }
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tiles_done) {
       const int row = tile / tpr, n0 = (tile % tpr) * MT;
       const int valid = min(MT, A.n - n0);
@@ -234,61 +296,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         m2[1] = pack_x2();
       }
       PROF_MARK(12);
-      acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[buf]), act_phase[buf] & 1u);
-      ++act_phase[buf];
-      PROF_MARK(13);
-      work_sync();
-      PROF_MARK(0);
 
-      // ---------------------------------------------- head
-      if (tid < MT) {
-        float pre[MAX_OUT];
-#pragma unroll
-        for (int a = 0; a < MAX_OUT; ++a) pre[a] = 0.f;
-        for (int k0 = 0; k0 < H3; k0 += 8) {        // head_pre's k-ascending FMA chain over the dense tile
-          float x[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) x[u] = S[(k0 + u) * MT + tid];
-#pragma unroll
-          for (int u = 0; u < 8; ++u)
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) pre[a] = fmaf(x[u], sm.Wh[(k0 + u) * nout + a], pre[a]);
-        }
-#pragma unroll
-        for (int a = 0; a < MAX_OUT; ++a)
-          if (a < nout) pre[a] = __fadd_rn(pre[a], sm.bh[a]);
-        float dh[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
-        head_apply<HEAD, MODE_TRAIN>(A, sm.log_std, nout, pre, live, row, col, hs, lsum, dls, dh);
-#pragma unroll
-        for (int a = 0; a < MAX_OUT; ++a)
-          if (a < nout) sm.dHead[a * MT + tid] = dh[a];
-      }
-      work_sync();
-      PROF_MARK(1);
-      {   // head weights and bias.  Thread k < H3 owns row k of the dense tile; rows are 512 bytes apart, so every thread
-          // starts at its own 16-byte column (k mod 32) and wraps: a warp's accesses are then 512 distinct bytes
-        if (tid < H3) {
-          for (int a = 0; a < nout; ++a) {
-            float acc = 0.f;
-#pragma unroll 8
-            for (int m4 = 0; m4 < MT / 4; ++m4) {
-              const int mm = (m4 + tid) & 31;
-              const float4 x = *reinterpret_cast<const float4*>(&S[tid * MT + 4 * mm]);
-              const float4 d = *reinterpret_cast<const float4*>(&sm.dHead[a * MT + 4 * mm]);
-              acc = fmaf(x.x, d.x, acc); acc = fmaf(x.y, d.y, acc); acc = fmaf(x.z, d.z, acc); acc = fmaf(x.w, d.w, acc);
-            }
-            gWh[a] += acc;
-          }
-        } else if (tid >= 128 && tid < 128 + nout) {
-          const int a = tid - 128;
-          float acc = 0.f;
-          for (int m = 0; m < MT; ++m) acc += sm.dHead[a * MT + m];
-          gbh += acc;
-        }
-      }
-      PROF_MARK(2);
-      work_sync();                                  // head-layer gradients have read their X3 rows
       // ---------------------------------------------- dPre3: A operand + HBM stream (staged in place over X3)
       {
         float dh[MAX_OUT];
@@ -322,6 +330,16 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       work_sync();
       bulk_rows_out(S, d3_out + cache_tile_off(tile, H3), H3);
       PROF_MARK(3);
+      {   // the next tile's head, while the tensor cores form dX2 (dHead of this tile was consumed above)
+        const int next = tile + gridDim.x;
+        if (next < ntiles) {
+          const int n0n = (next % tpr) * MT;
+          acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar_act[buf ^ 1]), act_phase[buf ^ 1] & 1u);
+          ++act_phase[buf ^ 1];
+          PROF_MARK(13);
+          do_head(sm.S[buf ^ 1], next / tpr, (size_t)n0n + s, s < min(MT, A.n - n0n));
+        }
+      }
       // ---------------------------------------------- dPre2 = dX2 * act'(X2): next A operand + HBM stream
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done[0]), par);
       fence_after_sync();
