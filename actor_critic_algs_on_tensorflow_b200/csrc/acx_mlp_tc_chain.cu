@@ -209,7 +209,8 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
     // Head of one tile: loss terms, seed gradients dHead (shared memory) and the head-layer gradients (registers) from the
     // tile's X3 block in staging buffer Sx.  It needs nothing from the tensor cores, so it runs one tile AHEAD: the
     // head of tile t+1 fills the wait for tile t's dX2 product (its X3 block was prefetched into the other buffer at the
-    // start of tile t, and dHead of tile t has been consumed by then); only the CTA's first tile pays for its head up front.
+    // start of tile t, and dHead of tile t has been consumed by then), its head-layer gradients the wait for dX1; only
+    // the CTA's first tile pays for its head up front.
     auto do_head = [&](const float* __restrict__ Sx, int row_h, size_t col_h, bool live_h) {
       // ---------------------------------------------- head
       if (tid < MT) {
@@ -237,6 +238,9 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       }
       work_sync();
       PROF_MARK(1);
+    };
+    // ... and its head-layer gradients, which fill the wait for dX1 (they read the same X3 block and dHead)
+    auto do_head_grads = [&](const float* __restrict__ Sx) {
       {   // head weights and bias.  Thread k < H3 owns row k of the dense tile; rows are 512 bytes apart, so every thread
           // starts at its own 16-byte column (k mod 32) and wraps: a warp's accesses are then 512 distinct bytes
         if (tid < H3) {
@@ -267,6 +271,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       ++act_phase[0];
       work_sync();
       do_head(sm.S[0], t0 / tpr, (size_t)n00 + s, s < min(MT, A.n - n00));
+      do_head_grads(sm.S[0]);
     }
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tiles_done) {
       const int row = tile / tpr, n0 = (tile % tpr) * MT;
@@ -367,6 +372,7 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
       work_sync();
       bulk_rows_out(S, d2_out + cache_tile_off(tile, H2), H2);
       PROF_MARK(15);
+      if (tile + (int)gridDim.x < ntiles) do_head_grads(sm.S[buf ^ 1]);      // while the tensor cores form dX1
       if (!MASKS) load_x2(tile + gridDim.x, 1);     // next tile's upper 32 (zeros past the last tile)
       // this thread's observation (registers; also the shared copy layer1_grad reads), while dX1 is formed
       float ob_r[MAX_OB];
