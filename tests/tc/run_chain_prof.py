@@ -15,9 +15,11 @@ for _ in range(2):
     tr.iteration()
 torch.cuda.synchronize()
 lib = L.load()
-names = ["sync after X3 wait", "head", "head grads", "dPre3 + sync + row stores", "wait MMA3", "next-tile mask / obs loads",
-         "wait MMA2 b0", "dPre1 b0", "l1grad b0", "wait MMA2 b1", "dPre1 b1", "l1grad b1",
-         "tile start: X3 prefetch, mask pack + loads", "tile start: wait X3", "dPre2 loop", "dPre2: st-wait, arrive, row stores"]
+names = ["(unused)", "head of the NEXT tile (inside the dX2 wait)", "head-layer gradients of the NEXT tile (inside the dX1 wait)",
+         "dPre3 + sync + bulk store", "wait MMA3 (what the head did not cover)", "obs loads",
+         "wait MMA2 b0 (what the head gradients did not cover)", "dPre1 b0", "l1grad b0", "wait MMA2 b1", "dPre1 b1", "l1grad b1",
+         "tile start: X3 prefetch issue, mask loads", "wait for the next tile's X3 block", "dPre2 loop",
+         "dPre2: st-wait, arrive, bulk store"]
 buf = (C.c_ulonglong * 16)()
 s = L.cur_stream()
 for which in ("actor", "critic"):
