@@ -262,6 +262,57 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
       }
     };
 
+    // Layer 1 of one 128-feature block of tile `tile_l` from the observation in o[] -> A operand (two hand-overs of 64
+    // features).  In the evaluation modes block 0 of the NEXT tile is produced right after the wait for this tile's
+    // layer-3 MMAs, before this tile's X3 epilogue and head: the tensor cores then form the next tile's layer 2 while
+    // the workers finish this tile (the A operand is free once layer 3 has been read; D3 is not touched by layer 2).
+    // The rollout cannot do that: its next observation comes out of this step's head.
+    float o[MAX_OB];
+    auto l1_block = [&](int blk, int tile_l) {
+#pragma unroll 1
+      for (int gq = 0; gq < 2; ++gq) {           // this thread: features gq*64 + half*32 .. +31 of the block
+        float v[32];
+        const int j0 = gq * 64 + half * 32;
+        if (ob <= 3) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const float4 w = sm.W1p[blk * 128 + j0 + e];
+            float acc = fmaf(o[0], w.x, 0.f);
+            if (ob > 1) acc = fmaf(o[1], w.y, acc);
+            if (ob > 2) acc = fmaf(o[2], w.z, acc);
+            v[e] = act_fn<LRELU>(__fadd_rn(acc, w.w));
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int k = blk * 128 + j0 + e;
+            float acc = 0.f;
+#pragma unroll
+            for (int i = 0; i < MAX_OB; ++i)
+              if (i < ob) acc = fmaf(o[i], sm.W1[i * H1 + k], acc);
+            v[e] = act_fn<LRELU>(__fadd_rn(acc, sm.b1[k]));
+          }
+        }
+        if (A.mask_out != nullptr) {             // act'(X1) for the chain kernel
+          unsigned int bits = 0u;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
+          A.mask_out[mask_tile_off(tile_l, H1) + (size_t)(blk * 4 + gq * 2 + half) * MT + s] = bits;
+        }
+        if (blk > 0 && gq == 0) {                // the MMAs reading the previous block must be done
+          FPROF(1);
+          acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
+          fence_after_sync();
+          FPROF(2);
+        }
+        a_store32(tl, j0, v);
+        tmem_wait_st();
+        fence_before_sync();
+        mbar_arrive(&sm.a_ready[gq]);            // features gq*64 .. +63 of the A operand are in place
+      }
+      FPROF(blk == 0 ? 0 : 3);
+    };
+    bool l1_ahead = false;                         // block 0 of the tile the loop is about to start is already in flight
     for (int outer = blockIdx.x; outer < nouter; outer += gridDim.x)
     for (int t = 0; t < T; ++t) {
       const int tile = ROLL ? t * tpr + outer : outer;
@@ -269,11 +320,12 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
       const int valid = min(MT, A.n - n0);
       const bool live = s < valid;
       const size_t col = (size_t)n0 + s;
-      float o[MAX_OB];
       if (!ROLL) {
+        if (!l1_ahead) {
 #pragma unroll
-        for (int i = 0; i < MAX_OB; ++i) o[i] = o_next[i];
-        load_obs(tile + gridDim.x, o_next);
+          for (int i = 0; i < MAX_OB; ++i) o[i] = o_next[i];
+          load_obs(tile + gridDim.x, o_next);
+        }
       } else if (t == 0) {
         load_obs(tile, o);
         if (half == 0 && live) {
@@ -288,48 +340,8 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
 
       // ---------------------------------------------- layer 1 -> A operand, one 128-feature block per stage
       for (int blk = 0; blk < NB; ++blk) {
-#pragma unroll 1
-        for (int gq = 0; gq < 2; ++gq) {           // this thread: features gq*64 + half*32 .. +31 of the block
-          float v[32];
-          const int j0 = gq * 64 + half * 32;
-          if (ob <= 3) {
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const float4 w = sm.W1p[blk * 128 + j0 + e];
-              float acc = fmaf(o[0], w.x, 0.f);
-              if (ob > 1) acc = fmaf(o[1], w.y, acc);
-              if (ob > 2) acc = fmaf(o[2], w.z, acc);
-              v[e] = act_fn<LRELU>(__fadd_rn(acc, w.w));
-            }
-          } else {
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const int k = blk * 128 + j0 + e;
-              float acc = 0.f;
-#pragma unroll
-              for (int i = 0; i < MAX_OB; ++i)
-                if (i < ob) acc = fmaf(o[i], sm.W1[i * H1 + k], acc);
-              v[e] = act_fn<LRELU>(__fadd_rn(acc, sm.b1[k]));
-            }
-          }
-          if (A.mask_out != nullptr) {             // act'(X1) for the chain kernel
-            unsigned int bits = 0u;
-#pragma unroll
-            for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
-            A.mask_out[mask_tile_off(tile, H1) + (size_t)(blk * 4 + gq * 2 + half) * MT + s] = bits;
-          }
-          if (blk > 0 && gq == 0) {                // the MMAs reading the previous block must be done
-            FPROF(1);
-            acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
-            fence_after_sync();
-            FPROF(2);
-          }
-          a_store32(tl, j0, v);
-          tmem_wait_st();
-          fence_before_sync();
-          mbar_arrive(&sm.a_ready[gq]);            // features gq*64 .. +63 of the A operand are in place
-        }
-        FPROF(blk == 0 ? 0 : 3);
+        if (blk == 0 && l1_ahead) continue;
+        l1_block(blk, tile);
       }
       // ---------------------------------------------- layer-2 epilogue: X2 = act(D2 + b2) -> A operand (+ cache)
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
@@ -368,6 +380,17 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
       fence_after_sync();
       FPROF(6);
+      if (!ROLL) {                                 // the next tile's layer-1 block 0, ahead of this tile's epilogue
+        const int nxt = tile + (int)gridDim.x;
+        l1_ahead = nxt < ntiles;
+        if (l1_ahead) {
+#pragma unroll
+          for (int i = 0; i < MAX_OB; ++i) o[i] = o_next[i];
+          load_obs(nxt + (int)gridDim.x, o_next);
+          l1_block(0, nxt);
+        }
+        FPROF(10);
+      }
 #pragma unroll 1
       for (int gq = 0; gq < H3 / 64; ++gq) {       // this thread: H3/2 features
         float v[32];
