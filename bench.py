@@ -450,12 +450,12 @@ def run_ours(args, rank, local_rank, world):
                     "frac_of_fp32_ffma_peak": dom["achieved"] / FP32_PEAK_TFLOPS,
                     "share_of_step": dom["ms"] / step_ms,
                     # dram__bytes_read.sum + dram__bytes_write.sum of the two kernels, one ncu --set full capture of this
-                    # workload (profiles/r01_ncu_tc_backward.md): chain 0.756 + 1.289 GB, wgrad 2.185 + 0.213 GB
+                    # workload (profiles/r01_ncu_tc_backward.md): chain 0.756 + 1.289 GB, wgrad 2.186 + 0.212 GB
                     "traffic": 4.443e9 if (N_ENVS, HORIZON) == (65536, 20) else None, "traffic_unit": "bytes per launch",
                     "algorithmic_bytes": 4.09e9 if (N_ENVS, HORIZON) == (65536, 20) else None,
                     # the same capture: sm__pipe_tc_cycles_active (the MMA instruction rate measured by
                     # tests/tc/run_mma_rate.py, 2,007 MAC/clk/SM, is above measured-bf16 / 2, so `frac` flatters the pipe)
-                    "tensor_pipe_active_ncu": {"chain": 0.316, "wgrad": 0.459},
+                    "tensor_pipe_active_ncu": {"chain": 0.370, "wgrad": 0.432},
                     "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
         else:
             roof = {"kernel": dom_kernel, "bound": "fp32",

@@ -16,8 +16,9 @@ for _ in range(2):
 torch.cuda.synchronize()
 lib = L.load()
 lib.acx_fwd_prof_read.argtypes = [C.c_void_p]
-names = ["layer 1 block 0 -> A", "layer 1 block 1 compute", "wait MMA block 0", "layer 1 block 1 -> A", "wait MMA layer 2",
-         "X2 epilogue (+cache) -> A", "wait MMA layer 3", "X3 epilogue (+cache), head partial", "sync", "head"]
+names = ["layer 1 block 0 -> A (first tile only: later tiles at [10])", "layer 1 block 1 compute", "wait MMA block 0",
+         "layer 1 block 1 -> A", "wait MMA layer 2", "X2 epilogue (+cache) -> A", "wait MMA layer 3",
+         "X3 epilogue (+cache), head partial", "sync", "head", "layer 1 block 0 of the NEXT tile -> A (ahead of the epilogue)"]
 buf = (C.c_ulonglong * 16)()
 s = L.cur_stream()
 T, N = tr.T, tr.N
@@ -33,7 +34,7 @@ for which in ("value", "logp"):
         tiles = T * 512 / 148
     torch.cuda.synchronize()
     lib.acx_fwd_prof_read(buf)
-    tot = sum(buf[i] for i in range(10))
+    tot = sum(buf[i] for i in range(11))
     print(which, "total cycles", tot, "tiles ~ %.1f" % tiles)
     for i, nm in enumerate(names):
         print("  %-40s %9d  %5.1f%%  per tile %7.0f" % (nm, buf[i], 100.0 * buf[i] / max(tot, 1), buf[i] / tiles))
