@@ -144,6 +144,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
     if (HEAD == HEAD_GAUSS) sm.log_std[tid] = P[L.log_std + tid];
   }
   constexpr bool ROLL = ENVR >= 0;
+  static_assert(!ROLL || (H3 == 64 && H1 == 128), "the rollout keeps two 64-column layer-3 accumulators (D3 buffer = unit & 1)");
   const int tpr = (A.n + MT - 1) / MT;
   const int ntiles = A.rows * tpr;
   const int nouter = ROLL ? tpr : ntiles;         // what a CTA iterates over: column tiles (x T steps each) or tiles
@@ -195,7 +196,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
           acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.a_ready[sub]), ready & 1u);
           fence_after_sync();
           for (int kc = sub * (N3C / 2); kc < (sub + 1) * (N3C / 2); ++kc)
-            pipe.mma_chunk(tmem, kc * KC3, KC3, H3, tmem + TC_D3, kc == 0);
+            pipe.mma_chunk(tmem, kc * KC3, KC3, H3, tmem + TC_D3 + (ROLL ? 64u * (t & 1u) : 0u), kc == 0);
         }
         ++ready;
         commit(reinterpret_cast<uint64_t*>(&sm.stage_done));
@@ -225,11 +226,11 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
 #endif
     // rollout: this sample's environment (first warpgroup), in registers for all T steps
     constexpr int ES = AcxEnv<ROLL ? ENVR : 0>::S, EOB = AcxEnv<ROLL ? ENVR : 0>::OB;   // (unused unless ROLL)
-    float est[ES];
-    int eel = 0;
+    float est[ES], est_b[ES];                      // (est_b / eel_b: the second tile of a pair, see the pair loop)
+    int eel = 0, eel_b = 0;
     const int emax = ROLL ? (A.max_steps > 0 ? A.max_steps : AcxEnv<ROLL ? ENVR : 0>::MAX_STEPS) : 0;
     // one environment transition after the action of step `row` (the arithmetic and order of acx_env_step_kernel)
-    auto env_step = [&](float act, int row, size_t col) {
+    auto env_step = [&](float act, int row, size_t col, float (&est)[ES], int& eel, float* __restrict__ obsx) {
       if (!ROLL) return;
       float rew;
       bool term;
@@ -258,10 +259,197 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
 #pragma unroll
       for (int k = 0; k < EOB; ++k) {
         A.obs_rw[((size_t)(row + 1) * EOB + k) * A.n + col] = ov[k];
-        sm.obs_x[k * MT + s] = ov[k];
+        obsx[k * MT + s] = ov[k];
       }
     };
 
+    // wait for the layer-2 MMAs, then X2 = act(D2 + b2) -> A operand (+ cache, masks) in two hand-overs
+    auto ph_x2 = [&](int tile, bool live, float (&pre)[MAX_OUT]) {
+      // ---------------------------------------------- layer-2 epilogue: X2 = act(D2 + b2) -> A operand (+ cache)
+      acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
+      fence_after_sync();
+      FPROF(4);
+#pragma unroll 1
+      for (int gq = 0; gq < 2; ++gq) {
+        float v[32];
+        const int j0 = gq * 64 + half * 32;
+        tmem_ld32(tl + TC_D2 + (uint32_t)j0, v);
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b2[j0 + e]));
+        if (A.mask_out != nullptr) {               // act'(X2)
+          unsigned int bits = 0u;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
+          A.mask_out[mask_tile_off(tile, H1) + (size_t)(H1 / 32 + gq * 2 + half) * MT + s] = bits;
+        }
+        if (A.x2_out != nullptr) {                 // tile-blocked cache; zeros beyond the batch
+          float* g2 = A.x2_out + cache_tile_off(tile, H2) + (size_t)j0 * MT + s;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) g2[e * MT] = live ? v[e] : 0.f;
+        }
+        if (basic) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) pre[0] = fmaf(v[e], sm.Wh[j0 + e], pre[0]);
+        }
+        a_store32(tl, j0, v);
+        tmem_wait_st();
+        fence_before_sync();
+        mbar_arrive(&sm.a_ready[gq]);
+      }
+      FPROF(5);
+    };
+    // X3 = act(D3 + b3) (+ cache) from the accumulator at column d3, head partial sums, exchange, head: outputs of the
+    // sample; pact = the action the env step takes (rollout)
+    auto ph_x3 = [&](int tile, int row, size_t col, bool live, uint32_t d3, float (&pre)[MAX_OUT], float& pact) {
+      (void)tile;
+#pragma unroll 1
+      for (int gq = 0; gq < H3 / 64; ++gq) {       // this thread: H3/2 features
+        float v[32];
+        const int j0 = half * (H3 / 2) + gq * 32;
+        tmem_ld32(tl + d3 + (uint32_t)j0, v);
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b3[j0 + e]));
+        if (A.x3_out != nullptr) {
+          float* g3 = A.x3_out + cache_tile_off(tile, H3) + (size_t)j0 * MT + s;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) g3[e * MT] = live ? v[e] : 0.f;
+        }
+        if (!basic) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) pre[a] = fmaf(v[e], sm.Wh[(j0 + e) * nout + a], pre[a]);
+          }
+        }
+      }
+      if (half == 1) {
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a)
+          if (a < nout) sm.pre[a * MT + s] = pre[a];
+      }
+      FPROF(7);
+      epi_sync();
+      FPROF(8);
+      if (half == 0) {
+#pragma unroll
+        for (int a = 0; a < MAX_OUT; ++a)
+          if (a < nout) pre[a] = __fadd_rn(__fadd_rn(pre[a], sm.pre[a * MT + s]), sm.bh[a]);
+        const size_t s_idx = (size_t)row * A.n + col;
+        if (live) {
+          if (HEAD == HEAD_VALUE) {
+            A.v_out[s_idx] = pre[0];
+          } else if (HEAD == HEAD_GAUSS) {
+            float lp = 0.f, ent = 0.f, ac_env = 0.f;
+            AcxRng4 g = {0u, 0u, 0u, 0u};
+            if (MODE == MODE_SAMPLE && A.noise == nullptr)
+              g = acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed);
+#pragma unroll
+            for (int d = 0; d < MAX_OUT; ++d)
+              if (d < nout) {
+                const float mu = __fmul_rn(tanhf(pre[d]), A.ac_scale);
+                const float ls = fminf(fmaxf(sm.log_std[d], ACX_LOG_STD_MIN), ACX_LOG_STD_MAX);
+                const float sd = expf(ls);
+                const size_t a_idx = ((size_t)row * nout + d) * A.n + col;
+                float ac;
+                if (MODE == MODE_SAMPLE) {
+                  float eps;
+                  if (A.noise) eps = A.noise[a_idx];
+                  else eps = (d == 0) ? acx_normal(g.x, g.y) : ((d == 1) ? acx_normal(g.z, g.w) : 0.f);
+                  ac = __fadd_rn(mu, __fmul_rn(sd, eps));
+                  A.ac_out_f[a_idx] = ac;
+                  if (d == 0) ac_env = ac;
+                } else {
+                  ac = A.ac_in_f[a_idx];
+                }
+                if (A.head_out) A.head_out[a_idx] = mu;
+                const float z = __fdiv_rn(__fsub_rn(ac, mu), sd);
+                lp += __fsub_rn(__fsub_rn(__fmul_rn(__fmul_rn(-0.5f, z), z), ls), ACX_HALF_LOG_2PI);
+                ent += __fadd_rn(__fadd_rn(0.5f, ACX_HALF_LOG_2PI), ls);
+              }
+            if (A.logp_out) A.logp_out[s_idx] = lp;
+            if (A.ent_out) A.ent_out[s_idx] = ent;
+            if (MODE == MODE_EVAL && A.logp_old) {
+              const double df = (double)A.logp_old[s_idx] - (double)lp;
+              kl_sum += df * df;
+            }
+            pact = ac_env;
+          } else {   // HEAD_CAT
+            float l1[MAX_OUT], logps[MAX_OUT], p[MAX_OUT];
+            float mx1 = -INFINITY, mx2 = -INFINITY;
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) {
+                l1[a] = __fadd_rn(pre[a], 1e-8f);
+                mx1 = fmaxf(mx1, l1[a]); mx2 = fmaxf(mx2, pre[a]);
+              }
+            float se1 = 0.f, se2 = 0.f;
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) {
+                se1 += expf(l1[a] - mx1);
+                p[a] = expf(pre[a] - mx2);
+                se2 += p[a];
+              }
+            const float lse = mx1 + logf(se1);
+            float ent = 0.f;
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout) {
+                logps[a] = l1[a] - lse;
+                p[a] = p[a] / se2;
+                ent -= p[a] * logps[a];
+              }
+            int ac;
+            if (MODE == MODE_SAMPLE) {
+              float u;
+              if (A.noise) u = A.noise[s_idx];
+              else u = acx_u01(acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed).x);
+              double cdf[MAX_OUT], run = 0.0;
+#pragma unroll
+              for (int a = 0; a < MAX_OUT; ++a)
+                if (a < nout) { run += exp((double)pre[a] - (double)mx2); cdf[a] = run; }
+              const double thr = (double)u * run;
+              ac = 0;
+#pragma unroll
+              for (int a = 0; a < MAX_OUT; ++a)
+                if (a < nout && cdf[a] <= thr) ++ac;
+              if (ac > nout - 1) ac = nout - 1;
+              A.ac_out_i[s_idx] = ac;
+            } else {
+              ac = A.ac_in_i[s_idx];
+            }
+            float lp = 0.f;
+#pragma unroll
+            for (int a = 0; a < MAX_OUT; ++a)
+              if (a < nout && a == ac) lp = logps[a];
+            if (A.head_out) {
+#pragma unroll
+              for (int a = 0; a < MAX_OUT; ++a)
+                if (a < nout) A.head_out[((size_t)row * nout + a) * A.n + col] = pre[a];
+            }
+            if (A.logp_out) A.logp_out[s_idx] = lp;
+            if (A.ent_out) A.ent_out[s_idx] = ent;
+            if (MODE == MODE_EVAL && A.logp_old) {
+              const double df = (double)A.logp_old[s_idx] - (double)lp;
+              kl_sum += df * df;
+            }
+            pact = (float)ac;
+          }
+        }
+      }
+    };
+    // rollout: the env step of the sample (first warpgroup) -> reward, done, next observation (HBM and obsx)
+    auto tail_env = [&](float pact, int row, size_t col, bool live, float (&est_x)[ES], int& eel_x, float* __restrict__ obsx) {
+      if (half != 0) return;
+      if (live) {
+        env_step(pact, row, col, est_x, eel_x, obsx);
+      } else {
+#pragma unroll
+        for (int k = 0; k < EOB; ++k) obsx[k * MT + s] = 0.f;
+      }
+    };
+    unsigned int units = 0;                        // rollout: (tile, step) units done; unit u accumulates layer 3 in D3 buffer u & 1
     // Layer 1 of one 128-feature block of tile `tile_l` from the observation in o[] -> A operand (two hand-overs of 64
     // features).  In the evaluation modes block 0 of the NEXT tile is produced right after the wait for this tile's
     // layer-3 MMAs, before this tile's X3 epilogue and head: the tensor cores then form the next tile's layer 2 while
@@ -343,39 +531,8 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         if (blk == 0 && l1_ahead) continue;
         l1_block(blk, tile);
       }
-      // ---------------------------------------------- layer-2 epilogue: X2 = act(D2 + b2) -> A operand (+ cache)
-      acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
-      fence_after_sync();
-      FPROF(4);
       float pre[MAX_OUT] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 1
-      for (int gq = 0; gq < 2; ++gq) {
-        float v[32];
-        const int j0 = gq * 64 + half * 32;
-        tmem_ld32(tl + TC_D2 + (uint32_t)j0, v);
-#pragma unroll
-        for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b2[j0 + e]));
-        if (A.mask_out != nullptr) {               // act'(X2)
-          unsigned int bits = 0u;
-#pragma unroll
-          for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
-          A.mask_out[mask_tile_off(tile, H1) + (size_t)(H1 / 32 + gq * 2 + half) * MT + s] = bits;
-        }
-        if (A.x2_out != nullptr) {                 // tile-blocked cache; zeros beyond the batch
-          float* g2 = A.x2_out + cache_tile_off(tile, H2) + (size_t)j0 * MT + s;
-#pragma unroll
-          for (int e = 0; e < 32; ++e) g2[e * MT] = live ? v[e] : 0.f;
-        }
-        if (basic) {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) pre[0] = fmaf(v[e], sm.Wh[j0 + e], pre[0]);
-        }
-        a_store32(tl, j0, v);
-        tmem_wait_st();
-        fence_before_sync();
-        mbar_arrive(&sm.a_ready[gq]);
-      }
-      FPROF(5);
+      ph_x2(tile, live, pre);
       // ---------------------------------------------- layer-3 epilogue + head
       acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
       fence_after_sync();
@@ -391,144 +548,11 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         }
         FPROF(10);
       }
-#pragma unroll 1
-      for (int gq = 0; gq < H3 / 64; ++gq) {       // this thread: H3/2 features
-        float v[32];
-        const int j0 = half * (H3 / 2) + gq * 32;
-        tmem_ld32(tl + TC_D3 + (uint32_t)j0, v);
-#pragma unroll
-        for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b3[j0 + e]));
-        if (A.x3_out != nullptr) {
-          float* g3 = A.x3_out + cache_tile_off(tile, H3) + (size_t)j0 * MT + s;
-#pragma unroll
-          for (int e = 0; e < 32; ++e) g3[e * MT] = live ? v[e] : 0.f;
-        }
-        if (!basic) {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) {
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) pre[a] = fmaf(v[e], sm.Wh[(j0 + e) * nout + a], pre[a]);
-          }
-        }
-      }
-      if (half == 1) {
-#pragma unroll
-        for (int a = 0; a < MAX_OUT; ++a)
-          if (a < nout) sm.pre[a * MT + s] = pre[a];
-      }
-      FPROF(7);
-      epi_sync();
-      FPROF(8);
-      if (half == 0) {
-#pragma unroll
-        for (int a = 0; a < MAX_OUT; ++a)
-          if (a < nout) pre[a] = __fadd_rn(__fadd_rn(pre[a], sm.pre[a * MT + s]), sm.bh[a]);
-        const size_t s_idx = (size_t)row * A.n + col;
-        if (live) {
-          if (HEAD == HEAD_VALUE) {
-            A.v_out[s_idx] = pre[0];
-          } else if (HEAD == HEAD_GAUSS) {
-            float lp = 0.f, ent = 0.f, ac_env = 0.f;
-            AcxRng4 g = {0u, 0u, 0u, 0u};
-            if (MODE == MODE_SAMPLE && A.noise == nullptr)
-              g = acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed);
-#pragma unroll
-            for (int d = 0; d < MAX_OUT; ++d)
-              if (d < nout) {
-                const float mu = __fmul_rn(tanhf(pre[d]), A.ac_scale);
-                const float ls = fminf(fmaxf(sm.log_std[d], ACX_LOG_STD_MIN), ACX_LOG_STD_MAX);
-                const float sd = expf(ls);
-                const size_t a_idx = ((size_t)row * nout + d) * A.n + col;
-                float ac;
-                if (MODE == MODE_SAMPLE) {
-                  float eps;
-                  if (A.noise) eps = A.noise[a_idx];
-                  else eps = (d == 0) ? acx_normal(g.x, g.y) : ((d == 1) ? acx_normal(g.z, g.w) : 0.f);
-                  ac = __fadd_rn(mu, __fmul_rn(sd, eps));
-                  A.ac_out_f[a_idx] = ac;
-                  if (d == 0) ac_env = ac;
-                } else {
-                  ac = A.ac_in_f[a_idx];
-                }
-                if (A.head_out) A.head_out[a_idx] = mu;
-                const float z = __fdiv_rn(__fsub_rn(ac, mu), sd);
-                lp += __fsub_rn(__fsub_rn(__fmul_rn(__fmul_rn(-0.5f, z), z), ls), ACX_HALF_LOG_2PI);
-                ent += __fadd_rn(__fadd_rn(0.5f, ACX_HALF_LOG_2PI), ls);
-              }
-            if (A.logp_out) A.logp_out[s_idx] = lp;
-            if (A.ent_out) A.ent_out[s_idx] = ent;
-            if (MODE == MODE_EVAL && A.logp_old) {
-              const double df = (double)A.logp_old[s_idx] - (double)lp;
-              kl_sum += df * df;
-            }
-            if (ROLL) env_step(ac_env, row, col);
-          } else {   // HEAD_CAT
-            float l1[MAX_OUT], logps[MAX_OUT], p[MAX_OUT];
-            float mx1 = -INFINITY, mx2 = -INFINITY;
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) {
-                l1[a] = __fadd_rn(pre[a], 1e-8f);
-                mx1 = fmaxf(mx1, l1[a]); mx2 = fmaxf(mx2, pre[a]);
-              }
-            float se1 = 0.f, se2 = 0.f;
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) {
-                se1 += expf(l1[a] - mx1);
-                p[a] = expf(pre[a] - mx2);
-                se2 += p[a];
-              }
-            const float lse = mx1 + logf(se1);
-            float ent = 0.f;
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) {
-                logps[a] = l1[a] - lse;
-                p[a] = p[a] / se2;
-                ent -= p[a] * logps[a];
-              }
-            int ac;
-            if (MODE == MODE_SAMPLE) {
-              float u;
-              if (A.noise) u = A.noise[s_idx];
-              else u = acx_u01(acx_philox(A.index0 + col, step0 + (unsigned)row, ACX_STREAM_ACTION, A.seed).x);
-              double cdf[MAX_OUT], run = 0.0;
-#pragma unroll
-              for (int a = 0; a < MAX_OUT; ++a)
-                if (a < nout) { run += exp((double)pre[a] - (double)mx2); cdf[a] = run; }
-              const double thr = (double)u * run;
-              ac = 0;
-#pragma unroll
-              for (int a = 0; a < MAX_OUT; ++a)
-                if (a < nout && cdf[a] <= thr) ++ac;
-              if (ac > nout - 1) ac = nout - 1;
-              A.ac_out_i[s_idx] = ac;
-            } else {
-              ac = A.ac_in_i[s_idx];
-            }
-            float lp = 0.f;
-#pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout && a == ac) lp = logps[a];
-            if (A.head_out) {
-#pragma unroll
-              for (int a = 0; a < MAX_OUT; ++a)
-                if (a < nout) A.head_out[((size_t)row * nout + a) * A.n + col] = pre[a];
-            }
-            if (A.logp_out) A.logp_out[s_idx] = lp;
-            if (A.ent_out) A.ent_out[s_idx] = ent;
-            if (MODE == MODE_EVAL && A.logp_old) {
-              const double df = (double)A.logp_old[s_idx] - (double)lp;
-              kl_sum += df * df;
-            }
-            if (ROLL) env_step((float)ac, row, col);
-          }
-        } else if (ROLL) {
-#pragma unroll
-          for (int k = 0; k < EOB; ++k) sm.obs_x[k * MT + s] = 0.f;
-        }
+      float pact = 0.f;
+      ph_x3(tile, row, col, live, ROLL ? TC_D3 + 64u * (units & 1u) : TC_D3, pre, pact);
+      if (ROLL) {
+        tail_env(pact, row, col, live, est, eel, sm.obs_x);
+        ++units;
       }
       if (ROLL) {
         if (t == T - 1 && half == 0 && live) {
