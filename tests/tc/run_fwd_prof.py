@@ -22,11 +22,17 @@ names = ["layer 1 block 0 -> A (first tile only: later tiles at [10])", "layer 1
 buf = (C.c_ulonglong * 16)()
 s = L.cur_stream()
 T, N = tr.T, tr.N
-for which in ("value", "logp"):
+for which in ("value", "logp", "rollout"):
     if which == "value":
         L.call("acx_value_forward_tc", L.ptr(tr.critic), L.ptr(tr.packed_c), tr.ob, T + 1, N, L.ptr(tr.obs_buf), L.ptr(tr.V),
                0, L.ptr(tr.cx2), L.ptr(tr.cx3), L.ptr(tr.cmask), s)
         tiles = (T + 1) * 512 / 148
+    elif which == "rollout":
+        st3, el3 = tr.state.clone(), tr.elapsed.clone()
+        L.call("acx_rollout_tc", tr.env, L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ac_scale, T, N, L.ptr(tr.obs_buf), L.ptr(st3),
+               L.ptr(el3), None, None, tr.seed, 0, None, tr.max_steps, L.ptr(tr.acs), L.ptr(tr.logps), L.ptr(tr.ent),
+               L.ptr(tr.rew), L.ptr(tr.done), L.ptr(tr.ax2), L.ptr(tr.ax3), L.ptr(tr.amask), s)
+        tiles = T * 4          # CTA 0: four column tiles x T steps
     else:
         L.call("acx_policy_logp_gauss_tc", L.ptr(tr.actor), L.ptr(tr.packed_a), tr.ob, tr.num_ac, tr.ac_scale, T, N,
                L.ptr(tr.obs_buf), L.ptr(tr.acs), None, None, None, L.ptr(tr.logps), L.ptr(tr.kl_part),
