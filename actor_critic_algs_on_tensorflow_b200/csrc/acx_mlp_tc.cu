@@ -276,6 +276,12 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         tmem_ld32(tl + TC_D2 + (uint32_t)j0, v);
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] = act_fn<LRELU>(__fadd_rn(v[e], sm.b2[j0 + e]));
+        a_store32(tl, j0, v);
+        tmem_wait_st();
+        fence_before_sync();
+        mbar_arrive(&sm.a_ready[gq]);
+        // everything else this thread does with the 32 values comes AFTER the hand-over: the cache / mask stores and
+        // the Basic_AC head sums then run while the tensor cores form layer 3
         if (A.mask_out != nullptr) {               // act'(X2)
           unsigned int bits = 0u;
 #pragma unroll
@@ -291,10 +297,6 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
 #pragma unroll
           for (int e = 0; e < 32; ++e) pre[0] = fmaf(v[e], sm.Wh[j0 + e], pre[0]);
         }
-        a_store32(tl, j0, v);
-        tmem_wait_st();
-        fence_before_sync();
-        mbar_arrive(&sm.a_ready[gq]);
       }
       FPROF(5);
     };
@@ -481,12 +483,6 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
             v[e] = act_fn<LRELU>(__fadd_rn(acc, sm.b1[k]));
           }
         }
-        if (A.mask_out != nullptr) {             // act'(X1) for the chain kernel
-          unsigned int bits = 0u;
-#pragma unroll
-          for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
-          A.mask_out[mask_tile_off(tile_l, H1) + (size_t)(blk * 4 + gq * 2 + half) * MT + s] = bits;
-        }
         if (blk > 0 && gq == 0) {                // the MMAs reading the previous block must be done
           FPROF(1);
           acx_mbar_wait(reinterpret_cast<uint64_t*>(&sm.stage_done), done & 1u); ++done;
@@ -497,6 +493,12 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         tmem_wait_st();
         fence_before_sync();
         mbar_arrive(&sm.a_ready[gq]);            // features gq*64 .. +63 of the A operand are in place
+        if (A.mask_out != nullptr) {             // act'(X1) for the chain kernel (after the hand-over)
+          unsigned int bits = 0u;
+#pragma unroll
+          for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
+          A.mask_out[mask_tile_off(tile_l, H1) + (size_t)(blk * 4 + gq * 2 + half) * MT + s] = bits;
+        }
       }
       FPROF(blk == 0 ? 0 : 3);
     };
