@@ -337,15 +337,15 @@ __global__ void __launch_bounds__(256) acx_grad_reduce_tc_kernel(const float* __
       const int r = H1 == 256 ? j : k1, c = H1 == 256 ? k1 : j;
       q = offW2 + ((c >> 2) * 128 + r) * 4 + (c & 3);
     }
-    // fixed order cta = 0, 1, ...; the loads of eight rows are issued ahead of the dependent adds
+    // fixed order cta = 0, 1, ...; the loads of sixteen rows are issued ahead of the dependent adds
     float acc = 0.f;
     int cta = 0;
-    for (; cta + 8 <= ncta; cta += 8) {
-      float x[8];
+    for (; cta + 16 <= ncta; cta += 16) {
+      float x[16];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) x[u] = scratch[(size_t)(cta + u) * size + q];
+      for (int u = 0; u < 16; ++u) x[u] = scratch[(size_t)(cta + u) * size + q];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) acc += x[u];
+      for (int u = 0; u < 16; ++u) acc += x[u];
     }
     for (; cta < ncta; ++cta) acc += scratch[(size_t)cta * size + q];
     grad[p] = acc;
