@@ -52,10 +52,14 @@ struct WgBars {
   float b1[256];
 };
 
-template <int H1> struct WgCfg {
+// PH = -1: one kernel runs both phases on one ring geometry; PH = 0 / 1: a kernel of its own per phase, each with the
+// geometry that suits it (the critic: phase 0 moves two operands from HBM per box and is bound by the latency of those
+// loads -- it gets three 2-block stages instead of two 3-block ones; the geometry is a compile-time constant either way).
+template <int H1, int PH> struct WgCfg {
   static constexpr int NB = H1 / 128;
-  static constexpr int STAGE = (NB + 1) * BLK;              // floats: A blocks, then the B box
-  static constexpr int NSTAGE = NB == 1 ? 3 : 2;
+  static constexpr int ABLK = PH == 0 ? 1 : NB;             // 128-row A blocks of a stage
+  static constexpr int STAGE = (ABLK + 1) * BLK;            // floats: A blocks, then the B box
+  static constexpr int NSTAGE = ABLK == 1 ? 3 : 2;
   static constexpr size_t SMEM = (size_t)NSTAGE * STAGE * 2 * sizeof(float) + 1024 + sizeof(WgBars);
 };
 
@@ -70,14 +74,15 @@ __device__ inline float4 lo_of(const float4 x) {
   return make_float4(lo_trunc_tf32(x.x), lo_trunc_tf32(x.y), lo_trunc_tf32(x.z), lo_trunc_tf32(x.w));
 }
 
-template <int H1, int H3, bool LRELU, int OBM>
+template <int H1, int H3, bool LRELU, int OBM, int PH>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constant__ CUtensorMap mapD3,
                  const __grid_constant__ CUtensorMap mapD2, const float* __restrict__ obs,
                  const float* __restrict__ params, int ob, int offW1, int offb1, int rows, int n,
                  float* __restrict__ scratch, int scr_stride, int offW3, int offW2, int offb3, int offb2) {
-  using Cfg = WgCfg<H1>;
-  constexpr int NB = Cfg::NB, NSTAGE = Cfg::NSTAGE;
+  using Cfg = WgCfg<H1, PH>;
+  constexpr int NB = Cfg::NB, NSTAGE = Cfg::NSTAGE, ABLK = Cfg::ABLK;
+  constexpr int PH0 = PH < 0 ? 0 : PH, PH1 = PH < 0 ? 2 : PH + 1;          // the phases this kernel runs
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   // NB: the round trip through uintptr_t drops the address space, so the splitters' accesses to the ring compile to
@@ -116,7 +121,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
   if (warp == 0) {
     if (lane == 0) {
       unsigned int it = 0;
-      for (int phase = 0; phase < 2; ++phase) {
+      for (int phase = PH0; phase < PH1; ++phase) {
         const int brows = phase == 0 ? H3 : 128;
         const CUtensorMap* mB = phase == 0 ? &mapD3 : &mapD2;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -131,7 +136,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             float* dst = raw + (size_t)slot * Cfg::STAGE;
             (void)row;
             if (phase == 0) tma_load_2d(dst, &mapX2, kk * BOX, tile * 128, full);          // phase 1: X1 is generated
-            tma_load_2d(dst + NB * BLK, mB, kk * BOX, tile * brows, full);
+            tma_load_2d(dst + ABLK * BLK, mB, kk * BOX, tile * brows, full);
           }
         }
       }
@@ -143,7 +148,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       long long pt_ = clock64(), pw_ = 0;
       unsigned int pit_ = 0;
 #endif
-      for (int phase = 0; phase < 2; ++phase) {
+      for (int phase = PH0; phase < PH1; ++phase) {
         // phase 1 with two X1 blocks (critic): the roles are swapped -- A = the dPre2 box (128 rows), B = both X1 blocks
         // (256 rows, contiguous under the 128-byte swizzle), ONE N = 256 instruction per split product; the accumulator
         // holds dW2 transposed (lane = j, column = k).  Per K step the tensor core then reads 3 x (4 + 8) KB of shared
@@ -180,7 +185,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             const bool fresh = in_group == 0 && kk == 0;
 #pragma unroll
             for (int ks = 0; ks < BOX / 8; ++ks) {
-              const uint64_t bh = smem_desc_sw128(r + NB * BLK + ks * 8), bl = smem_desc_sw128(l + NB * BLK + ks * 8);
+              const uint64_t bh = smem_desc_sw128(r + ABLK * BLK + ks * 8), bl = smem_desc_sw128(l + ABLK * BLK + ks * 8);
               if (wide) {
                 const uint64_t xh = smem_desc_sw128(r + ks * 8), xl = smem_desc_sw128(l + ks * 8);
                 mma_tf32(dbase, bl, xh, idesc, !(fresh && ks == 0));
@@ -275,7 +280,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
                    ? __ldg(reinterpret_cast<const float4*>(obs + ((size_t)row * ob + i) * n + col))
                    : make_float4(0.f, 0.f, 0.f, 0.f);
     };
-    for (int phase = 0; phase < 2; ++phase) {
+    for (int phase = PH0; phase < PH1; ++phase) {
       const int brows = phase == 0 ? H3 : 128;
       float bacc[4] = {0.f, 0.f, 0.f, 0.f};       // bias-gradient partials of rows r0 + 32 m (chunk c4 of every box)
       float4 o[OBM], o_next[OBM];
@@ -336,7 +341,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
 #pragma unroll
           for (int m = 0; m < 4; ++m)
             if (r0 + 32 * m < brows) {
-              const int idx = NB * (BLK / 4) + (r0 + 32 * m) * 8 + c4;
+              const int idx = ABLK * (BLK / 4) + (r0 + 32 * m) * 8 + c4;
               const float4 x = r4[idx];
               l4[idx] = lo_of(x);
               bacc[m] += (x.x + x.y) + (x.z + x.w);
@@ -383,6 +388,17 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
+template <int H1, int H3, bool LRELU, int OBM, int PH>
+int launch_wgrad_ph(const AcxWgradArgs& a, const CUtensorMap& mX2, const CUtensorMap& mD3, const CUtensorMap& mD2,
+                    cudaStream_t st) {
+  auto kern = acx_wgrad_kernel<H1, H3, LRELU, OBM, PH>;
+  ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgCfg<H1, PH>::SMEM));
+  kern<<<a.grid, WG_THREADS, WgCfg<H1, PH>::SMEM, st>>>(mX2, mD3, mD2, a.obs, a.params, a.ob, a.offW1, a.offb1, a.rows,
+                                                       a.n, a.scratch, a.scr_stride, a.offW3, a.offW2, a.offb3, a.offb2);
+  ACX_LAUNCH_OK("acx_wgrad_kernel");
+  return ACX_OK;
+}
+
 template <int H1, int H3, bool LRELU, int OBM>
 int launch_wgrad(const AcxWgradArgs& a, cudaStream_t st) {
   CUtensorMap mX2, mD3, mD2;
@@ -392,12 +408,9 @@ int launch_wgrad(const AcxWgradArgs& a, cudaStream_t st) {
   if (!rc) rc = acx_tmap_2d(&mD3, a.d3, 128, tiles * H3, 512, BOX, H3);
   if (!rc) rc = acx_tmap_2d(&mD2, a.d2, 128, tiles * 128, 512, BOX, 128);
   ACX_REQUIRE(rc == 0, "acx_wgrad: cuTensorMapEncodeTiled failed (%d) for rows=%d n=%d", rc, a.rows, a.n);
-  auto kern = acx_wgrad_kernel<H1, H3, LRELU, OBM>;
-  ACX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgCfg<H1>::SMEM));
-  kern<<<a.grid, WG_THREADS, WgCfg<H1>::SMEM, st>>>(mX2, mD3, mD2, a.obs, a.params, a.ob, a.offW1, a.offb1, a.rows, a.n,
-                                                    a.scratch, a.scr_stride, a.offW3, a.offW2, a.offb3, a.offb2);
-  ACX_LAUNCH_OK("acx_wgrad_kernel");
-  return ACX_OK;
+  rc = launch_wgrad_ph<H1, H3, LRELU, OBM, 0>(a, mX2, mD3, mD2, st);                        // dW3, db3
+  if (rc) return rc;
+  return launch_wgrad_ph<H1, H3, LRELU, OBM, 1>(a, mX2, mD3, mD2, st);                      // dW2, db2
 }
 
 }  // namespace
