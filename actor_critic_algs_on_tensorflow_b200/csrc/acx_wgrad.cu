@@ -84,11 +84,10 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
   constexpr int NB = Cfg::NB, NSTAGE = Cfg::NSTAGE, ABLK = Cfg::ABLK;
   constexpr int PH0 = PH < 0 ? 0 : PH, PH1 = PH < 0 ? 2 : PH + 1;          // the phases this kernel runs
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  // NB: the round trip through uintptr_t drops the address space, so the splitters' accesses to the ring compile to
-  // generic LD / ST instead of LDS / STS.  Measured both ways (make prof): with LDS / STS the dW2 phase is SLOWER
-  // (critic 3,600 -> 4,040, actor 2,620 -> 3,220 cycles per box; the dW3 phase unchanged) -- the 16-byte stores of a
-  // whole X1 box then queue in the MIO pipe in front of the mbarrier operations; the generic path has its own queue.
+  // 1024-byte alignment for the swizzled boxes as an offset added to the __shared__ array: a round trip through
+  // uintptr_t loses the address space and every ring access becomes a generic LD / ST.  (In the two-phase kernel, which
+  // spilled, the generic path measured FASTER; in the per-phase kernels LDS / STS win: step 5.64 -> 5.54 ms.)
+  unsigned char* base = smem_raw + ((1024u - (acx_smem_u32(smem_raw) & 1023u)) & 1023u);
   float* raw = reinterpret_cast<float*>(base);                         // [NSTAGE][STAGE]
   float* lo = raw + (size_t)NSTAGE * Cfg::STAGE;                       // [NSTAGE][STAGE]
   WgBars& B = *reinterpret_cast<WgBars*>(lo + (size_t)NSTAGE * Cfg::STAGE);
