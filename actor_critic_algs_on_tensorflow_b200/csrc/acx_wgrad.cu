@@ -271,11 +271,12 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
     };
     auto flush = [&]() { while (!flush_slice()) {} };
     // observations of this thread's 4 samples of box (tile, kk); zeros beyond the batch
-    auto load_obs = [&](int tile, int kk, float4 (&o)[OBM]) {
-      const int row = tile / tpr, col = (tile % tpr) * 128 + kk * BOX + 4 * c4;
+    // (row, n0) of the tile come from the caller: one division per tile, not one per box
+    auto load_obs = [&](bool tile_ok, int row, int n0, int kk, float4 (&o)[OBM]) {
+      const int col = n0 + kk * BOX + 4 * c4;
 #pragma unroll
       for (int i = 0; i < OBM; ++i)
-        o[i] = (i < ob && tile < ntiles && col < n)
+        o[i] = (i < ob && tile_ok && col < n)
                    ? __ldg(reinterpret_cast<const float4*>(obs + ((size_t)row * ob + i) * n + col))
                    : make_float4(0.f, 0.f, 0.f, 0.f);
     };
@@ -287,11 +288,12 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       const bool sprof_ = blockIdx.x == 0 && tid == 64 + 128;
       long long sp_[5] = {0, 0, 0, 0, 0}, sl_ = clock64();
 #endif
-      if (phase == 1) load_obs(blockIdx.x, 0, o_next);
+      if (phase == 1) load_obs((int)blockIdx.x < ntiles, (int)blockIdx.x / tpr, ((int)blockIdx.x % tpr) * 128, 0, o_next);
       int in_group = 0, groups_done = 0;          // within this phase
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int n0 = (tile % tpr) * 128;
         const int nsub = (min(128, n - n0) + BOX - 1) / BOX;
+        const int trow = tile / tpr, nxt = tile + (int)gridDim.x, nrow = nxt / tpr, nn0 = (nxt % tpr) * 128;
         for (int kk = 0; kk < nsub; ++kk, ++it) {
           const unsigned int slot = it % NSTAGE;
           float4* r4 = reinterpret_cast<float4*>(raw + (size_t)slot * Cfg::STAGE);
@@ -301,7 +303,7 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
             // Needs no loaded data, only the slot: start as soon as the MMAs that read it last are done.
 #pragma unroll
             for (int i = 0; i < OBM; ++i) o[i] = o_next[i];
-            if (kk + 1 < nsub) load_obs(tile, kk + 1, o_next); else load_obs(tile + gridDim.x, 0, o_next);
+            if (kk + 1 < nsub) load_obs(true, trow, n0, kk + 1, o_next); else load_obs(nxt < ntiles, nrow, nn0, 0, o_next);
             WG_SPLIT_MARK(4);
             if (it >= (unsigned)NSTAGE)
               acx_mbar_wait(reinterpret_cast<uint64_t*>(&B.empty[slot]), ((it / NSTAGE) - 1u) & 1u);
