@@ -264,7 +264,7 @@ class A2CTrainer:
             else:
                 L.call("acx_loss_backward_cat_tc", *head, self.n_act, T, N, *cached)
             split = self.N % 4 == 0
-            return 2 + (6 if split else 4)      # value, scan, 2 x (mlp train, [weight gradients,] grad reduce)
+            return 2 + (8 if split else 4)      # value, scan, 2 x (chain, dW3 kernel, dW2 kernel, grad reduce | train, reduce)
         if self.cache:
             cached = common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3)) + common[-3:]
             if self.cont:
