@@ -1,4 +1,5 @@
-// Weight-gradient products of K4 on the tensor cores (tcgen05, 3xTF32), one launch per network:
+// Weight-gradient products of K4 on the tensor cores (tcgen05, 3xTF32), one launch per network and PHASE (template
+// parameter PH: 0 = dW3 / db3, 1 = dW2 / db2, each with its own compile-time ring geometry; -1 = both in one launch):
 //     dW3[k][j] = sum_s X2[k][s] * dPre3[j][s]          (A3C/policies.py:82,155: compute_gradients of the
 //     dW2[k][j] = sum_s X1[k][s] * dPre2[j][s]           third / second dense layer's kernel and bias)
 //     db3[j] = sum_s dPre3[j][s],   db2[j] = sum_s dPre2[j][s]
@@ -11,7 +12,7 @@
 // operands, tests/tc/run_wgrad_accuracy.py).  So the accumulators are double-buffered and flushed every WG_FLUSH
 // tiles: while the MMAs fill one buffer, warps 2-5 add the other into the CTA's scratch row with ordinary fp32
 // (round-to-nearest) adds; acx_grad_reduce then sums the rows in fixed order (bit-reproducible run to run).
-//   warp 0     producer: TMA tensor loads of [features x 32 samples] boxes, 128-byte swizzle, NSTAGE-deep ring
+//   warp 0     producer: TMA tensor loads of [features x 32 samples] boxes, 128-byte swizzle, 2- or 3-deep ring (WgCfg)
 //   warp 1     issuer:   per box 4 K-steps x 3 kind::tf32 MMAs (lo*hi, hi*lo, hi*hi) per 128-row block
 //   warps 2-9  splitters: lo = rna(x - trunc(x)) of every landed word into the stage's second buffer (the MMA itself
 //              ignores the low 13 mantissa bits of the raw word, which therefore serves as hi); they also generate the
