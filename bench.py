@@ -423,7 +423,7 @@ def run_ours(args, rank, local_rank, world):
             .acx_loss_backward_workspace_bytes(tr.ob, tr.num_ac, int(tr.cont))
         if getattr(tr, "tc_bwd", False) and tr.ws_bwd_bytes > base_bytes_:
             dom_name = "loss_backward_critic_tc, chain + wgrad kernels (K4, tcgen05 3xTF32)"
-            dom_kernel = ("acx_mlp_tc_chain_kernel<critic> + acx_wgrad_kernel<critic> (fused loss+backward on "
+            dom_kernel = ("acx_mlp_tc_chain_kernel<critic> + acx_wgrad_kernel<critic, dW3> + <critic, dW2> (fused loss+backward on "
                           "cached activations, K4)")
             note = "every product of the pair runs on tcgen05 as 3xTF32"
         elif getattr(tr, "tc_bwd", False):
@@ -450,12 +450,12 @@ def run_ours(args, rank, local_rank, world):
                     "frac_of_fp32_ffma_peak": dom["achieved"] / FP32_PEAK_TFLOPS,
                     "share_of_step": dom["ms"] / step_ms,
                     # dram__bytes_read.sum + dram__bytes_write.sum of the two kernels, one ncu --set full capture of this
-                    # workload (profiles/r01_ncu_tc_backward.md): chain 0.756 + 1.289 GB, wgrad 2.186 + 0.212 GB
-                    "traffic": 4.443e9 if (N_ENVS, HORIZON) == (65536, 20) else None, "traffic_unit": "bytes per launch",
+                    # workload (profiles/r01_ncu_tc_backward.md): chain 0.756 + 1.289 GB, the two wgrad kernels 2.177 + 0.197 GB
+                    "traffic": 4.419e9 if (N_ENVS, HORIZON) == (65536, 20) else None, "traffic_unit": "bytes per launch",
                     "algorithmic_bytes": 4.09e9 if (N_ENVS, HORIZON) == (65536, 20) else None,
                     # the same capture: sm__pipe_tc_cycles_active (the MMA instruction rate measured by
                     # tests/tc/run_mma_rate.py, 2,007 MAC/clk/SM, is above measured-bf16 / 2, so `frac` flatters the pipe)
-                    "tensor_pipe_active_ncu": {"chain": 0.370, "wgrad": 0.432},
+                    "tensor_pipe_active_ncu": {"chain": 0.370, "wgrad": 0.556},
                     "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
         else:
             roof = {"kernel": dom_kernel, "bound": "fp32",
