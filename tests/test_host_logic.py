@@ -113,3 +113,21 @@ def test_world_size_2_update_logic_gloo():
     np.testing.assert_allclose(s0, want, rtol=1e-6, atol=1e-7)
     # async: both workers' first Adam steps (lr * sign(g)) land on the shared parameters
     np.testing.assert_allclose(a0 - theta0, -0.005 * (np.sign(g0) + np.sign(g1)), rtol=1e-3, atol=1e-6)
+
+
+def test_bench_workload_flop_constants_match_the_network_shapes():
+    """bench.py quotes algorithmic FLOPs per sample (2 per MAC) for its workloads: they must follow from the layer shapes
+    of A3C/policies.py:44-50,63,146-150 at each env's observation / action sizes."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(os.path.dirname(__file__), "..", "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    shapes = {"pendulum": (3, 1), "cartpole": (4, 2)}
+    for name, (ob, nout) in shapes.items():
+        w = bench.WORKLOADS[name]
+        assert w["flop_actor"] == 2 * (ob * 128 + 128 * 128 + 128 * 64 + 64 * nout)
+        assert w["flop_critic"] == 2 * (ob * 256 + 256 * 128 + 128 * 128 + 128 * 1)
+        assert w["horizon"] == 20
+    assert bench.WORKLOADS["pendulum"]["n_envs"] == 65536 and bench.WORKLOADS["cartpole"]["n_envs"] == 262144
+    assert (bench.FLOP_ACTOR_FWD, bench.FLOP_CRITIC_FWD) == (50048.0, 100096.0)
