@@ -18,7 +18,8 @@ SCAN_STATIC_MAX_COLUMNS = 131072
 (OPT_ACTOR_LR, OPT_CRITIC_LR, OPT_BETA_KL, OPT_GAMMA_ENT, OPT_BETA1_POW, OPT_BETA2_POW, OPT_CLIP, OPT_DESIRED_KL,
  OPT_MIN_LR, OPT_MAX_LR, OPT_ITER, OPT_SCHEDULE, OPT_ADAM_T) = range(13)
 (STAT_ADV_MEAN, STAT_ADV_INV_STD, STAT_ADV_STD, STAT_ACTOR_LOSS, STAT_CRITIC_LOSS, STAT_KL_PRE, STAT_ENT_MEAN,
- STAT_KL_POST, STAT_REW_LOSS, STAT_ACTOR_LR_USED) = range(10)
+ STAT_KL_POST, STAT_REW_LOSS, STAT_ACTOR_LR_USED, STAT_EV_BEFORE, STAT_EV_AFTER, STAT_EP_REW_MEAN,
+ STAT_EP_COUNT) = range(14)
 
 
 class AcxError(RuntimeError):
@@ -79,6 +80,11 @@ SIGNATURES = {
     "acx_returns_adv_workspace_bytes": (_sz, [_i, _i]),
     "acx_returns_adv_scan": (_i, [_i, _i, _p, _p, _p, _d, _i, _p, _p, _p, _p, _sz, _i, _p]),
     "acx_returns_adv_scan_static": (_i, [_i, _i, _p, _p, _p, _d, _i, _p, _p, _p, _i, _p]),
+    "acx_diag_workspace_bytes": (_sz, []),
+    "acx_episode_returns": (_i, [_i, _i, _p, _p, _p, _p, _p, _sz, _p]),
+    "acx_explained_variance": (_i, [C.c_longlong, _p, _p, _p, _p, _sz, _p]),
+    "acx_log_push": (_i, [_p, _i, _p, _p, _p]),
+    "acx_env_stagger": (_i, [_i, _i, _p, _u64, _u64, _i, _p]),
     "acx_loss_backward_workspace_bytes": (_sz, [_i, _i, _i]),
     "acx_loss_backward_gauss": (_i, [_p, _p, _i, _i, _f, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "acx_loss_backward_cat": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
@@ -89,6 +95,7 @@ SIGNATURES = {
     "acx_counter_add": (_i, [_p, _u32, _p]),
     "acx_kl_finalize": (_i, [_p, _i, _d, _p, _p]),
     "acx_kl_lr_update": (_i, [_p, _p, _p]),
+    "acx_kl_lr_update_split": (_i, [_p, _p, _p, _f, _i, _p]),
 }
 
 _lib = None

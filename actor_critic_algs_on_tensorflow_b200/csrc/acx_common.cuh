@@ -153,11 +153,26 @@ __device__ inline bool acx_mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// bounded wait: a protocol bug traps (launch error) instead of hanging the GPU
+// bounded wait: a protocol bug traps (launch error) instead of hanging the GPU.  The bound is wall time
+// (%globaltimer, ns), not a poll count: under ncu replay, compute-sanitizer or a throttled clock a legitimate
+// wait can outlast any fixed number of polls, and a trap is sticky for the whole CUDA context.
+#ifndef ACX_MBAR_TIMEOUT_NS
+#define ACX_MBAR_TIMEOUT_NS 20000000000ull      // 20 s
+#endif
+__device__ inline uint64_t acx_globaltimer() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ inline void acx_mbar_wait(uint64_t* bar, uint32_t parity) {
-  for (uint32_t spin = 0; spin < (1u << 24); ++spin)
+  for (uint32_t spin = 0; spin < (1u << 16); ++spin)
     if (acx_mbar_try_wait(bar, parity)) return;
-  __trap();
+  const uint64_t t0 = acx_globaltimer();          // slow path only: the common case never reads the timer
+  for (;;) {
+    for (uint32_t spin = 0; spin < (1u << 12); ++spin)
+      if (acx_mbar_try_wait(bar, parity)) return;
+    if (acx_globaltimer() - t0 > ACX_MBAR_TIMEOUT_NS) __trap();
+  }
 }
 // 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier (TMA engine)
 __device__ inline void acx_bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
@@ -176,5 +191,72 @@ __device__ inline double acx_warp_sum_d(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
+}
+
+// ------------------------------------------------------------------ grid-wide sums without atomics on the data
+// Every block leaves its K partial sums in ws->partial[K * blockIdx.x ..]; the block that takes the last ticket folds
+// them (thread j takes blocks j, j + blockDim, ... in index order, then a fixed butterfly and a fixed walk over the
+// warps): the result depends on the grid size only, never on block timing, and the fold is a handful of dependent
+// L2 reads long.  Returns true in thread 0 of that last block, with the totals in tot[]; the ticket is back at zero
+// when it does.  blockDim.x: a multiple of 32, at most 256.  ws: 16-byte aligned, ticket zero before the first use.
+struct AcxFoldWs {
+  unsigned int ticket;
+  unsigned int pad[3];
+  double partial[1];         // [K * gridDim.x]
+};
+template <int K>
+__device__ inline bool acx_fold_blocks(const double (&m)[K], AcxFoldWs* ws, double (&tot)[K]) {
+  __shared__ double sh[K][8];
+  __shared__ bool last;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (int)(blockDim.x >> 5);
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const double r = acx_warp_sum_d(m[k]);
+    if (l == 0) sh[k][w] = r;
+  }
+  __syncthreads();
+  if (threadIdx.x < K) {
+    double a = 0;
+    for (int i = 0; i < nw; ++i) a += sh[threadIdx.x][i];
+    ws->partial[(size_t)K * blockIdx.x + threadIdx.x] = a;
+    __threadfence();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) last = (atomicAdd(&ws->ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!last) return false;
+  __threadfence();
+  double a[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) a[k] = 0;
+  for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) a[k] += ((volatile double*)ws->partial)[(size_t)K * i + k];
+  }
+  __syncthreads();           // sh[] is reused
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const double r = acx_warp_sum_d(a[k]);
+    if (l == 0) sh[k][w] = r;
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return false;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    tot[k] = 0;
+    for (int i = 0; i < nw; ++i) tot[k] += sh[k][i];
+  }
+  ws->ticket = 0;
+  return true;
+}
+
+// np.mean(((x - mean x) / std x) * ((y - mean y) / std y)) from the five raw sums over c samples -- var_accounted_for,
+// A3C/util.py:5-13 (population std; nan for a constant input, like numpy's 0/0)
+__device__ inline double acx_corr_from_sums(double sx, double sxx, double sy, double syy, double sxy, double c) {
+  const double mx = sx / c, my = sy / c;
+  double vx = sxx / c - mx * mx, vy = syy / c - my * my;
+  if (vx < 0) vx = 0;
+  if (vy < 0) vy = 0;
+  return (sxy / c - mx * my) / (sqrt(vx) * sqrt(vy));
 }
 #endif  // __CUDACC__

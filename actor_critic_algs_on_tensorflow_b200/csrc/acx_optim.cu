@@ -138,19 +138,26 @@ __device__ inline double lin_sched(double t, double init_t, double end_t, double
   return ((t - init_t) * end_v + (end_t - t) * init_v) / (end_t - init_t);
 }
 
-__global__ void acx_kl_lr_kernel(float* opt, float* stats) {
+// flags & 1: the lr rule; flags & 2: the schedules + the iteration counter.  kl_sum != NULL: the KL the rule sees is
+// *kl_sum * kl_scale (a cross-rank sum that rode along with the gradient all-reduce) and is left in stats[KL_POST].
+__global__ void acx_kl_lr_kernel(float* opt, float* stats, const float* kl_sum, float kl_scale, int flags) {
   if (threadIdx.x == 0 && blockIdx.x == 0) {
-    const double kl = (double)stats[ACX_STAT_KL_POST], want = (double)opt[ACX_OPT_DESIRED_KL];
-    const double lr = (double)opt[ACX_OPT_ACTOR_LR];
-    stats[ACX_STAT_ACTOR_LR_USED] = (float)lr;
-    if (kl < want / 4.0) opt[ACX_OPT_ACTOR_LR] = (float)fmin((double)opt[ACX_OPT_MAX_LR], lr * 1.5);
-    else if (kl > want * 4.0) opt[ACX_OPT_ACTOR_LR] = (float)fmax((double)opt[ACX_OPT_MIN_LR], lr / 1.5);
-    const int it = (int)opt[ACX_OPT_ITER];
-    if (opt[ACX_OPT_SCHEDULE] != 0.f && it % 100 == 0) {          // A3C/process.py:173-174,271-278
-      opt[ACX_OPT_GAMMA_ENT] = (float)pow(10.0, lin_sched((double)it, 100.0, 3000.0, -2.0, -8.0));
-      opt[ACX_OPT_BETA_KL] = (float)pow(10.0, lin_sched((double)it, 100.0, 3000.0, 0.0, -4.0));
+    if (flags & 1) {
+      if (kl_sum != nullptr) stats[ACX_STAT_KL_POST] = __fmul_rn(*kl_sum, kl_scale);
+      const double kl = (double)stats[ACX_STAT_KL_POST], want = (double)opt[ACX_OPT_DESIRED_KL];
+      const double lr = (double)opt[ACX_OPT_ACTOR_LR];
+      stats[ACX_STAT_ACTOR_LR_USED] = (float)lr;
+      if (kl < want / 4.0) opt[ACX_OPT_ACTOR_LR] = (float)fmin((double)opt[ACX_OPT_MAX_LR], lr * 1.5);
+      else if (kl > want * 4.0) opt[ACX_OPT_ACTOR_LR] = (float)fmax((double)opt[ACX_OPT_MIN_LR], lr / 1.5);
     }
-    opt[ACX_OPT_ITER] = (float)(it + 1);
+    if (flags & 2) {
+      const int it = (int)opt[ACX_OPT_ITER];
+      if (opt[ACX_OPT_SCHEDULE] != 0.f && it % 100 == 0) {          // A3C/process.py:173-174,271-278
+        opt[ACX_OPT_GAMMA_ENT] = (float)pow(10.0, lin_sched((double)it, 100.0, 3000.0, -2.0, -8.0));
+        opt[ACX_OPT_BETA_KL] = (float)pow(10.0, lin_sched((double)it, 100.0, 3000.0, 0.0, -4.0));
+      }
+      opt[ACX_OPT_ITER] = (float)(it + 1);
+    }
   }
 }
 
@@ -215,7 +222,17 @@ extern "C" int acx_kl_finalize(const double* kl_partial, int kl_blocks, double c
 
 extern "C" int acx_kl_lr_update(float* opt, float* stats, void* stream) {
   ACX_REQUIRE(opt && stats, "acx_kl_lr_update: null buffer");
-  acx_kl_lr_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(opt, stats);
+  acx_kl_lr_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(opt, stats, nullptr, 1.f, 3);
+  ACX_LAUNCH_OK("acx_kl_lr_kernel");
+  return ACX_OK;
+}
+
+extern "C" int acx_kl_lr_update_split(float* opt, float* stats, const float* kl_sum, float kl_scale, int flags,
+                                      void* stream) {
+  ACX_REQUIRE(opt && stats, "acx_kl_lr_update_split: null buffer");
+  ACX_REQUIRE(flags >= 1 && flags <= 3, "acx_kl_lr_update_split: flags must be 1 (lr rule), 2 (schedules) or 3 (got %d)",
+              flags);
+  acx_kl_lr_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(opt, stats, kl_sum, kl_scale, flags);
   ACX_LAUNCH_OK("acx_kl_lr_kernel");
   return ACX_OK;
 }

@@ -19,48 +19,37 @@
 //                            time with shuffles -- for few, long columns (the reference's own
 //                            shape: 1 env x ~1200 steps).
 // Recurrences run in fp64 like the reference's numpy code.
+#include <mutex>
+
 #include "acx_common.cuh"
 
-struct ScanWs {              // caller-provided workspace, see acx_returns_adv_workspace_bytes
-  unsigned int ticket;       // self-resetting "last block" counter (must be 0 before the first call)
-  unsigned int pad[3];
-  double partial[1];         // [2 * grid]
-};
+// per-block partial sums kept for the batch statistics: adv, adv^2 (advantage normalisation, A3C/process.py:247) and
+// G, G^2, V, V^2, G*V over the T x N samples (ev_before = var_accounted_for(target = G, pred = V), A3C/util.py:5-13,
+// A3C/process.py:111-116)
+constexpr int SCAN_NMOM = 7;
+constexpr int SCAN_MAX_BLOCKS = 2048;      // grid cap == partial[] capacity of acx_returns_adv_workspace_bytes()
+typedef AcxFoldWs ScanWs;    // caller-provided workspace, see acx_returns_adv_workspace_bytes
 
-__device__ inline void scan_finish_moments(double s, double q, ScanWs* ws, float* stats, long long count) {
-  // block reduce (fixed order) -> partials -> last block folds them in index order: deterministic
-  __shared__ double sh[2][8];
-  __shared__ bool last;
-  s = acx_warp_sum_d(s);
-  q = acx_warp_sum_d(q);
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  if (l == 0) { sh[0][w] = s; sh[1][w] = q; }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double a = 0, b = 0;
-    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { a += sh[0][i]; b += sh[1][i]; }
-    ws->partial[2 * blockIdx.x] = a;
-    ws->partial[2 * blockIdx.x + 1] = b;
-    __threadfence();
-    last = (atomicAdd(&ws->ticket, 1u) == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (last && threadIdx.x == 0) {
-    __threadfence();
-    double a = 0, b = 0;
-    for (unsigned i = 0; i < gridDim.x; ++i) {
-      a += ((volatile double*)ws->partial)[2 * i];
-      b += ((volatile double*)ws->partial)[2 * i + 1];
-    }
-    const double mean = a / (double)count;
-    double var = b / (double)count - mean * mean;
-    if (var < 0) var = 0;
-    stats[0] = (float)mean;
-    stats[1] = (float)(1.0 / (1e-8 + sqrt(var)));      // A3C/process.py:247
-    stats[2] = (float)sqrt(var);
-    ws->ticket = 0;
-  }
+__device__ inline void scan_finish_moments(const double (&m)[SCAN_NMOM], ScanWs* ws, float* stats, long long count) {
+  double t[SCAN_NMOM];
+  if (!acx_fold_blocks<SCAN_NMOM>(m, ws, t)) return;
+  const double c = (double)count;
+  const double mean = t[0] / c;
+  double var = t[1] / c - mean * mean;
+  if (var < 0) var = 0;
+  stats[ACX_STAT_ADV_MEAN] = (float)mean;
+  stats[ACX_STAT_ADV_INV_STD] = (float)(1.0 / (1e-8 + sqrt(var)));      // A3C/process.py:247
+  stats[ACX_STAT_ADV_STD] = (float)sqrt(var);
+  stats[ACX_STAT_EV_BEFORE] = (float)acx_corr_from_sums(t[2], t[3], t[4], t[5], t[6], c);
 }
+
+// the seven running sums of one sample
+#define SCAN_ACC(m, a, g, v)                                                         \
+  do {                                                                               \
+    const double a__ = (double)(a), g__ = (double)(g), v__ = (double)(v);            \
+    m[0] += a__; m[1] += a__ * a__; m[2] += g__; m[3] += g__ * g__; m[4] += v__;     \
+    m[5] += v__ * v__; m[6] += g__ * v__;                                            \
+  } while (0)
 
 constexpr int SCAN_CHUNK = 8;
 
@@ -69,7 +58,7 @@ __global__ void __launch_bounds__(256) acx_scan_cols_kernel(int T, int N, const 
                                                             const float* __restrict__ V, double gamma, int L,
                                                             float* __restrict__ G, float* __restrict__ adv,
                                                             ScanWs* ws, float* __restrict__ stats) {
-  double msum = 0, msq = 0;
+  double m[SCAN_NMOM] = {0, 0, 0, 0, 0, 0, 0};
   const double gL = pow(gamma, (double)L);
   for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
     const bool windowed = T > L;
@@ -100,7 +89,7 @@ __global__ void __launch_bounds__(256) acx_scan_cols_kernel(int T, int N, const 
             boot = 0.0;
             const float g = (float)carry, a = (float)(carry - (double)v[i]);
             G[off] = g; adv[off] = a;
-            msum += (double)a; msq += (double)a * (double)a;
+            SCAN_ACC(m, a, g, v[i]);
           } else {
             carry = (double)r[i] + gamma * carry;
             G[off] = (float)carry;
@@ -121,23 +110,28 @@ __global__ void __launch_bounds__(256) acx_scan_cols_kernel(int T, int N, const 
           const bool terminal = done[(size_t)(et - 1) * N + n] != 0;
           if (!terminal) g += pow(gamma, (double)(et - t)) * (double)V[(size_t)et * N + n];
         }
-        const float a = (float)(g - (double)V[off]);
+        const float vt = V[off];
+        const float a = (float)(g - (double)vt);
         G[off] = (float)g; adv[off] = a;
-        msum += (double)a; msq += (double)a * (double)a;
+        SCAN_ACC(m, a, (float)g, vt);
       }
     }
   }
-  scan_finish_moments(msum, msq, ws, stats, (long long)T * N);
+  scan_finish_moments(m, ws, stats, (long long)T * N);
 }
 
 // Plain (T <= L) column scan, four adjacent env columns per thread: every row access of a warp is one
 // 512-byte burst (float4 rew / V / G / adv, uchar4 done).  Same arithmetic as acx_scan_cols_kernel.
-__global__ void __launch_bounds__(256) acx_scan_cols4_kernel(int T, int N, const float* __restrict__ rew,
-                                                             const unsigned char* __restrict__ done,
-                                                             const float* __restrict__ V, double gamma,
-                                                             float* __restrict__ G, float* __restrict__ adv,
-                                                             ScanWs* ws, float* __restrict__ stats) {
-  double msum = 0, msq = 0;
+// CHUNK rows are loaded before the first is used.  <4, 256>: wide batches (>= 2 CTAs per SM at 4 columns per thread);
+// <10, 64>: narrow ones (65,536 columns = 16,384 threads), where small CTAs spread the columns over every SM and the
+// deep chunk puts half of a 20-row column's loads in flight at once -- the kernel is latency-bound there.
+template <int CHUNK, int BLOCK>
+__global__ void __launch_bounds__(BLOCK) acx_scan_cols4_kernel(int T, int N, const float* __restrict__ rew,
+                                                               const unsigned char* __restrict__ done,
+                                                               const float* __restrict__ V, double gamma,
+                                                               float* __restrict__ G, float* __restrict__ adv,
+                                                               ScanWs* ws, float* __restrict__ stats) {
+  double m[SCAN_NMOM] = {0, 0, 0, 0, 0, 0, 0};
   const int N4 = N >> 2;
   for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < N4; q += gridDim.x * blockDim.x) {
     const int n = q << 2;
@@ -147,12 +141,12 @@ __global__ void __launch_bounds__(256) acx_scan_cols4_kernel(int T, int N, const
     const float gf = (float)gamma, glo = (float)(gamma - (double)(float)gamma);   // gamma = gf + glo to ~2^-48
     float carry[4] = {0.f, 0.f, 0.f, 0.f};
     float boot[4] = {vT.x, vT.y, vT.z, vT.w};
-    for (int t1 = T; t1 > 0; t1 -= 4) {
-      const int cnt = t1 < 4 ? t1 : 4;
-      float4 r[4], v[4];
-      uchar4 d[4];
+    for (int t1 = T; t1 > 0; t1 -= CHUNK) {
+      const int cnt = t1 < CHUNK ? t1 : CHUNK;
+      float4 r[CHUNK], v[CHUNK];
+      uchar4 d[CHUNK];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < CHUNK; ++i)
         if (i < cnt) {
           const size_t off = (size_t)(t1 - 1 - i) * N + n;
           r[i] = __ldg(reinterpret_cast<const float4*>(rew + off));
@@ -160,12 +154,13 @@ __global__ void __launch_bounds__(256) acx_scan_cols4_kernel(int T, int N, const
           d[i] = __ldg(reinterpret_cast<const uchar4*>(done + off));
         }
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < CHUNK; ++i)
         if (i < cnt) {
           const size_t off = (size_t)(t1 - 1 - i) * N + n;
           const float rr[4] = {r[i].x, r[i].y, r[i].z, r[i].w}, vv[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
           const unsigned char dd[4] = {d[i].x, d[i].y, d[i].z, d[i].w};
-          float g[4], a[4], rs = 0.f, rq = 0.f;
+          float g[4], a[4];
+          float p[SCAN_NMOM] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};      // this row's four columns, fp32
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             if (dd[c]) { carry[c] = 0.f; boot[c] = 0.f; }
@@ -174,15 +169,19 @@ __global__ void __launch_bounds__(256) acx_scan_cols4_kernel(int T, int N, const
             boot[c] = 0.f;
             g[c] = carry[c];
             a[c] = carry[c] - vv[c];
-            rs += a[c]; rq = fmaf(a[c], a[c], rq);
+            p[0] += a[c]; p[1] = fmaf(a[c], a[c], p[1]);
+            p[2] += g[c]; p[3] = fmaf(g[c], g[c], p[3]);
+            p[4] += vv[c]; p[5] = fmaf(vv[c], vv[c], p[5]);
+            p[6] = fmaf(g[c], vv[c], p[6]);
           }
-          msum += (double)rs; msq += (double)rq;
+#pragma unroll
+          for (int k = 0; k < SCAN_NMOM; ++k) m[k] += (double)p[k];
           *reinterpret_cast<float4*>(G + off) = make_float4(g[0], g[1], g[2], g[3]);
           *reinterpret_cast<float4*>(adv + off) = make_float4(a[0], a[1], a[2], a[3]);
         }
     }
   }
-  scan_finish_moments(msum, msq, ws, stats, (long long)T * N);
+  scan_finish_moments(m, ws, stats, (long long)T * N);
 }
 
 // affine element of the reverse recurrence x_t = b + a * x_{t+1}; `e` rides along as a min-scan
@@ -199,7 +198,7 @@ __global__ void __launch_bounds__(256) acx_scan_warp_kernel(int T, int N, const 
                                                             ScanWs* ws, float* __restrict__ stats) {
   const int lane = threadIdx.x & 31;
   const int warps_per_block = blockDim.x >> 5;
-  double msum = 0, msq = 0;
+  double m[SCAN_NMOM] = {0, 0, 0, 0, 0, 0, 0};
   const double gL = pow(gamma, (double)L);
   const bool windowed = T > L;
   for (int n = blockIdx.x * warps_per_block + (threadIdx.x >> 5); n < N; n += gridDim.x * warps_per_block) {
@@ -232,7 +231,7 @@ __global__ void __launch_bounds__(256) acx_scan_warp_kernel(int T, int N, const 
         if (!windowed) {
           const float a = (float)(val - (double)v);
           G[off] = (float)val; adv[off] = a;
-          msum += (double)a; msq += (double)a * (double)a;
+          SCAN_ACC(m, a, (float)val, v);
         } else {
           G[off] = (float)val;
           reinterpret_cast<int*>(adv)[off] = e;
@@ -249,7 +248,7 @@ __global__ void __launch_bounds__(256) acx_scan_warp_kernel(int T, int N, const 
       // S_{t+L} must be read for the whole 32-step block before any slot of it is rewritten
       for (int lo = 0; lo < T; lo += 32) {
         const int t = lo + lane;
-        double g = 0; float a = 0; bool live = t < T;
+        double g = 0; float a = 0, vt = 0; bool live = t < T;
         if (live) {
           const size_t off = (size_t)t * N + n;
           const int et = reinterpret_cast<const int*>(adv)[off];
@@ -260,32 +259,59 @@ __global__ void __launch_bounds__(256) acx_scan_warp_kernel(int T, int N, const 
             const bool terminal = done[(size_t)(et - 1) * N + n] != 0;
             if (!terminal) g += pow(gamma, (double)(et - t)) * (double)V[(size_t)et * N + n];
           }
-          a = (float)(g - (double)V[off]);
+          vt = V[off];
+          a = (float)(g - (double)vt);
         }
         __syncwarp();
         if (live) {
           const size_t off = (size_t)t * N + n;
           G[off] = (float)g; adv[off] = a;
-          msum += (double)a; msq += (double)a * (double)a;
+          SCAN_ACC(m, a, (float)g, vt);
         }
         __syncwarp();
         __threadfence_block();
       }
     }
   }
-  scan_finish_moments(msum, msq, ws, stats, (long long)T * N);
+  scan_finish_moments(m, ws, stats, (long long)T * N);
 }
 
-static int scan_grid(int N, int mode) {
-  int g = mode == 1 ? (N + 7) / 8 : (N + 255) / 256;
+static int scan_grid(int N, int per_block) {
+  int g = (N + per_block - 1) / per_block;
   int cap = acx_num_sms() * 8;
+  if (cap > SCAN_MAX_BLOCKS) cap = SCAN_MAX_BLOCKS;      // what the workspace has room for, on any part
   if (g > cap) g = cap;
   return g < 1 ? 1 : g;
 }
 
 extern "C" size_t acx_returns_adv_workspace_bytes(int T, int n) {
   (void)T; (void)n;
-  return sizeof(ScanWs) + sizeof(double) * 2 * (size_t)(148 * 8 + 64);
+  return sizeof(ScanWs) + sizeof(double) * SCAN_NMOM * (size_t)SCAN_MAX_BLOCKS;
+}
+
+static int scan_launch(int T, int n, const float* rew, const unsigned char* done, const float* V, double gamma,
+                       int look_ahead, float* G_out, float* adv_out, float* stats_out, ScanWs* ws, int mode,
+                       int max_blocks, cudaStream_t st) {
+  auto grid = [&](int cols, int per_block) {
+    const int g = scan_grid(cols, per_block);
+    return g > max_blocks ? max_blocks : g;
+  };
+  if (mode == ACX_SCAN_WARP)
+    acx_scan_warp_kernel<<<grid(n, 8), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out, adv_out, ws,
+                                                     stats_out);
+  else if (T <= look_ahead && (n & 3) == 0 && acx_aligned16(rew) && acx_aligned16(V) && acx_aligned16(G_out) &&
+           acx_aligned16(adv_out) && (reinterpret_cast<uintptr_t>(done) & 3u) == 0) {
+    if (n / 4 >= 2 * 256 * acx_num_sms())
+      acx_scan_cols4_kernel<4, 256><<<grid(n / 4, 256), 256, 0, st>>>(T, n, rew, done, V, gamma, G_out, adv_out, ws,
+                                                                      stats_out);
+    else
+      acx_scan_cols4_kernel<10, 64><<<grid(n / 4, 64), 64, 0, st>>>(T, n, rew, done, V, gamma, G_out, adv_out, ws,
+                                                                    stats_out);
+  } else
+    acx_scan_cols_kernel<<<grid(n, 256), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out, adv_out, ws,
+                                                       stats_out);
+  ACX_LAUNCH_OK("acx_scan kernel");
+  return ACX_OK;
 }
 
 extern "C" int acx_returns_adv_scan(int T, int n, const float* rew, const unsigned char* done, const float* V,
@@ -301,20 +327,8 @@ extern "C" int acx_returns_adv_scan(int T, int n, const float* rew, const unsign
   ACX_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 15u) == 0, "acx_returns_adv_scan: workspace must be 16-byte aligned");
   if (mode == ACX_SCAN_AUTO) mode = (n < 2048 && T >= 64) ? ACX_SCAN_WARP : ACX_SCAN_COLS;
   ACX_REQUIRE(mode == ACX_SCAN_COLS || mode == ACX_SCAN_WARP, "acx_returns_adv_scan: bad mode %d", mode);
-  cudaStream_t st = (cudaStream_t)stream;
-  ScanWs* ws = reinterpret_cast<ScanWs*>(workspace);
-  if (mode == ACX_SCAN_WARP)
-    acx_scan_warp_kernel<<<scan_grid(n, 1), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out,
-                                                         adv_out, ws, stats_out);
-  else if (T <= look_ahead && (n & 3) == 0 && acx_aligned16(rew) && acx_aligned16(V) && acx_aligned16(G_out) &&
-           acx_aligned16(adv_out) && (reinterpret_cast<uintptr_t>(done) & 3u) == 0)
-    acx_scan_cols4_kernel<<<scan_grid(n / 4, 0), 256, 0, st>>>(T, n, rew, done, V, gamma, G_out, adv_out, ws,
-                                                              stats_out);
-  else
-    acx_scan_cols_kernel<<<scan_grid(n, 0), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out,
-                                                         adv_out, ws, stats_out);
-  ACX_LAUNCH_OK("acx_scan kernel");
-  return ACX_OK;
+  return scan_launch(T, n, rew, done, V, gamma, look_ahead, G_out, adv_out, stats_out,
+                     reinterpret_cast<ScanWs*>(workspace), mode, SCAN_MAX_BLOCKS, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------ allocation-free variant
@@ -322,16 +336,20 @@ extern "C" int acx_returns_adv_scan(int T, int n, const float* rew, const unsign
 // device image instead of a caller workspace.  Every GPU that loads libacx.so carries these
 // ACX_SCAN_STATIC_SCRATCH_BYTES until the process exits.
 #define ACX_SCAN_STATIC_MAX_BLOCKS 512
-#define ACX_SCAN_STATIC_SCRATCH_BYTES (16 + 16 * ACX_SCAN_STATIC_MAX_BLOCKS)
+#define ACX_SCAN_STATIC_SCRATCH_BYTES (16 + 8 * 7 * ACX_SCAN_STATIC_MAX_BLOCKS)
 static __device__ __align__(256) unsigned char g_scan_static_scratch[ACX_SCAN_STATIC_SCRATCH_BYTES];
 
 // In host code `g_scan_static_scratch` is only a handle for the runtime, not an address a kernel can
-// use: the device address has to be asked for, once per device, while that device is current.
+// use: the device address has to be asked for, once per device, while that device is current.  The
+// look-up is serialised (two host threads may make their first call at the same time); the cached
+// address belongs to the device's primary context and is stale after cudaDeviceReset().
 static int scan_static_scratch(ScanWs** out) {
+  static std::mutex mu;
   static void* addr[64] = {nullptr};
   int dev = 0;
   ACX_CUDA_OK(cudaGetDevice(&dev));
   ACX_REQUIRE(dev >= 0 && dev < 64, "acx_returns_adv_scan_static: device ordinal %d not supported (max 63)", dev);
+  std::lock_guard<std::mutex> lock(mu);
   if (addr[dev] == nullptr) {
     void* p = nullptr;
     ACX_CUDA_OK(cudaGetSymbolAddress(&p, g_scan_static_scratch));

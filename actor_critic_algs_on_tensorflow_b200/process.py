@@ -240,15 +240,21 @@ def evaluate_batched(env_id, model_path, num_episodes, greedy=True, seed=12321, 
     return np.concatenate(out)
 
 
-def save_checkpoint(save_path, basename, gstep, actor_tensors, critic_tensors, keep=3, _kept=[]):
+_KEPT = {}      # Saver(max_to_keep) ring per checkpoint directory
+
+
+def save_checkpoint(save_path, basename, gstep, actor_tensors, critic_tensors, keep=3):
     """What the chief's CheckpointSaverHook + Saver(max_to_keep=3) leave on disk (A3C/process.py:197,211-214):
     ``<save_path>/<basename>-<gstep>.{index,data-00000-of-00001}`` holding the 22 global tensors, plus the
-    ``checkpoint`` state file."""
+    ``checkpoint`` state file.  The max_to_keep ring is kept per directory."""
     os.makedirs(save_path, exist_ok=True)
     prefix = os.path.join(save_path, "%s-%d" % (basename, gstep))
     t = dict(actor_tensors)
     t.update(critic_tensors)
     write_bundle(prefix, t)
+    _kept = _KEPT.setdefault(os.path.abspath(save_path), [])
+    if prefix in _kept:
+        _kept.remove(prefix)
     _kept.append(prefix)
     while len(_kept) > keep:
         old = _kept.pop(0)
@@ -290,13 +296,31 @@ def trainer_checkpoint_tensors(tr):
     return at, ct
 
 
+def _emit_log_rows(tr, logger, task_id, first, count, stdout_freq):
+    """One logger row per iteration (A3C/process.py:280-281) from the trainer's device ring: a single read-back for
+    ``count`` iterations."""
+    if logger is None or count <= 0:
+        return
+    for j, row in enumerate(tr.read_log(first, count), start=first):
+        logger(j, act_loss=row['act_loss'], worker_id=task_id, act_lr=row['act_lr'], kl_dist=row['kl_dist'],
+               circ_loss=np.sqrt(max(row['crit_loss'], 0.0)), avg_rew=row['avg_rew'], ev_before=row['ev_before'],
+               ev_after=row['ev_after'], print_tog=(j % max(1, stdout_freq)) == 0, avg_ent=row['avg_ent'])
+        if j % 100 == 50:
+            logger.flush()
+
+
 def process_fn(cluster, task_id, job, env_id, logger, save_path, stdout_freq, random_seed=12321, gamma=0.98,
                look_ahead=40, stack_frames=3, animate=False, save_every=600, desired_kl=0.002, TB_log=False,
                run_mode='train', checkpoint_basename='model', n_envs=4096, horizon=20, max_iters=None,
-               mode='sync', use_graph=True):
+               mode='sync', use_graph=True, diagnostics=True):
     """Worker body on the fused GPU path (reference: A3C/process.py:156-288).  One call = one rank.
     Extra keywords (``n_envs``, ``horizon``, ``max_iters``, ``mode``) size the batched rollout; everything
-    else keeps the reference's meaning.  ``random_seed`` arrives as seed + task (A3C/train.py:40)."""
+    else keeps the reference's meaning.  ``random_seed`` arrives as seed + task (A3C/train.py:40).
+    Every iteration leaves one log row (losses, lr, KL, avg_rew = mean return of the episodes that ended in the
+    batch, ev_before, ev_after, entropy) in a device ring; the host reads the ring back once per ``stdout_freq``
+    iterations (at most every 128) and feeds the rows to ``logger`` in order, so the log file has the reference's one
+    row per iteration without a host synchronisation per iteration.  ``diagnostics=False`` drops ev_after (one extra
+    critic pass per update; logged as -1)."""
     from .trainer import A2CTrainer
     if job == 'ps':
         print("ps %d: parameters are replicated on every GPU and reduced over NCCL; nothing to serve" % task_id)
@@ -312,31 +336,24 @@ def process_fn(cluster, task_id, job, env_id, logger, save_path, stdout_freq, ra
             dist.init_process_group("nccl", rank=task_id, world_size=world)
     tr = A2CTrainer(env_id, n_envs=n_envs, horizon=horizon, seed=random_seed - task_id, gamma=gamma,
                     look_ahead=look_ahead, desired_kl=desired_kl, min_lr=MIN_LR, max_lr=MAX_LR, rank=task_id,
-                    world=world, mode=mode, use_graph=use_graph, frames=stack_frames)
+                    world=world, mode=mode, use_graph=use_graph, frames=stack_frames, diagnostics=diagnostics)
     if is_chief:
         print('Initilizing chief. Envirnoment action type {}.'.format('cont' if tr.cont else 'disc'))
     print('\n\nREACHING THE MAIN LOOP OF WORKER %d\n' % task_id)
-    i, gstep, last_saved = 0, 0, -1
+    i, gstep, last_saved, logged = 0, 0, -1, 0
     limit = MAX_ITERS if max_iters is None else max_iters
-    stats = None
+    window = max(1, min(int(stdout_freq) if stdout_freq else 1, tr.log_rows))
     while gstep < limit:
         tr.iteration()
         gstep += world            # the reference bumps global_step once per worker update (policies.py:89)
-        if i % max(1, stdout_freq) == 0 or i % 100 == 50 or gstep >= limit:
-            stats = tr.read_stats()                       # the only host sync of the loop
-            done_eps = float(tr.done.sum().item())
-            avg_rew = float(tr.rew.sum().item()) / max(1.0, done_eps)
-            if logger is not None:
-                logger(i, act_loss=stats['act_loss'], worker_id=task_id, act_lr=stats['act_lr'],
-                       kl_dist=stats['kl_dist'], circ_loss=np.sqrt(max(stats['crit_loss'], 0.0)), avg_rew=avg_rew,
-                       ev_before=-1, ev_after=-1, print_tog=(i % max(1, stdout_freq)) == 0, avg_ent=stats['avg_ent'])
-                if i % 100 == 50:
-                    logger.flush()
+        i += 1
+        if i - logged >= window or gstep >= limit:
+            _emit_log_rows(tr, logger, task_id, logged, i - logged, stdout_freq)      # the only host sync of the loop
+            logged = i
         if is_chief and save_path and gstep // save_every > last_saved:
             last_saved = gstep // save_every
             at, ct = trainer_checkpoint_tensors(tr)
             save_checkpoint(save_path, checkpoint_basename, gstep, at, ct)
-        i += 1
     if logger is not None:
         logger.flush()
     return tr

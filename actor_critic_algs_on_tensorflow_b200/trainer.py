@@ -17,7 +17,10 @@ memory, streams and torch.distributed.  No CPU fallback.
 Multi-GPU (``world > 1``): environments are sharded by rank (index0 = rank * N keeps the Philox
 streams disjoint, mirroring seed+task of ``A3C/train.py:40``); parameters, Adam moments and the
 opt block are replicated.  ``mode='sync'`` is synchronous A2C: all-reduce(sum) of the flat
-gradient, x 1/world, clip, one identical Adam step on every rank, KL averaged over ranks.
+gradient, x 1/world, clip, one identical Adam step on every rank.  ONE collective per update: the
+post-update KL of update i (which only feeds the lr rule, and the lr is first consumed by update
+i+1's Adam step) rides as one extra float behind update i+1's gradient, so a step is
+graph -> all-reduce -> graph.
 ``mode='async'`` mirrors the reference's parameter-server semantics (per-worker clip, per-worker
 Adam moments and lr applied to shared parameters, then pull -- ``A3C/policies.py:85-98``,
 ``A3C/process.py:257-260``): every rank applies its own clipped gradient with its own moments to
@@ -53,12 +56,35 @@ def glorot_flat(net, ob_dim, num_ac, cont, gen):
     return flat
 
 
+GRAD_TAIL = 4      # floats behind the flat gradient in the exchange buffer: [KL of the previous update, 3 x pad]
+
+
+def sync_exchange(gradbuf, pg=None):
+    """The one collective of a synchronous update: SUM over ranks of [flat gradient ‖ previous post-update KL]
+    (replaces the workers' gradient pushes onto the ps variables, A3C/policies.py:88-89)."""
+    import torch.distributed as dist
+    dist.all_reduce(gradbuf, op=dist.ReduceOp.SUM, group=pg)
+    return gradbuf
+
+
+def async_push_pull(params, old_params, pg=None):
+    """The one collective of a stale-gradient update: every rank has applied its own Adam step to the
+    iteration-start parameters ``old_params``; the per-rank deltas are summed onto them (all pushes land,
+    A3C/policies.py:88-89) and every rank continues from the sum (the pull, A3C/process.py:259-260)."""
+    import torch.distributed as dist
+    params.sub_(old_params)
+    dist.all_reduce(params, op=dist.ReduceOp.SUM, group=pg)
+    params.add_(old_params)
+    return params
+
+
 class A2CTrainer:
     def __init__(self, env_id="Pendulum-v0", n_envs=65536, horizon=20, seed=12321, gamma=0.98, look_ahead=40,
                  desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1, actor_lr=0.005, critic_lr=0.001, beta=1.0,
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
                  critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=True,
-                 cache_activations=True, tensor_core_backward=True, frames=1, fused_rollout=True):
+                 cache_activations=True, tensor_core_backward=True, frames=1, fused_rollout=True, stagger=True,
+                 diagnostics=False, log_rows=128):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
@@ -110,7 +136,9 @@ class A2CTrainer:
         self.actor, self.critic = self.params[:self.Pa], self.params[self.Pa:]
         self.m = torch.zeros(P, device=d, dtype=f32)
         self.v = torch.zeros(P, device=d, dtype=f32)
-        self.grads = torch.zeros(P, device=d, dtype=f32)
+        # exchange buffer of the multi-rank update: flat gradient (actor ‖ critic) + GRAD_TAIL floats
+        self._gradbuf = torch.zeros(P + GRAD_TAIL, device=d, dtype=f32)
+        self.grads = self._gradbuf[:P]
         self.old_params = torch.empty(P, device=d, dtype=f32) if mode == "async" else None
 
         self.state = torch.empty((self.S, N), device=d, dtype=f32)
@@ -129,6 +157,14 @@ class A2CTrainer:
         self.stats = torch.zeros(L.STATS_SIZE, device=d, dtype=f32)
         self.opt = torch.zeros(L.OPT_SIZE, device=d, dtype=f32)
         self.step_ctr = torch.zeros(1, device=d, dtype=torch.int32)
+        # training-log diagnostics kept on the device (avg_rew, ev_before, ev_after, one ring row per iteration)
+        self.diagnostics = bool(diagnostics)
+        self.ep_ret = torch.zeros(N, device=d, dtype=f32)
+        self.ws_diag_bytes = L.load().acx_diag_workspace_bytes()
+        self.ws_diag = torch.zeros(self.ws_diag_bytes, device=d, dtype=torch.uint8)
+        self.V_after = torch.empty((T, N), device=d, dtype=f32) if self.diagnostics else None
+        self.log_rows = int(log_rows)
+        self.log_ring = torch.zeros((self.log_rows, 32), device=d, dtype=f32)
         self.ws_scan_bytes = L.load().acx_returns_adv_workspace_bytes(T, N)
         self.ws_scan = torch.zeros(self.ws_scan_bytes, device=d, dtype=torch.uint8)
         self.ws_bwd_bytes = L.load().acx_loss_backward_workspace_bytes(self.ob, self.num_ac, int(self.cont))
@@ -171,6 +207,15 @@ class A2CTrainer:
                L.ptr(self.obs_buf[0] if self.frames == 1 else self.raw_obs), None, self.seed, self.index0, 0xFFFFFFFF, s)
         if self.frames > 1:
             L.call("acx_frame_push", N, self.env_ob, self.frames, None, L.ptr(self.raw_obs), None, L.ptr(self.obs_buf[0]), s)
+        # N environments reset together would hit the TimeLimit together: every 20-step batch would hold one phase of
+        # the episode and (Pendulum) all done flags of a run would fall into every tenth update.  The reference batches
+        # whole episodes; spreading the time-limit counters over [0, max_steps) gives every update every phase.
+        self.stagger = bool(stagger)
+        if self.stagger:
+            L.call("acx_env_stagger", self.env, N, L.ptr(self.elapsed), self.seed, self.index0, self.max_steps, s)
+            # an episode that starts with part of its time limit spent is shorter than a real one: its return is not
+            # counted when it ends (NaN marker, acx_episode_returns)
+            self.ep_ret.copy_(torch.where(self.elapsed > 0, float("nan"), 0.0))
         self._pack()
 
     # ------------------------------------------------------------------ pieces (all enqueue on the current stream)
@@ -236,6 +281,11 @@ class A2CTrainer:
                 n += 1
         L.call("acx_counter_add", L.ptr(self.step_ctr), self.T, s)
         return n + 1
+
+    def _episode_stats(self):
+        L.call("acx_episode_returns", self.T, self.N, L.ptr(self.rew), L.ptr(self.done), L.ptr(self.ep_ret),
+               L.ptr(self.stats), L.ptr(self.ws_diag), self.ws_diag_bytes, L.cur_stream())
+        return 1
 
     def _gradients(self):
         s, N, T = L.cur_stream(), self.N, self.T
@@ -304,14 +354,55 @@ class A2CTrainer:
         L.call("acx_kl_finalize", L.ptr(self.kl_part), self.kl_blocks.value, float(T) * float(N), L.ptr(self.stats), s)
         return 2
 
-    def _lr_update(self):
-        L.call("acx_kl_lr_update", L.ptr(self.opt), L.ptr(self.stats), L.cur_stream())
+    def _lr_update(self, flags=3, kl_sum=None, kl_scale=1.0):
+        """flags 3: the lr rule on stats[KL_POST] + schedules + iteration bump (acx_kl_lr_update); 1 / 2: one half."""
+        if flags == 3 and kl_sum is None:
+            L.call("acx_kl_lr_update", L.ptr(self.opt), L.ptr(self.stats), L.cur_stream())
+        else:
+            L.call("acx_kl_lr_update_split", L.ptr(self.opt), L.ptr(self.stats), kl_sum, kl_scale, flags, L.cur_stream())
+        return 1
+
+    def _ev_after(self):
+        """ev_after of the reference's log row (A3C/process.py:261): the updated critic on the batch's observations
+        against the targets the update was fitted to.  One more value pass -- only with diagnostics=True."""
+        if not self.diagnostics:
+            return 0
+        s, N, T = L.cur_stream(), self.N, self.T
+        if self.tc:
+            L.call("acx_value_forward_tc", L.ptr(self.critic), L.ptr(self.packed_c), self.ob, T, N, L.ptr(self.obs_buf),
+                   L.ptr(self.V_after), 0, None, None, None, s)
+        else:
+            L.call("acx_value_forward", L.ptr(self.critic), self.ob, T, N, L.ptr(self.obs_buf), L.ptr(self.V_after), 0, s)
+        L.call("acx_explained_variance", T * N, L.ptr(self.G), L.ptr(self.V_after),
+               self.stats.data_ptr() + 4 * L.STAT_EV_AFTER, L.ptr(self.ws_diag), self.ws_diag_bytes, s)
+        return 2
+
+    def _log_push(self):
+        L.call("acx_log_push", L.ptr(self.log_ring), self.log_rows, L.ptr(self.stats), L.ptr(self.opt), L.cur_stream())
         return 1
 
     # ------------------------------------------------------------------ segments + graphs
     def _seg_a(self, buffered):
         self.obs_buf[0].copy_(self.obs_buf[self.T])      # the last observation of the previous rollout
-        return self._rollout(buffered) + self._gradients() + 1
+        return self._rollout(buffered) + self._episode_stats() + self._gradients() + 1
+
+    def _seg_b_single(self):
+        return self._apply(1.0) + self._post_kl() + self._ev_after() + self._lr_update() + self._log_push()
+
+    def _seg_b_sync(self, first):
+        """After the all-reduce of [gradient ‖ previous KL]: the previous update's lr rule on the rank-averaged KL
+        (not in the very first update), Adam on the averaged gradient, this update's local KL, which is left behind
+        the gradient for the next exchange, then the schedules and the iteration bump."""
+        P = self.Pa + self.Pc
+        n = 0
+        if not first:
+            n += self._lr_update(1, self._gradbuf.data_ptr() + 4 * P, 1.0 / self.world)
+        n += self._apply(1.0 / self.world) + self._post_kl() + self._ev_after()
+        self._gradbuf[P:P + 1].copy_(self.stats[L.STAT_KL_POST:L.STAT_KL_POST + 1])
+        return n + 1 + self._lr_update(2) + self._log_push()
+
+    def _seg_c_async(self):
+        return self._pack() + self._post_kl() + self._ev_after() + self._lr_update() + self._log_push()
 
     def _run(self, key, fn):
         """Run fn() on the current stream, through a CUDA graph after the first (eager, warm-up) call."""
@@ -330,12 +421,6 @@ class A2CTrainer:
             ent[2] = g
         ent[2].replay()
         return ent[0]
-
-    def _allreduce(self, t, average=False):
-        import torch.distributed as dist
-        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.pg)
-        if average:
-            t.mul_(1.0 / self.world)
 
     iterations_started = False
 
@@ -391,41 +476,54 @@ class A2CTrainer:
             self.noise_buf, self.reset_u_buf = self._own       # the "a_buf" graph is captured on this set
             self.noise_buf.copy_(noise, non_blocking=True)
             self.reset_u_buf.copy_(reset_u, non_blocking=True)
-        if not self.iterations_started:
+        first = not self.iterations_started
+        if first:
             # first iteration: obs_buf[0] already holds the reset observations
-            n = self._rollout(buffered) + self._gradients()
+            n = self._rollout(buffered) + self._episode_stats() + self._gradients()
             self.iterations_started = True
         else:
             n = self._run("a_" + tag, lambda: self._seg_a(buffered))
         if self.world == 1:
-            n += self._run("b1", lambda: self._apply(1.0) + self._post_kl() + self._lr_update())
+            n += self._run("b1", self._seg_b_single)
         elif self.mode == "sync":
-            self._allreduce(self.grads)
-            n += self._run("b", lambda: self._apply(1.0 / self.world) + self._post_kl())
-            self._allreduce(self.stats[L.STAT_KL_POST:L.STAT_KL_POST + 1], average=True)
-            n += self._run("c", self._lr_update)
+            sync_exchange(self._gradbuf, self.pg)
+            n += self._seg_b_sync(True) if first else self._run("b", lambda: self._seg_b_sync(False))
         else:   # async: stale-gradient pushes onto shared parameters, then pull
             self.old_params.copy_(self.params)
             n += self._run("b", lambda: self._apply(1.0))
-            self.params.sub_(self.old_params)                      # this worker's delta
-            self._allreduce(self.params)                           # every worker's push lands
-            self.params.add_(self.old_params)                      # pull
-            n += self._run("c", lambda: self._pack() + self._post_kl() + self._lr_update())
+            async_push_pull(self.params, self.old_params, self.pg)
+            n += self._run("c", self._seg_c_async)
         self.iterations += 1
         self.launches_per_iteration = n
         return n
 
     # ------------------------------------------------------------------ host-side views (synchronise)
-    def read_stats(self):
-        """Device -> host copy of the stats/opt blocks as a dict (the values the reference logs)."""
-        st = self.stats.cpu().numpy()
-        op = self.opt.cpu().numpy()
+    def _row_dict(self, st, op):
+        # sync multi-rank: the lr rule of update i runs at the start of update i+1, so opt[ACTOR_LR] of the row is the
+        # lr update i used; otherwise the rule has already run and stats[ACTOR_LR_USED] holds it
+        deferred = self.world > 1 and self.mode == "sync"
         return dict(act_loss=float(st[L.STAT_ACTOR_LOSS]), crit_loss=float(st[L.STAT_CRITIC_LOSS]),
                     kl_dist=float(st[L.STAT_KL_POST]), kl_pre=float(st[L.STAT_KL_PRE]),
-                    avg_ent=float(st[L.STAT_ENT_MEAN]), act_lr=float(st[L.STAT_ACTOR_LR_USED]),
+                    avg_ent=float(st[L.STAT_ENT_MEAN]),
+                    act_lr=float(op[L.OPT_ACTOR_LR] if deferred else st[L.STAT_ACTOR_LR_USED]),
                     next_lr=float(op[L.OPT_ACTOR_LR]), beta=float(op[L.OPT_BETA_KL]),
                     gamma_ent=float(op[L.OPT_GAMMA_ENT]), adv_mean=float(st[L.STAT_ADV_MEAN]),
-                    adv_std=float(st[L.STAT_ADV_STD]), iteration=int(op[L.OPT_ITER]), adam_t=int(op[L.OPT_ADAM_T]))
+                    adv_std=float(st[L.STAT_ADV_STD]), iteration=int(op[L.OPT_ITER]), adam_t=int(op[L.OPT_ADAM_T]),
+                    ev_before=float(st[L.STAT_EV_BEFORE]),
+                    ev_after=float(st[L.STAT_EV_AFTER]) if self.diagnostics else -1.0,
+                    avg_rew=float(st[L.STAT_EP_REW_MEAN]), episodes=int(st[L.STAT_EP_COUNT]))
+
+    def read_stats(self):
+        """Device -> host copy of the stats/opt blocks as a dict (the values the reference logs)."""
+        return self._row_dict(self.stats.cpu().numpy(), self.opt.cpu().numpy())
+
+    def read_log(self, first, count):
+        """The log rows of iterations first .. first+count-1 (count <= log_rows, all already run) from the device
+        ring: ONE device -> host copy however many iterations it covers."""
+        assert 0 < count <= self.log_rows and first + count <= self.iterations
+        ring = self.log_ring.cpu().numpy()
+        return [self._row_dict(ring[i % self.log_rows, :16], ring[i % self.log_rows, 16:]) for i in
+                range(first, first + count)]
 
     def env_steps_per_iteration(self):
         return self.N * self.T

@@ -76,6 +76,10 @@ extern "C" {
 #define ACX_STAT_KL_POST 7
 #define ACX_STAT_REW_LOSS 8
 #define ACX_STAT_ACTOR_LR_USED 9
+#define ACX_STAT_EV_BEFORE 10     /* var_accounted_for(target = G, pred = V[:T]) -- A3C/util.py:5-13, process.py:111-116 */
+#define ACX_STAT_EV_AFTER 11      /* the same after the update (acx_explained_variance on fresh values, process.py:261) */
+#define ACX_STAT_EP_REW_MEAN 12   /* mean return of the episodes that ended in the batch (avg_rew, process.py:243) */
+#define ACX_STAT_EP_COUNT 13      /* how many ended */
 
 int acx_abi_version(void);
 const char* acx_last_error(void);
@@ -227,7 +231,9 @@ int acx_value_forward_tc(const float* critic, const float* packed, int ob_dim, i
  * PathAdv.__call__ -- A3C/process.py:54-66 -- over time-major [T][n] buffers with done masks
  * (each column may hold several episode segments; the tail is cut by the horizon and
  * bootstraps from V[T]); plus the batch moments of A3C/process.py:247:
- * stats_out[0] = mean(adv), [1] = 1/(1e-8 + std(adv)), [2] = std(adv) (population).
+ * stats_out[0] = mean(adv), [1] = 1/(1e-8 + std(adv)), [2] = std(adv) (population), and the
+ * critic diagnostic the reference logs as ev_before (A3C/process.py:111-116, util.py:5-13):
+ * stats_out[ACX_STAT_EV_BEFORE] = mean(standardised G * standardised V[:T]).
  * V is [T+1][n].  workspace: 16-byte aligned, first 16 bytes zero before the first call. */
 size_t acx_returns_adv_workspace_bytes(int T, int n);
 int acx_returns_adv_scan(int T, int n, const float* rew, const unsigned char* done, const float* V,
@@ -239,13 +245,15 @@ int acx_returns_adv_scan(int T, int n, const float* rew, const unsigned char* do
  * a fresh cudaMalloc fails; of a control loop that cannot afford the device-wide synchronisation an
  * allocation implies; or of a sandboxed plugin thread that is given input and output buffers and
  * nothing else.  Inputs and outputs are still the caller's; only the few KB of partial-moment
- * scratch come from a fixed array inside the library's device image (about 8 KB that every GPU
+ * scratch come from a fixed array inside the library's device image (about 28 KB that every GPU
  * loading the library keeps until the process exits).
  *   - Limit: n <= ACX_SCAN_STATIC_MAX_COLUMNS env columns per call (T is unlimited); wider batches
  *     are refused with ACX_ERR_INVALID and a message -- use acx_returns_adv_scan for those.
  *   - Nothing is allocated or freed, here or in any library it calls.
  *   - The first call on each device looks up the array's device address (that device must be
- *     current); make that first call before any stream capture begins.
+ *     current; the look-up is serialised between host threads); make that first call before any
+ *     stream capture begins.  cudaDeviceReset() invalidates the cached address: do not call this
+ *     entry point again on that device afterwards.
  *   - All calls on a device share the one array and it keeps the previous call's contents; the
  *     entry point re-zeroes the counter it depends on (stream-ordered) before launching.  Two calls
  *     whose kernels can overlap on the GPU (different streams, no dependency) race on it: keep
@@ -254,6 +262,30 @@ int acx_returns_adv_scan(int T, int n, const float* rew, const unsigned char* do
 int acx_returns_adv_scan_static(int T, int n, const float* rew, const unsigned char* done, const float* V,
                                 double gamma, int look_ahead, float* G_out, float* adv_out,
                                 float* stats_out, int mode, void* stream);
+
+/* ---------------------------------------------------------------- diagnostics of the training log
+ * The reference prints avg_rew, ev_before and ev_after every iteration (A3C/process.py:243,261,280-283).  These keep
+ * them on the device: workspace = acx_diag_workspace_bytes() bytes, 16-byte aligned, first 16 bytes zero before the
+ * first call (each entry point may have its own or share one, stream-ordered).
+ * acx_episode_returns: rew/done [T][n] of one rollout; ep_ret[n] (in/out) is the running return of each column's
+ * unfinished episode (a NaN marks an episode whose start was not seen: dropped when it ends).  Writes
+ * stats[ACX_STAT_EP_COUNT] = episodes that ended in the batch and, when that is > 0,
+ * stats[ACX_STAT_EP_REW_MEAN] = their mean return (tot_rews / rolls, process.py:234,243).
+ * acx_explained_variance: *out = mean(standardised target * standardised pred) over count samples
+ * (var_accounted_for, A3C/util.py:5-13). */
+size_t acx_diag_workspace_bytes(void);
+int acx_episode_returns(int T, int n, const float* rew, const unsigned char* done, float* ep_ret, float* stats,
+                        void* workspace, size_t workspace_bytes, void* stream);
+int acx_explained_variance(long long count, const float* target, const float* pred, float* out, void* workspace,
+                           size_t workspace_bytes, void* stream);
+/* One log row per iteration without a host sync per iteration (the reference logs every iteration,
+ * A3C/process.py:280-281): copies stats[16] ‖ opt[16] into row (opt[ITER] - 1) mod rows of ring[rows][32]; call it
+ * after acx_kl_lr_update and read the ring back at leisure. */
+int acx_log_push(float* ring, int rows, const float* stats, const float* opt, void* stream);
+/* Spread the TimeLimit counters of n freshly reset environments over [0, max_steps) (Philox stream 3 of
+ * (seed, index0 + i)), so that a batched rollout sees every phase of the episode in every update, as the reference's
+ * whole-episode batches do (A3C/process.py:221-235).  max_steps <= 0: the env's default. */
+int acx_env_stagger(int env, int n, int* elapsed, uint64_t seed, uint64_t index0, int max_steps, void* stream);
 
 /* ---------------------------------------------------------------- K4: loss + backward
  * Actor loss  -mean(adv*lp) + beta*mean((lp_old-lp)^2) - gamma*mean(entropy) and its gradient
@@ -354,6 +386,13 @@ int acx_counter_add(uint32_t* counter, uint32_t inc, void* stream);
  * stats[KL_POST] can sit between them. */
 int acx_kl_finalize(const double* kl_partial, int kl_blocks, double count, float* stats, void* stream);
 int acx_kl_lr_update(float* opt, float* stats, void* stream);
+/* The two halves of acx_kl_lr_update on their own, for data-parallel ranks that exchange ONE buffer per update (the
+ * reference's workers push and pull once, A3C/policies.py:88-98): flags = 1 applies the lr rule of
+ * A3C/process.py:262-270 only, flags = 2 the LinearSchedule updates of :271-278 and the opt[ITER] bump only, 3 both.
+ * kl_sum (nullable DEVICE pointer): the rule then uses *kl_sum * kl_scale -- the post-update KL summed over ranks, which
+ * travelled as one extra float behind the flat gradient of the NEXT update's all-reduce; the lr is first consumed by
+ * that update's acx_adam_apply, so applying the rule there changes nothing -- and leaves it in stats[ACX_STAT_KL_POST]. */
+int acx_kl_lr_update_split(float* opt, float* stats, const float* kl_sum, float kl_scale, int flags, void* stream);
 
 #ifdef __cplusplus
 }

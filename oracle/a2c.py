@@ -14,12 +14,13 @@ import numpy as np
 from . import envs as E
 from . import philox as R
 from . import policies as P
-from .pathadv import linear_schedule_val, path_adv_columns
+from .pathadv import linear_schedule_val, path_adv_columns, var_accounted_for
 
 
 class A2CState:
     def __init__(self, env, n_envs, seed=12321, rank=0, world=1, frames=1, dtype=np.float32,
-                 actor=None, critic=None, actor_lr=0.005, critic_lr=0.001, beta=1.0, gamma_ent=0.01):
+                 actor=None, critic=None, actor_lr=0.005, critic_lr=0.001, beta=1.0, gamma_ent=0.01, stagger=False,
+                 max_steps=None):
         self.env, self.N, self.seed, self.rank, self.world = env, n_envs, seed, rank, world
         self.f = dtype
         self.cont = env == E.PENDULUM
@@ -45,6 +46,11 @@ class A2CState:
         u = R.uniforms(self.idx, 0xFFFFFFFF, R.STREAM_RESET, seed).T            # [4, N]
         self.state = E.reset_from_uniforms(env, u[:E.STATE_DIM[env]], dtype)
         self.elapsed = np.zeros(n_envs, dtype=np.int32)
+        self.ep_ret = np.zeros(n_envs, dtype=np.float32)       # running return of each column's unfinished episode
+        if stagger:     # the batched trainer's phase stagger (acx_env_stagger): time-limit counters over [0, max_steps)
+            limit = int(max_steps or E.MAX_EPISODE_STEPS[env])
+            self.elapsed = (R.philox4x32(self.idx, 0, R.STREAM_PHASE, seed)[:, 0] % np.uint32(limit)).astype(np.int32)
+            self.ep_ret[self.elapsed > 0] = np.nan              # started mid-way: not counted when it ends
         self.obs = np.tile(E.observe(env, self.state, dtype), (self.frames, 1))     # fresh episode: k copies
 
 
@@ -57,6 +63,7 @@ def rollout(S, T, max_steps=None):
     rew = np.zeros((T, S.N), dtype=f)
     done = np.zeros((T, S.N), dtype=np.uint8)
     ent_sum = 0.0
+    ep_sum, ep_count = 0.0, 0
     for t in range(T):
         obs_buf[t] = S.obs
         if S.cont:
@@ -72,16 +79,23 @@ def rollout(S, T, max_steps=None):
         else:       # drop the oldest frame, append the newest; a finished episode restarts with k copies (auto-reset)
             shifted = np.concatenate([S.obs[S.env_ob:], raw], axis=0)
             S.obs = np.where(done[t][None, :] != 0, np.tile(raw, (S.frames, 1)), shifted).astype(f)
+        S.ep_ret = (S.ep_ret + rew[t]).astype(np.float32)      # tot_rews of A3C/process.py:234, per finished episode
+        ended = done[t] != 0
+        counted = ended & ~np.isnan(S.ep_ret)
+        ep_sum += float(np.sum(S.ep_ret[counted], dtype=np.float64))
+        ep_count += int(counted.sum())
+        S.ep_ret[ended] = 0.0
         acs[t] = ac.T if S.cont else ac[None, :]
         logps[t] = lp
         ent_sum += float(np.sum(ent, dtype=np.float64))
         S.gstep += 1
     obs_buf[T] = S.obs
-    return dict(obs=obs_buf, acs=acs, logps=logps, rew=rew, done=done, ent_sum=ent_sum)
+    return dict(obs=obs_buf, acs=acs, logps=logps, rew=rew, done=done, ent_sum=ent_sum, ep_sum=ep_sum,
+                ep_count=ep_count)
 
 
 def update(S, ro, gamma=0.98, look_ahead=40, desired_kl=0.002, min_lr=1e-6, max_lr=0.1, clip=0.1,
-           allreduce=None, grad_dtype=np.float32):
+           allreduce=None, grad_dtype=np.float32, diagnostics=False):
     """One update from a rollout; ``allreduce(x)`` (optional) averages an array over ranks."""
     f = S.f
     T = ro["rew"].shape[0]
@@ -105,11 +119,15 @@ def update(S, ro, gamma=0.98, look_ahead=40, desired_kl=0.002, min_lr=1e-6, max_
     S.actor, S.am, S.av = P.adam_step(S.actor, g_a, S.am, S.av, S.t_adam, S.actor_lr)
     lp_new = P.actor_logp(S.actor, S.alay, obs, acs, S.cont, S.ac_scale, dtype=f)
     kl = float(np.mean((lp_old.astype(np.float64) - lp_new.astype(np.float64)) ** 2))
+    ev_before = float(var_accounted_for(target=G.reshape(-1), pred=V[:T].reshape(-1).astype(np.float64)))
+    ev_after = float(var_accounted_for(target=G.reshape(-1), pred=P.critic_value(
+        S.critic, S.clay, obs, dtype=f).astype(np.float64))) if diagnostics else None
     if allreduce is not None:
         kl = float(allreduce(np.array([kl]))[0])
     stats = dict(actor_loss=float(ag["loss"]), critic_loss=float(cg["loss"]), kl=kl, actor_lr=S.actor_lr,
                  avg_ent=ro["ent_sum"] / B, mean_rew=float(ro["rew"].mean()), G=G, adv=adv, V=V, rollout=ro,
-                 grad_actor=g_a, grad_critic=g_c)
+                 grad_actor=g_a, grad_critic=g_c, ev_before=ev_before, ev_after=ev_after,
+                 avg_rew=(ro["ep_sum"] / ro["ep_count"]) if ro.get("ep_count") else None, episodes=ro.get("ep_count", 0))
     S.actor_lr = float(np.float32(P.kl_lr_rule(S.actor_lr, kl, desired_kl, min_lr, max_lr)))
     if S.it % 100 == 0:                                  # A3C/process.py:271-278
         S.gamma_ent = float(10.0 ** linear_schedule_val(S.it, 100, 3000, -2, -8))

@@ -24,6 +24,7 @@ MASK = np.uint64(0xFFFFFFFF)
 # stream ids shared with the device code
 STREAM_RESET = 1     # env reset uniforms
 STREAM_ACTION = 2    # action noise (normal eps / categorical uniform)
+STREAM_PHASE = 3     # time-limit phase stagger of the batched trainer (word 0 mod max_episode_steps)
 
 
 def philox4x32(index, step, stream, seed):

@@ -1,7 +1,9 @@
 """The fused rollout+update loop (trainer.A2CTrainer) against the oracle's iteration (oracle/a2c.py)
 from the same Philox streams and the same initial weights; CUDA-graph replay vs eager launches;
 caller-supplied noise; checkpoint export.  Tolerances: rollout quantities 1e-4 (T chained fp32 env steps
-and forwards), returns 2e-4, gradients 2e-3 of the tensor's max (they inherit the rollout's rounding)."""
+and forwards), returns 2e-4, gradients GRAD_TOL of the tensor's max (they inherit the rollout's rounding: the
+oracle's rollout and the kernel's differ by fp32 rounding of sin/cos/tanh, and every later quantity is computed from
+its own rollout; the measured error is printed)."""
 import os
 
 import numpy as np
@@ -13,6 +15,7 @@ from actor_critic_algs_on_tensorflow_b200.trainer import A2CTrainer
 from actor_critic_algs_on_tensorflow_b200 import process, tf_bundle
 
 pytestmark = pytest.mark.gpu
+GRAD_TOL = 2e-3
 
 
 def _cmp_iteration(tr, st, cont):
@@ -28,9 +31,17 @@ def _cmp_iteration(tr, st, cont):
     np.testing.assert_allclose(tr.V.cpu().numpy(), st["V"], rtol=1e-4, atol=1e-4)
     np.testing.assert_allclose(tr.G.cpu().numpy(), st["G"], rtol=2e-4, atol=2e-4)
     ga, gc = tr.grads[:tr.Pa].cpu().numpy(), tr.grads[tr.Pa:].cpu().numpy()
-    for g, w in ((np.clip(ga, -0.1, 0.1), st["grad_actor"]), (gc, st["grad_critic"])):
-        assert np.abs(g - w).max() <= 2e-3 * np.abs(w).max()
+    for name, g, w in (("actor", np.clip(ga, -0.1, 0.1), st["grad_actor"]), ("critic", gc, st["grad_critic"])):
+        err = np.abs(g - w).max() / np.abs(w).max()
+        print("trainer vs oracle, %s gradient: %.2e of max" % (name, err))
+        assert err <= GRAD_TOL
     got = tr.read_stats()
+    np.testing.assert_allclose(got["ev_before"], st["ev_before"], rtol=1e-3, atol=1e-4)
+    assert got["episodes"] == st["episodes"]
+    if st["episodes"]:
+        np.testing.assert_allclose(got["avg_rew"], st["avg_rew"], rtol=1e-4, atol=1e-4)
+    if st.get("ev_after") is not None and tr.diagnostics:
+        np.testing.assert_allclose(got["ev_after"], st["ev_after"], rtol=2e-2, atol=2e-3)
     np.testing.assert_allclose(got["act_loss"], st["actor_loss"], rtol=1e-3, atol=1e-4)
     np.testing.assert_allclose(got["crit_loss"], st["critic_loss"], rtol=1e-3)
     np.testing.assert_allclose(got["kl_dist"], st["kl"], rtol=2e-2, atol=1e-6)
@@ -42,13 +53,16 @@ def _cmp_iteration(tr, st, cont):
 @pytest.mark.parametrize("env_id,env,N,T", [("Pendulum-v0", E.PENDULUM, 256, 8), ("CartPole-v0", E.CARTPOLE, 192, 12),
                                             ("Acrobot-v1", E.ACROBOT, 128, 6)])
 def test_first_iteration_matches_oracle(env_id, env, N, T, tensor_cores):
-    S = a2c.A2CState(env, N, seed=777)
+    ms = 5 if env != E.PENDULUM else None
+    S = a2c.A2CState(env, N, seed=777, stagger=True, max_steps=ms)
     tr = A2CTrainer(env_id, n_envs=N, horizon=T, seed=777, actor_params=S.actor.copy(), critic_params=S.critic.copy(),
-                    use_graph=False, max_episode_steps=5 if env != E.PENDULUM else 0, tensor_cores=tensor_cores)
+                    use_graph=False, max_episode_steps=ms or 0, tensor_cores=tensor_cores, diagnostics=True)
     np.testing.assert_array_equal(tr.state.cpu().numpy(), S.state)          # Philox reset, exact
+    np.testing.assert_array_equal(tr.elapsed.cpu().numpy(), S.elapsed)      # Philox phase stagger, exact
+    assert len(np.unique(S.elapsed)) > 1
     tr.iteration()
     torch.cuda.synchronize()
-    st = a2c.iteration(S, T=T, max_steps=5 if env != E.PENDULUM else None)
+    st = a2c.iteration(S, T=T, max_steps=ms, diagnostics=True)
     _cmp_iteration(tr, st, env == E.PENDULUM)
     assert tr.done.sum().item() > 0 or env == E.PENDULUM
     np.testing.assert_allclose(tr.read_stats()["next_lr"], S.actor_lr, rtol=1e-6)
@@ -57,7 +71,7 @@ def test_first_iteration_matches_oracle(env_id, env, N, T, tensor_cores):
 @pytest.mark.parametrize("env_id,env,N,T", [("Pendulum-v0", E.PENDULUM, 256, 8), ("CartPole-v0", E.CARTPOLE, 192, 12)])
 def test_frame_stacking_matches_oracle(env_id, env, N, T):
     """--frames 2 (Framer, A3C/process.py:25-43) on the fused path: stacked observations, 2 x ob_dim network inputs."""
-    S = a2c.A2CState(env, N, seed=31, frames=2)
+    S = a2c.A2CState(env, N, seed=31, frames=2, stagger=True, max_steps=5 if env != E.PENDULUM else 3)
     tr = A2CTrainer(env_id, n_envs=N, horizon=T, seed=31, actor_params=S.actor.copy(), critic_params=S.critic.copy(),
                     use_graph=False, max_episode_steps=5 if env != E.PENDULUM else 3, frames=2)
     assert tr.ob == 2 * E.OBS_DIM[env]
@@ -208,3 +222,50 @@ def test_activation_cache_from_the_tensor_core_forward_matches_recomputing():
     np.testing.assert_array_equal(outs[0][2], outs[1][2])
     for i in (0, 1):
         assert np.abs(outs[0][i] - outs[1][i]).max() <= 2e-5 * np.abs(outs[0][i]).max()
+
+
+def test_log_ring_holds_one_row_per_iteration():
+    """acx_log_push: the row of iteration i in the device ring equals what read_stats() returned right after iteration i
+    (one D2H copy for the whole window instead of a host sync per iteration), through CUDA-graph replays and ring wrap."""
+    tr = A2CTrainer("CartPole-v0", n_envs=512, horizon=8, seed=3, log_rows=4, diagnostics=True, max_episode_steps=9)
+    rows = []
+    for _ in range(7):
+        tr.iteration()
+        rows.append(tr.read_stats())
+    got = tr.read_log(3, 4)
+    for g, w in zip(got, rows[3:]):
+        for key in w:
+            np.testing.assert_array_equal(np.float32(g[key]), np.float32(w[key]), err_msg=key)
+    assert rows[-1]["episodes"] > 0 and np.isfinite(rows[-1]["ev_before"]) and np.isfinite(rows[-1]["ev_after"])
+    assert abs(rows[-1]["ev_before"]) <= 1.0 + 1e-5 and abs(rows[-1]["ev_after"]) <= 1.0 + 1e-5
+
+
+def test_staggered_phases_put_done_flags_into_every_iteration():
+    """Pendulum never ends early: without the stagger all 200-step limits fire in the same iteration (one in ten at
+    T = 20); with it every iteration finishes ~N * T / 200 episodes."""
+    N, T = 4096, 20
+    tr = A2CTrainer("Pendulum-v0", n_envs=N, horizon=T, seed=5)
+    counts = []
+    for _ in range(12):
+        tr.iteration()
+        counts.append(int(tr.done.sum().item()))
+    assert min(counts) > 0.5 * N * T / 200 and max(counts) < 1.5 * N * T / 200, counts
+    off = A2CTrainer("Pendulum-v0", n_envs=256, horizon=T, seed=5, stagger=False)
+    c2 = []
+    for _ in range(10):
+        off.iteration()
+        c2.append(int(off.done.sum().item()))
+    assert c2[:9] == [0] * 9 and c2[9] == 256
+
+
+def test_fused_path_learns_cartpole():
+    """The fused rollout + update actually learns: mean episode return of CartPole-v0 (A2C, 4,096 envs x 20 steps per
+    update, the reference's hyper-parameters) rises well above the random policy's ~22 within 150 updates."""
+    tr = A2CTrainer("CartPole-v0", n_envs=4096, horizon=20, seed=12321)
+    hist = []
+    for i in range(150):
+        tr.iteration()
+        if i % 10 == 9:
+            hist.append(tr.read_stats()["avg_rew"])
+    print("CartPole mean episode return every 10 updates:", ["%.1f" % h for h in hist])
+    assert hist[0] < 40 and max(hist[-3:]) > 2.0 * hist[0], hist
