@@ -155,3 +155,69 @@ def test_frame_push_is_the_reference_framer(lib, dev, ob, frames, n):
     f = lib.load().acx_frame_push
     assert f(8, ob, frames, out[0].data_ptr(), o_d[0].data_ptr(), None, out[0].data_ptr(), None) == -1      # aliasing
     assert f(0, ob, frames, None, None, None, None, None) == 0
+
+
+# ------------------------------------------------------------------ the kernels against the physics (tests/test_env_physics.py)
+def _gpu_dynamics(lib, dev, env):
+    """(state, action) -> (next state, reward, terminal) through acx_env_step with the time limit out of reach."""
+    def dyn(s, a):
+        s32 = np.ascontiguousarray(np.asarray(s, dtype=np.float32))
+        n = s32.shape[1]
+        a = np.asarray(a)
+        a = a.astype(np.float32) if env == E.PENDULUM else a.astype(np.int32)
+        ru = np.full((E.STATE_DIM[env], n), 0.5, np.float32)
+        st, _, _, rew, done = _step_gpu(lib, dev, env, s32, np.zeros(n, np.int32), a, ru, max_steps=1 << 30)
+        return st.astype(np.float64), rew.astype(np.float64), done.astype(bool)
+    return dyn
+
+
+def test_env_kernels_obey_the_equations_of_motion(lib, dev):
+    """The CUDA transitions satisfy the Lagrangian equations of the three systems with the documented constants,
+    integrator and time step -- the same property checks as the oracle, at fp32 resolution (an acceleration recovered
+    from a velocity difference over dt carries eps * |v| / dt ~ 1e-4)."""
+    import test_env_physics as PH
+    PH.check_pendulum_equation_of_motion(_gpu_dynamics(lib, dev, E.PENDULUM), atol=3e-4)
+    PH.check_pendulum_energy_and_period(_gpu_dynamics(lib, dev, E.PENDULUM), tol_scale=1.02)
+    PH.check_cartpole_equations_of_motion(_gpu_dynamics(lib, dev, E.CARTPOLE), atol=5e-4, theta_range=0.15)
+    dsdt = lambda s, a: E._acrobot_dsdt(s, a, np.float64)
+    PH.check_acrobot_step(_gpu_dynamics(lib, dev, E.ACROBOT), dsdt, tol=2e-3, terminal_states=False)
+
+
+def test_env_kernel_time_limits_fire_on_the_documented_step(lib, dev):
+    import test_env_physics as PH
+
+    def step_fn(env, state, elapsed, ac, ru):
+        a = np.asarray(ac).reshape(-1)
+        a = a.astype(np.float32) if env == E.PENDULUM else a.astype(np.int32)
+        st, el, obs, rew, done = _step_gpu(lib, dev, env, np.ascontiguousarray(state, dtype=np.float32),
+                                           np.asarray(elapsed, np.int32), a, np.ascontiguousarray(ru, dtype=np.float32))
+        return st.astype(np.float64), el, obs, rew, done
+    PH.check_time_limits(step_fn)
+
+
+def test_categorical_kernel_draws_from_softmax(lib, dev):
+    """acx_policy_forward_sample_cat (the tf.multinomial restatement, A3C/policies.py:64): 10^7 draws per logit vector
+    follow softmax(logits) (chi^2 at p ~ 1e-7), with caller uniforms and with the device's Philox stream; u = 0 and the
+    largest u < 1 give the first and the last category; the action index is monotone in u."""
+    import test_env_physics as PH
+    from oracle import policies as P
+
+    def sampler(seed_box=[1]):
+        def sample(lg, u):
+            n, k = lg.shape
+            lay = P.actor_layout(4, k, False)
+            flat = np.zeros(lay["_size"], np.float32)
+            o, _ = lay["bh"]
+            flat[o:o + k] = lg[0]                       # zero weights: logits = head bias for every observation
+            a = torch.tensor(flat, device=dev)
+            obs = torch.zeros((1, 4, n), device=dev)
+            ac = torch.empty((1, n), device=dev, dtype=torch.int32)
+            ud = None if u is None else torch.tensor(np.ascontiguousarray(u, dtype=np.float32).reshape(1, n), device=dev)
+            seed_box[0] += 1
+            lib.call("acx_policy_forward_sample_cat", lib.ptr(a), 4, k, 1, n, lib.ptr(obs), lib.ptr(ud), 1000 + seed_box[0], 0, 0,
+                     None, lib.ptr(ac), None, None, None, lib.cur_stream())
+            torch.cuda.synchronize()
+            return ac.cpu().numpy().reshape(-1)
+        return sample
+    PH.check_sampler_distribution(sampler(), n=10_000_000, given_u=True)
+    PH.check_sampler_distribution(sampler(), n=10_000_000, given_u=False)

@@ -65,28 +65,33 @@ def test_cli_flag_sets_match_reference():
 
 
 def _gloo_worker(rank, world, port, q):
-    """The cross-rank arithmetic of trainer.A2CTrainer.iteration on host tensors with gloo."""
+    """The cross-rank part of trainer.A2CTrainer.iteration -- the trainer's own exchange functions (sync_exchange,
+    async_push_pull, the GRAD_TAIL slot that carries the previous update's KL) -- on host tensors over gloo; the
+    oracle's adam_step stands in for the acx_adam_apply launch between them."""
     import torch
     import torch.distributed as dist
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from oracle import policies as P
+    from actor_critic_algs_on_tensorflow_b200 import trainer as TR
+    n = 64
     rng = np.random.default_rng(100 + rank)
-    theta0 = np.random.default_rng(7).normal(size=64).astype(np.float32)     # replicated parameters
-    g = rng.normal(size=64).astype(np.float32) * 0.3                          # this rank's local gradient
-    # --- sync: all-reduce(sum) x 1/world, clip, identical Adam step everywhere
-    t = torch.from_numpy(g.copy())
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
-    gm = np.clip(t.numpy() / world, -0.1, 0.1)
-    th_sync, _, _ = P.adam_step(theta0, gm, np.zeros(64, np.float32), np.zeros(64, np.float32), 1, 0.005)
-    # --- async: own clip + own moments on the stale parameters, deltas summed (every push lands), then pull
-    th_loc, _, _ = P.adam_step(theta0, np.clip(g, -0.1, 0.1), np.zeros(64, np.float32), np.zeros(64, np.float32), 1, 0.005)
-    d = torch.from_numpy((th_loc - theta0).copy())
-    dist.all_reduce(d, op=dist.ReduceOp.SUM)
-    th_async = theta0 + d.numpy()
-    kl = torch.tensor([0.001 * (rank + 1)])
-    dist.all_reduce(kl, op=dist.ReduceOp.SUM)
-    q.put((rank, th_sync, th_async, float(kl.item() / world), g))
+    theta0 = np.random.default_rng(7).normal(size=n).astype(np.float32)     # replicated parameters
+    g = rng.normal(size=n).astype(np.float32) * 0.3                          # this rank's local gradient
+    zeros = np.zeros(n, np.float32)
+    # --- sync: ONE all-reduce of [gradient | previous update's local KL | pad], x 1/world, clip, identical Adam step
+    buf = torch.zeros(n + TR.GRAD_TAIL)
+    buf[:n] = torch.from_numpy(g)
+    buf[n] = 0.001 * (rank + 1)                                              # this rank's post-update KL, one update ago
+    TR.sync_exchange(buf)
+    gm = np.clip(buf[:n].numpy() / world, -0.1, 0.1)
+    kl_avg = float(buf[n].item() / world)
+    th_sync, _, _ = P.adam_step(theta0, gm, zeros, zeros, 1, P.kl_lr_rule(0.005, kl_avg, 0.002))
+    # --- async: own clip + own moments on the stale parameters, then the trainer's push / pull
+    th_loc, _, _ = P.adam_step(theta0, np.clip(g, -0.1, 0.1), zeros, zeros, 1, 0.005)
+    params, old = torch.from_numpy(th_loc.copy()), torch.from_numpy(theta0.copy())
+    TR.async_push_pull(params, old)
+    q.put((rank, th_sync, params.numpy().copy(), kl_avg, g))
     dist.destroy_process_group()
 
 
@@ -108,10 +113,13 @@ def test_world_size_2_update_logic_gloo():
     np.testing.assert_array_equal(a0, a1)
     assert kl0 == kl1 == pytest.approx(0.0015)
     theta0 = np.random.default_rng(7).normal(size=64).astype(np.float32)
-    want, _, _ = P.adam_step(theta0, np.clip((g0 + g1) / 2, -0.1, 0.1), np.zeros(64, np.float32), np.zeros(64, np.float32),
-                             1, 0.005)
+    zeros = np.zeros(64, np.float32)
+    # the averaged KL 0.0015 lies inside [d/4, 4d] of desired_kl = 0.002: the rule leaves lr at 0.005
+    want, _, _ = P.adam_step(theta0, np.clip((g0 + g1) / 2, -0.1, 0.1), zeros, zeros, 1, 0.005)
     np.testing.assert_allclose(s0, want, rtol=1e-6, atol=1e-7)
-    # async: both workers' first Adam steps (lr * sign(g)) land on the shared parameters
+    # async: theta0 + the sum of both workers' own Adam deltas (every push lands, then the pull)
+    d = [P.adam_step(theta0, np.clip(g, -0.1, 0.1), zeros, zeros, 1, 0.005)[0] - theta0 for g in (g0, g1)]
+    np.testing.assert_allclose(a0, theta0 + d[0] + d[1], rtol=1e-6, atol=1e-7)
     np.testing.assert_allclose(a0 - theta0, -0.005 * (np.sign(g0) + np.sign(g1)), rtol=1e-3, atol=1e-6)
 
 
