@@ -100,8 +100,25 @@ class ClockSampler(object):
                 "reasons": reasons, "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
+def host_threads():
+    """Give the numpy/BLAS arithmetic of the CPU arms every host core, explicitly: torchrun exports OMP_NUM_THREADS=1
+    to its children, which would quietly make the reference arm single-threaded.  Must run before numpy is imported."""
+    cores = os.cpu_count() or 1
+    for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[k] = str(cores)
+    return cores
+
+
+def blas_threads():
+    try:
+        from threadpoolctl import threadpool_info
+        return max([int(x.get("num_threads", 1)) for x in threadpool_info()] or [1])
+    except Exception:
+        return None
+
+
 def cpu_baseline(steps=2, n_envs=2048, warmup=1):
-    """Oracle A2C iteration (numpy, all host threads through BLAS) on a bounded sample."""
+    """Oracle A2C iteration (numpy, all host threads through BLAS) on n_envs x HORIZON env-steps per iteration."""
     from oracle import a2c, envs as E
     S = a2c.A2CState(E.ENV_IDS[ENV_ID], n_envs, seed=SEED)
     for _ in range(warmup):
@@ -114,20 +131,44 @@ def cpu_baseline(steps=2, n_envs=2048, warmup=1):
         n_envs, HORIZON, steps)
 
 
+def b_ref_baselines(seconds=3.0):
+    """The reference's OWN loop shape on the host cores (oracle/ref_loop.py; BASELINE.md section 3 "B-ref"): batch-1 act
+    per env step, whole episodes, PathAdv per episode, one update per >= 1,200 (A3C) / >= 800 or 7 episodes (Basic_AC)
+    steps -- without TensorFlow's per-call dispatch, i.e. an upper bound on the real reference."""
+    from oracle import ref_loop as RL
+    out = {}
+    for key, env, workers, basic in (("a3c_pendulum_1_worker", "Pendulum-v0", 1, False),
+                                     ("a3c_pendulum_runner_sh_2_workers", "Pendulum-v0", 2, False),
+                                     ("basic_ac_cartpole_1_process", "CartPole-v0", 1, True)):
+        v, n = RL.run_workers(env, workers, basic, seconds=seconds, seed=SEED)
+        out[key] = {"value": v, "unit": "env-steps/s", "processes": workers, "env_steps_timed": n,
+                    "config": "BASELINE.json configs[%d]" % (0 if basic else 1)}
+    return out
+
+
 def run_reference(args, rank):
+    """--impl reference: the numpy restatement of the reference's math on the box's host cores, on THIS arm's config
+    (65,536 envs x 20 steps per iteration, full size): at 10-30 s per iteration the timed region is capped at 2 iterations
+    after 1 warm-up iteration on a 4,096-env sample, whatever --steps / --warmup say."""
     if rank != 0:
         return
     cores = os.cpu_count()
-    v, sec, sample = cpu_baseline(steps=max(1, args.steps), n_envs=2048, warmup=min(args.warmup, 1))
+    k = max(1, min(args.steps, 2))
+    cpu_baseline(steps=1, n_envs=4096, warmup=0)                       # warm-up: BLAS threads, allocator
+    v, sec, sample = cpu_baseline(steps=k, n_envs=N_ENVS, warmup=0)
+    bref = b_ref_baselines()
     line = {"impl": "reference", "metric": "env-steps/sec (rollout+update)", "value": v, "unit": "env-steps/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+            "n_gpus": args.gpus, "steps": k, "warmup": 1, "ms_per_step": sec * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": sample},
-            "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
+            "config": {"workload": WORKLOAD, "envs_per_gpu": N_ENVS, "horizon": HORIZON, "sample": sample,
+                       "same_config": True, "host_threads": blas_threads(), "host_cores": cores},
+            "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "blas_threads": blas_threads(),
+                             "kind": "port", "sample": sample, "b_ref": bref},
             "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
-            "note": "numpy restatement of the reference's math (oracle/a2c.py): TF 1.3 and gym are not installable "
-                    "here (BASELINE.md section 2); an upper bound on the real reference, which runs batch-1 sess.run"}
+            "note": "numpy restatement of the reference's math (oracle/a2c.py), vectorised over the env batch: TF 1.3 and "
+                    "gym are not installable here (BASELINE.md section 2); faster than the real reference, whose own "
+                    "shape (batch-1 sess.run per env step) is timed as cpu_baseline.b_ref"}
     print(json.dumps(line), flush=True)
 
 
@@ -466,6 +507,7 @@ def run_ours(args, rank, local_rank, world):
                     "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
         total_flops = (FLOP_ACTOR_FWD * (1 + 3 + 1) + FLOP_CRITIC_FWD * (3 + (HORIZON + 1) / HORIZON)) * steps_per_it
         cb_v, cb_sec, cb_sample = (cpu_baseline() if world == 1 else (None, None, None))
+        bref = b_ref_baselines(seconds=2.0) if world == 1 else None
         line = {"metric": "env-steps/sec (rollout+update)", "value": value, "unit": "env-steps/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": step_ms, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
@@ -486,8 +528,9 @@ def run_ours(args, rank, local_rank, world):
                 "step_tflops": total_flops / (sec / args.steps) / 1e12,
                 "train_stats": stats}
         if cb_v is not None:
-            line["cpu_baseline"] = {"value": cb_v, "unit": "env-steps/s", "cores": os.cpu_count(), "kind": "port",
-                                    "sample": cb_sample, "sec_per_iteration": cb_sec}
+            line["cpu_baseline"] = {"value": cb_v, "unit": "env-steps/s", "cores": os.cpu_count(),
+                                    "blas_threads": blas_threads(), "kind": "port", "sample": cb_sample,
+                                    "sec_per_iteration": cb_sec, "b_ref": bref}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -506,8 +549,8 @@ def run_eval(args, rank, local_rank, world):
             return
         import numpy as np
         from oracle import envs as E, policies as P, philox as R
-        from actor_critic_algs_on_tensorflow_b200.tf_bundle import read_bundle
-        t = read_bundle(model)
+        from oracle.demo_ckpt import read_demo_checkpoint
+        t = read_demo_checkpoint(model)
         lay = P.actor_layout(3, 1, True)
         g = "global_actor/"
         actor = P.pack({"W1": t[g + "first_layer/kernel"], "b1": t[g + "first_layer/bias"],
@@ -621,6 +664,7 @@ def main():
         w = WORKLOADS[args.workload]
         ENV_ID, N_ENVS, HORIZON, WORKLOAD = w["env_id"], w["n_envs"], w["horizon"], w["name"]
         FLOP_ACTOR_FWD, FLOP_CRITIC_FWD = w["flop_actor"], w["flop_critic"]
+    host_threads()                     # before numpy / torch load their BLAS: the CPU arms use every host core
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -250,7 +250,7 @@ def check_sampler_distribution(sample, n=1_000_000, given_u=True):
     """sample(logits[B, k], u[B]) -> actions: counts follow softmax(logits) (chi^2), u = 0 gives the first category,
     u -> 1 the last one."""
     rng = np.random.default_rng(4)
-    for logits in ([0.3, -1.2], [2.0, 0.0, -1.0], [-0.5, -0.5, 3.0, 1.0, 0.0]):
+    for logits in ([0.3, -1.2], [2.0, 0.0, -1.0], [-0.5, -0.5, 3.0, 1.0]):
         lg = np.broadcast_to(np.asarray(logits, np.float32), (n, len(logits)))
         u = rng.random(n).astype(np.float32) if given_u else None        # None: the sampler draws its own uniforms
         a = np.asarray(sample(lg, u))

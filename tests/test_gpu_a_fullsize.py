@@ -71,7 +71,7 @@ def fill_caches_with_the_tensor_core_forwards(k):
     nb = ctypes.c_int(0)
     if k.cont:
         lib.call("acx_policy_logp_gauss_tc", lib.ptr(k.a), lib.ptr(pf_a), k.ob, k.num_ac, 2.0, k.rows, k.n, lib.ptr(k.o),
-                 lib.ptr(k.acs_d), lib.ptr(lp), None, None, None, lib.ptr(kl_part), ctypes.byref(nb), s)
+                 lib.ptr(k.acs_d), lib.ptr(lp), None, None, lib.ptr(k.lp_d), lib.ptr(kl_part), ctypes.byref(nb), s)
         # the policy forward on the tensor cores, given the stored actions' noise, rewrites the actor's caches
         eps = torch.zeros((k.rows, k.num_ac, k.n), device=dev)
         ac2, lp2 = torch.empty_like(k.acs_d), torch.empty((k.rows, k.n), device=dev)
@@ -80,7 +80,7 @@ def fill_caches_with_the_tensor_core_forwards(k):
                  lib.ptr(k.ax3), s)
     else:
         lib.call("acx_policy_logp_cat_tc", lib.ptr(k.a), lib.ptr(pf_a), k.ob, k.num_ac, k.rows, k.n, lib.ptr(k.o),
-                 lib.ptr(k.acs_d), lib.ptr(lp), None, None, None, lib.ptr(kl_part), ctypes.byref(nb), s)
+                 lib.ptr(k.acs_d), lib.ptr(lp), None, None, lib.ptr(k.lp_d), lib.ptr(kl_part), ctypes.byref(nb), s)
         u = torch.full((k.rows, k.n), 0.5, device=dev)
         ac2, lp2 = torch.empty_like(k.acs_d), torch.empty((k.rows, k.n), device=dev)
         lib.call("acx_policy_forward_sample_cat_tc", lib.ptr(k.a), lib.ptr(pf_a), k.ob, k.num_ac, k.rows, k.n,

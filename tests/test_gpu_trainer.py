@@ -15,7 +15,7 @@ from actor_critic_algs_on_tensorflow_b200.trainer import A2CTrainer
 from actor_critic_algs_on_tensorflow_b200 import process, tf_bundle
 
 pytestmark = pytest.mark.gpu
-GRAD_TOL = 2e-3
+GRAD_TOL = 1e-4      # measured on B200: 1e-7 .. 3.1e-5 over the cases below
 
 
 def _cmp_iteration(tr, st, cont):
@@ -260,12 +260,13 @@ def test_staggered_phases_put_done_flags_into_every_iteration():
 
 def test_fused_path_learns_cartpole():
     """The fused rollout + update actually learns: mean episode return of CartPole-v0 (A2C, 4,096 envs x 20 steps per
-    update, the reference's hyper-parameters) rises well above the random policy's ~22 within 150 updates."""
+    update, the reference's hyper-parameters) rises from the random policy's ~22 to > 150 of the 200 possible within
+    60 updates (measured on B200: 65 after 10 updates, 170-198 from 20 on)."""
     tr = A2CTrainer("CartPole-v0", n_envs=4096, horizon=20, seed=12321)
     hist = []
-    for i in range(150):
+    for i in range(60):
         tr.iteration()
-        if i % 10 == 9:
+        if i % 10 == 0 or i == 59:
             hist.append(tr.read_stats()["avg_rew"])
-    print("CartPole mean episode return every 10 updates:", ["%.1f" % h for h in hist])
-    assert hist[0] < 40 and max(hist[-3:]) > 2.0 * hist[0], hist
+    print("CartPole mean episode return after updates 1, 11, 21, ...:", ["%.1f" % h for h in hist])
+    assert hist[0] < 35 and max(hist[-3:]) > 150, hist

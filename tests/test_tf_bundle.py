@@ -82,3 +82,17 @@ def test_corruption_is_detected(golden_dir, tmp_path):
 def test_crc32c_known_answers():
     assert B.crc32c(b"123456789") == 0xE3069283           # the standard CRC-32C check value
     assert B.crc32c(b"") == 0 and B.crc32c(bytes(32)) == 0x8A9136AA
+
+
+def test_oracle_side_checkpoint_table_matches_the_bundle_reader(golden_dir):
+    """oracle/demo_ckpt.py (offset table of SURVEY.md Appendix A, used by bench.py's CPU arms so that they do not import
+    the product) and the product's TF V2 bundle reader give the same 22 tensors."""
+    import os
+    import numpy as np
+    from oracle.demo_ckpt import read_demo_checkpoint
+    from actor_critic_algs_on_tensorflow_b200.tf_bundle import read_bundle
+    prefix = os.path.join(golden_dir, "model-Pendulum_a3c")
+    a, b = read_demo_checkpoint(prefix), read_bundle(prefix)
+    assert set(a) == set(b) and len(a) == 22
+    for k in a:
+        np.testing.assert_array_equal(a[k], b[k])
