@@ -175,10 +175,12 @@ def critic_value(flat, lay, obs, basic_head=False, dtype=np.float32):
 
 # ------------------------------------------------------------------ losses + analytic gradients
 def actor_loss_grads(flat, lay, obs, acs, advs, logp_old, beta, gamma_ent, cont,
-                     ac_scale=2.0, clip=0.1, dtype=np.float64):
+                     ac_scale=2.0, clip=0.1, dtype=np.float64, abs_sums=False):
     """loss = -mean(adv*lp) + beta*mean((lp_old-lp)^2) - gamma*mean(entropy)  (policies.py:74-80)
     and its gradient wrt every actor tensor, clipped elementwise to +-clip (policies.py:85).
-    Returns dict(loss, rew_loss, kl, ent, grad (flat, clipped), grad_raw (flat))."""
+    Returns dict(loss, rew_loss, kl, ent, grad (flat, clipped), grad_raw (flat)).
+    abs_sums=True adds ``grad_abs``: every gradient element with its per-sample terms summed as absolute values
+    (sum_i |t_ij| instead of sum_i t_ij) -- the condition number of the batch sum is grad_abs / |grad_raw|."""
     f = dtype
     P = {k: v.astype(f) for k, v in unpack(flat, lay).items()}
     B = len(obs)
@@ -222,22 +224,32 @@ def actor_loss_grads(flat, lay, obs, acs, advs, logp_old, beta, gamma_ent, cont,
         dhead = dlogits
     G["Wh"] = x3.T @ dhead
     G["bh"] = dhead.sum(axis=0)
+    A = {}
+    if abs_sums:
+        A["Wh"], A["bh"] = np.abs(x3).T @ np.abs(dhead), np.abs(dhead).sum(axis=0)
+        if cont:
+            A["log_std"] = np.sum(np.abs(dlp[:, None] * (z * z - f(1.0))) + np.abs(dent[:, None]), axis=0)
 
-    def back(dout, x_out, x_in, W):
+    def back(dout, x_out, x_in, W, name=None):
         dpre = dout * np.where(x_out > 0, f(1.0), f(0.2))         # lrelu': 0.8*[x>0] + 0.2
+        if abs_sums:
+            A["W" + name], A["b" + name] = np.abs(x_in).T @ np.abs(dpre), np.abs(dpre).sum(axis=0)
         return x_in.T @ dpre, dpre.sum(axis=0), dpre @ W.T
 
     dx3 = dhead @ P["Wh"].T
-    G["W3"], G["b3"], dx2 = back(dx3, x3, x2, P["W3"])
-    G["W2"], G["b2"], dx1 = back(dx2, x2, x1, P["W2"])
-    G["W1"], G["b1"], _ = back(dx1, x1, obs, P["W1"])
+    G["W3"], G["b3"], dx2 = back(dx3, x3, x2, P["W3"], "3")
+    G["W2"], G["b2"], dx1 = back(dx2, x2, x1, P["W2"], "2")
+    G["W1"], G["b1"], _ = back(dx1, x1, obs, P["W1"], "1")
     raw = pack(G, lay, dtype=f)
-    return dict(loss=loss, rew_loss=rew_loss, kl=kl, ent=np.mean(ent), lp=lp,
-                grad_raw=raw, grad=np.clip(raw, -f(clip), f(clip)) if clip is not None else raw)
+    out = dict(loss=loss, rew_loss=rew_loss, kl=kl, ent=np.mean(ent), lp=lp,
+               grad_raw=raw, grad=np.clip(raw, -f(clip), f(clip)) if clip is not None else raw)
+    if abs_sums:
+        out["grad_abs"] = pack(A, lay, dtype=f)
+    return out
 
 
-def critic_loss_grads(flat, lay, obs, targets, basic_head=False, dtype=np.float64):
-    """loss = mean((v - target)^2), gradients unclipped (policies.py:152-158)."""
+def critic_loss_grads(flat, lay, obs, targets, basic_head=False, dtype=np.float64, abs_sums=False):
+    """loss = mean((v - target)^2), gradients unclipped (policies.py:152-158).  abs_sums: see actor_loss_grads."""
     f = dtype
     P = {k: v.astype(f) for k, v in unpack(flat, lay).items()}
     B = len(obs)
@@ -252,20 +264,28 @@ def critic_loss_grads(flat, lay, obs, targets, basic_head=False, dtype=np.float6
     loss = np.mean(err * err)
     dv = (f(2.0) * err / f(B))[:, None]
     G = {"Wv": h.T @ dv, "bv": dv.sum(axis=0)}
+    A = {"Wv": np.abs(h).T @ np.abs(dv), "bv": np.abs(dv).sum(axis=0)} if abs_sums else {}
     dh = dv @ P["Wv"].T
 
-    def back(dout, x_out, x_in, W):
+    def back(dout, x_out, x_in, W, name=None):
         dpre = dout * (x_out > 0)
+        if abs_sums:
+            A["W" + name], A["b" + name] = np.abs(x_in).T @ np.abs(dpre), np.abs(dpre).sum(axis=0)
         return x_in.T @ dpre, dpre.sum(axis=0), dpre @ W.T
 
     if basic_head:
         G["W3"], G["b3"] = np.zeros_like(P["W3"]), np.zeros_like(P["b3"])   # dead third layer
+        if abs_sums:
+            A["W3"], A["b3"] = np.zeros_like(P["W3"]), np.zeros_like(P["b3"])
         dx1 = dh
     else:
-        G["W3"], G["b3"], dx1 = back(dh, x2, x1, P["W3"])
-    G["W2"], G["b2"], dx = back(dx1, x1, x, P["W2"])
-    G["W1"], G["b1"], _ = back(dx, x, obs, P["W1"])
-    return dict(loss=loss, v=v, grad=pack(G, lay, dtype=f))
+        G["W3"], G["b3"], dx1 = back(dh, x2, x1, P["W3"], "3")
+    G["W2"], G["b2"], dx = back(dx1, x1, x, P["W2"], "2")
+    G["W1"], G["b1"], _ = back(dx, x, obs, P["W1"], "1")
+    out = dict(loss=loss, v=v, grad=pack(G, lay, dtype=f))
+    if abs_sums:
+        out["grad_abs"] = pack(A, lay, dtype=f)
+    return out
 
 
 # ------------------------------------------------------------------ optimiser + lr rule
