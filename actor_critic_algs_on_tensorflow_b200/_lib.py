@@ -8,7 +8,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libacx.so")
+# ACX_LIB_PATH: development override (A/B builds of the same ABI, e.g. `make prof`); the product loads the in-tree library
+LIB_PATH = os.environ.get("ACX_LIB_PATH") or os.path.join(_HERE, "libacx.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 ENV_PENDULUM, ENV_CARTPOLE, ENV_ACROBOT = 0, 1, 2

@@ -7,11 +7,15 @@
 // wrote (dPre3, dPre2) and the activation cache (X2): the sample index is contiguous, i.e. both operands are K-major
 // as they lie in HBM.  X1 = act(obs W1 + b1) is not read but recomputed (ob_dim <= 8 FMAs per element) straight into the swizzled
 // operand layout.  Each persistent CTA owns the 128-sample tiles  blockIdx.x, +gridDim.x, ...  and keeps
-// its partial dW3 / dW2 in tensor memory (fp32).  The tensor core's accumulate truncates: over the ~3,300 accumulating
-// MMAs of a CTA's whole share the error reached 7.7e-5 of the result (measured against an fp64 product of the same
-// operands, tests/tc/run_wgrad_accuracy.py).  So the accumulators are double-buffered and flushed every WG_FLUSH
-// tiles: while the MMAs fill one buffer, warps 2-5 add the other into the CTA's scratch row with ordinary fp32
-// (round-to-nearest) adds; acx_grad_reduce then sums the rows in fixed order (bit-reproducible run to run).
+// its partial dW3 / dW2 in tensor memory (fp32).  The tensor core's accumulate TRUNCATES, once per instruction: a bias of
+// about half an ulp of the accumulator per accumulating MMA, towards zero.  Where the per-sample terms cancel it hides
+// (7.7e-5 of the result over a CTA's whole share of ~3,300 MMAs, 8.4e-6 with a flush every 8 tiles); where they have one
+// sign it adds up linearly in the number of MMAs per accumulation -- measured against an fp64 product of the same
+// operands on one-signed data (tests/test_gpu_a_fullsize.py, tests/tc/run_flush_ab.py): 2.2e-5 of the result at 8 tiles
+// per accumulation, 1.1e-5 at 4, 5.4e-6 at 2.  So the accumulators are double-buffered and flushed every WG_FLUSH = 2
+// tiles (96 accumulating MMAs): while the MMAs fill one buffer, warps 2-5 add the other into the CTA's scratch row with
+// ordinary fp32 (round-to-nearest) adds; acx_grad_reduce then sums the rows in fixed order (bit-reproducible run to run).
+// Cost against 8 tiles: +5 % of the two kernels' time (critic pair 2.11 -> 2.21 ms); it buys the 1e-5 parity bar.
 //   warp 0     producer: TMA tensor loads of [features x 32 samples] boxes, 128-byte swizzle, 2- or 3-deep ring (WgCfg)
 //   warp 1     issuer:   per box 4 K-steps x 3 kind::tf32 MMAs (lo*hi, hi*lo, hi*hi) per 128-row block
 //   warps 2-9  splitters: lo = rna(x - trunc(x)) of every landed word into the stage's second buffer (the MMA itself
@@ -42,9 +46,9 @@ constexpr int WG_THREADS = 320;
 constexpr int BOX = 32;                    // samples per box row (128 bytes)
 constexpr int BLK = 128 * BOX;             // floats of a 128-row box
 #ifndef ACX_WG_FLUSH
-#define ACX_WG_FLUSH 8
+#define ACX_WG_FLUSH 2
 #endif
-constexpr int WG_FLUSH = ACX_WG_FLUSH;                // tiles (1,024 samples, 384 accumulating MMAs) per tensor-memory accumulation
+constexpr int WG_FLUSH = ACX_WG_FLUSH;                // tiles (256 samples, 96 accumulating MMAs) per tensor-memory accumulation
 
 struct WgBars {
   unsigned long long full[3], split[3], empty[3], dfull[2], dfree[2];

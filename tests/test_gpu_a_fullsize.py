@@ -20,7 +20,8 @@ Bars (north_star: 1e-5 relative, fp32):
     plus the absolute rounding floor 3e-6 / sqrt(B) that matters only for the one-element tensors (see
     tests/test_gpu_backward_tc.py::check_grads);
   * the tensor-core accumulate truncates: the weight-gradient kernel flushes its tensor-memory accumulators into fp32
-    scratch every 8 tiles; its product is checked against an fp64 product of the very operands it read
+    scratch every 2 tiles; its product is checked against an fp64 product of the very operands it read, on
+    cancelling AND on one-signed data (where the truncation bias adds up instead of averaging out)
     (was tests/tc/run_wgrad_accuracy.py) so that a longer flush interval cannot slip through.
 The measured errors are printed (pytest -s / the GPU log).
 
@@ -137,7 +138,7 @@ def test_tcgen05_forward_and_backward_at_the_bench_size_match_the_fp64_oracle(li
         k.adv_d, k.tg_d = dev_t(k.adv, dev), dev_t(k.targets, dev)
         ga, gc, stats = k.run("tc", critic_masks=True)
         t0 = time.time()
-        wa, wc, sums, lp_want, v_want = chunked_oracle(k, np.float64, abs_sums=(regime == "zero-mean"))
+        wa, wc, sums, lp_want, v_want = chunked_oracle(k, np.float64, abs_sums=True)
         t64 = time.time() - t0
         if regime == "one-signed":          # ---- K2 (the forward passes do not depend on the regime)
             for name, got, want in (("V (acx_value_forward_tc)", v_got, v_want),
@@ -153,16 +154,20 @@ def test_tcgen05_forward_and_backward_at_the_bench_size_match_the_fp64_oracle(li
         failures, worst = [], 0.0
         for net, got, want, lay in (("actor", ga, wa, k.lay), ("critic", gc, wc, k.clay)):
             e = per_tensor_errors(got, want, lay)
+            eabs = per_tensor_errors(sums["abs_a"] if net == "actor" else sums["abs_c"], 0 * want, lay)
             if regime == "zero-mean":
                 e32 = per_tensor_errors(wa32 if net == "actor" else wc32, want, lay)
-                eabs = per_tensor_errors(sums["abs_a"] if net == "actor" else sums["abs_c"], 0 * want, lay)
             for name in e:
                 err, scale = e[name]
+                kappa = eabs[name][0] / scale
                 if regime == "one-signed":
-                    print("%s | %s | %s.%s: cuda %.2e of max |grad| = %.3e" % (label, regime, net, name, err / scale, scale))
-                    ok = err <= BAR * scale + floor
+                    # log_std: d lp / d log_std = z^2 - 1 has zero mean over the batch whatever the advantages are --
+                    # that one element cancels in every regime and gets the condition-number bar
+                    strict = name != "log_std"
+                    print("%s | %s | %s.%s: cuda %.2e of max |grad| = %.3e; kappa = %.1f" % (
+                        label, regime, net, name, err / scale, scale, kappa))
+                    ok = err <= BAR * (1.0 if strict else kappa) * scale + floor
                 else:
-                    kappa = eabs[name][0] / scale
                     print("%s | %s | %s.%s: cuda %.2e, numpy-fp32 oracle %.2e of max |grad| = %.3e; kappa = %.0f" % (
                         label, regime, net, name, err / scale, e32[name][0] / scale, scale, kappa))
                     ok = err <= BAR * kappa * scale + floor and err <= 3.0 * e32[name][0] + BAR * scale + floor
@@ -178,13 +183,19 @@ def test_tcgen05_forward_and_backward_at_the_bench_size_match_the_fp64_oracle(li
         np.testing.assert_allclose(stats[6], sums["ent"], rtol=BAR)
 
 
-def test_weight_gradient_kernel_against_fp64_of_its_own_operands(lib, dev):
+@pytest.mark.parametrize("one_signed", [False, True])
+def test_weight_gradient_kernel_against_fp64_of_its_own_operands(lib, dev, one_signed):
     """acx_wgrad_kernel at 20 x 65,536: dW3 = X2 . dPre3^T and db3 against an fp64 product of the very arrays the
     kernel read (the X2 cache and the dPre3 stream the chain kernel left in the workspace).  The tensor core's fp32
-    accumulate truncates: without the periodic flush of the tensor-memory accumulators this error was 7.7e-5; with a
-    flush every 8 tiles 8.4e-6.  Bar 1e-5 -- a change of the flush interval has to pass here."""
+    accumulate truncates once per MMA: with cancelling terms the error was 7.7e-5 without a flush of the tensor-memory
+    accumulators and 8.4e-6 with one every 8 tiles; with one-signed terms (targets above every value) the bias adds up:
+    2.2e-5 at 8 tiles, 1.1e-5 at 4, 5.4e-6 at the shipped 2.  Bar 1e-5 -- a change of the flush interval has to pass
+    here."""
     rows, n = 20, 65536
     k = TB.Case(lib, dev, True, 3, 1, rows, n, 77)
+    if one_signed:
+        k.targets = k.targets + np.float32(12.0)
+        k.tg_d = dev_t(k.targets, dev)
     _, gc, _ = k.run("tc", actor=False)
     _, fc, _ = k.run("ffma", actor=False)
     base = (lib.load().acx_loss_backward_workspace_bytes(3, 1, 1) + 255) & ~255
@@ -198,5 +209,6 @@ def test_weight_gradient_kernel_against_fp64_of_its_own_operands(lib, dev):
         b3 = torch.tensor(g[ob3:ob3 + 128], device=dev).double()
         ew = ((w3 - ref_w3).abs().max() / ref_w3.abs().max()).item()
         eb = ((b3 - ref_b3).abs().max() / ref_b3.abs().max()).item()
-        print("%s: dW3 %.2e, db3 %.2e of max, against fp64 of the same operands" % (name, ew, eb))
+        print("%s (%s): dW3 %.2e, db3 %.2e of max, against fp64 of the same operands" % (
+            name, "one-signed" if one_signed else "cancelling", ew, eb))
         assert ew <= bar and eb <= bar, (name, ew, eb)
