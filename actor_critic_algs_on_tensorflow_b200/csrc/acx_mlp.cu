@@ -324,7 +324,7 @@ int tile_grid(int rows, int n) {
 int check_common(const char* fn, const float* params, int ob_dim, int nout, int rows, int n, const float* obs) {
   ACX_REQUIRE(params && obs, "%s: null params/obs", fn);
   ACX_REQUIRE(acx_aligned16(params), "%s: params must be 16-byte aligned (bulk-TMA source)", fn);
-  ACX_REQUIRE(ob_dim >= 1 && ob_dim <= MAX_OB, "%s: ob_dim %d outside [1,%d]", fn, ob_dim, MAX_OB);
+  ACX_REQUIRE(ob_dim >= 1 && ob_dim <= MAX_OB_WIDE, "%s: ob_dim %d outside [1,%d]", fn, ob_dim, MAX_OB_WIDE);
   ACX_REQUIRE(nout >= 1 && nout <= MAX_OUT, "%s: output width %d outside [1,%d]", fn, nout, MAX_OUT);
   ACX_REQUIRE(rows >= 0 && n >= 0, "%s: negative batch (rows=%d, n=%d)", fn, rows, n);
   return ACX_OK;

@@ -33,7 +33,9 @@ constexpr int CH = 32;              // weight rows per ring chunk
 constexpr int SLOT_FLOATS = CH * 128;
 constexpr int NSLOT = 3;
 constexpr int H2 = 128;
-constexpr int MAX_OB = 8;
+constexpr int MAX_OB = 8;           // network inputs of the tensor-core kernels (shared memory is full of weights there)
+constexpr int MAX_OB_WIDE = 24;     // of the FFMA engine: 3 stacked frames of Acrobot's 6 observations (--frames 3, the
+                                    // reference's process_fn default, A3C/process.py:156-157)
 constexpr int MAX_OUT = 4;
 
 enum { HEAD_GAUSS = 0, HEAD_CAT = 1, HEAD_VALUE = 2 };
@@ -93,11 +95,12 @@ struct Args {
 };
 
 struct Smem {
+  static constexpr int OBW = MAX_OB_WIDE;
   float slot[NSLOT][SLOT_FLOATS];
   float X2[H2 * MS];
   float X3[128 * MS];        // layer-3 output / dPre3; also the staging area of a 128-row block of layer 1
-  float obs[MAX_OB * MT];
-  float W1[MAX_OB * 256];
+  float obs[MAX_OB_WIDE * MT];
+  float W1[MAX_OB_WIDE * 256];
   float b1[256];
   float b2[128];
   float b3[128];
@@ -383,15 +386,16 @@ __device__ inline void layer1_grad(SM& sm, int h, int ob, const float* __restric
                                    float* __restrict__ scrb1, bool first) {
   const int j = threadIdx.x;
   if (j < 128) {
-    float sb = 0.f, sw[MAX_OB];
+    constexpr int OBW = SM::OBW;
+    float sb = 0.f, sw[OBW];
 #pragma unroll
-    for (int i = 0; i < MAX_OB; ++i) sw[i] = 0.f;
+    for (int i = 0; i < OBW; ++i) sw[i] = 0.f;
 #pragma unroll 4
     for (int m4 = 0; m4 < MT / 4; ++m4) {
       const float4 d = *reinterpret_cast<const float4*>(D + j * MS + 4 * m4);
       sb += d.x; sb += d.y; sb += d.z; sb += d.w;
 #pragma unroll
-      for (int i = 0; i < MAX_OB; ++i)
+      for (int i = 0; i < OBW; ++i)
         if (i < ob) {
           const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + 4 * m4]);
           sw[i] = fmaf(o.x, d.x, sw[i]); sw[i] = fmaf(o.y, d.y, sw[i]);
@@ -401,7 +405,7 @@ __device__ inline void layer1_grad(SM& sm, int h, int ob, const float* __restric
     const int k = h * 128 + j;
     scrb1[k] = first ? sb : scrb1[k] + sb;
 #pragma unroll
-    for (int i = 0; i < MAX_OB; ++i)
+    for (int i = 0; i < OBW; ++i)
       if (i < ob) {
         float* p = scrW1 + i * H1 + k;
         *p = first ? sw[i] : *p + sw[i];

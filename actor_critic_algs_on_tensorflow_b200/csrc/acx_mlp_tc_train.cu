@@ -35,6 +35,7 @@ struct TtSmem {
   float X2[H2 * MS];
   float X3[128 * MS];          // X3 / dPre3, later the recomputed X1 block / dPre1 block
   float slot[TT_NSLOT][TT_SLOT_FLOATS];
+  static constexpr int OBW = MAX_OB;
   float obs[MAX_OB * MT];
   float W1[MAX_OB * 256];
   float b1[256];

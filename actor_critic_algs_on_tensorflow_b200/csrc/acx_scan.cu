@@ -120,65 +120,83 @@ __global__ void __launch_bounds__(256) acx_scan_cols_kernel(int T, int N, const 
   scan_finish_moments(m, ws, stats, (long long)T * N);
 }
 
-// Plain (T <= L) column scan, four adjacent env columns per thread: every row access of a warp is one
-// 512-byte burst (float4 rew / V / G / adv, uchar4 done).  Same arithmetic as acx_scan_cols_kernel.
-// CHUNK rows are loaded before the first is used.  <4, 256>: wide batches (>= 2 CTAs per SM at 4 columns per thread);
-// <10, 64>: narrow ones (65,536 columns = 16,384 threads), where small CTAs spread the columns over every SM and the
-// deep chunk puts half of a 20-row column's loads in flight at once -- the kernel is latency-bound there.
-template <int CHUNK, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) acx_scan_cols4_kernel(int T, int N, const float* __restrict__ rew,
+// Plain (T <= L) column scan, VEC adjacent env columns per thread (VEC = 4: every row access of a warp is one 512-byte
+// burst -- float4 rew / V / G / adv, uchar4 done; VEC = 1: 128-byte bursts, four times the threads).  Same arithmetic as
+// acx_scan_cols_kernel.  CHUNK rows are loaded before the first is used.
+//   <4, 4, 256>   wide batches (>= 2 CTAs per SM at 4 columns per thread): HBM-bound, 66 % (1M columns) to 78 % (8M) of the
+//                 measured copy bandwidth (ncu dram bytes / duration, profiles/r02_ncu_hbm.md);
+//   <1, 10, 128>  narrow ones.  At 65,536 columns 4 columns per thread are 16,384 threads = 3.5 warps per SM, and the
+//                 kernel is bound by the instruction latency of those few warps (20 us for 22 MB); one column per thread
+//                 gives 14 warps per SM and half a 20-row column's loads in flight per thread.
+template <int VEC, int CHUNK, int BLOCK>
+__global__ void __launch_bounds__(BLOCK) acx_scan_plain_kernel(int T, int N, const float* __restrict__ rew,
                                                                const unsigned char* __restrict__ done,
                                                                const float* __restrict__ V, double gamma,
                                                                float* __restrict__ G, float* __restrict__ adv,
                                                                ScanWs* ws, float* __restrict__ stats) {
   double m[SCAN_NMOM] = {0, 0, 0, 0, 0, 0, 0};
-  const int N4 = N >> 2;
-  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < N4; q += gridDim.x * blockDim.x) {
-    const int n = q << 2;
-    const float4 vT = __ldg(reinterpret_cast<const float4*>(V + (size_t)T * N + n));
+  const int NV = N / VEC;
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < NV; q += gridDim.x * blockDim.x) {
+    const int n = q * VEC;
     // fp32 recurrence: T <= look_ahead steps of r + gamma * x carry ~T * 2^-24 of relative error, far inside the
     // 1e-5 budget, and keep the kernel on the HBM roofline (the fp64 pipe and its converts are ~10x slower)
     const float gf = (float)gamma, glo = (float)(gamma - (double)(float)gamma);   // gamma = gf + glo to ~2^-48
-    float carry[4] = {0.f, 0.f, 0.f, 0.f};
-    float boot[4] = {vT.x, vT.y, vT.z, vT.w};
+    float carry[VEC], boot[VEC];
+    if (VEC == 4) {
+      const float4 vT = __ldg(reinterpret_cast<const float4*>(V + (size_t)T * N + n));
+      boot[0] = vT.x; boot[VEC > 1 ? 1 : 0] = vT.y; boot[VEC > 2 ? 2 : 0] = vT.z; boot[VEC > 3 ? 3 : 0] = vT.w;
+    } else {
+      boot[0] = __ldg(V + (size_t)T * N + n);
+    }
+#pragma unroll
+    for (int c = 0; c < VEC; ++c) carry[c] = 0.f;
     for (int t1 = T; t1 > 0; t1 -= CHUNK) {
       const int cnt = t1 < CHUNK ? t1 : CHUNK;
-      float4 r[CHUNK], v[CHUNK];
-      uchar4 d[CHUNK];
+      float r[CHUNK][VEC], v[CHUNK][VEC];
+      unsigned char d[CHUNK][VEC];
 #pragma unroll
       for (int i = 0; i < CHUNK; ++i)
         if (i < cnt) {
           const size_t off = (size_t)(t1 - 1 - i) * N + n;
-          r[i] = __ldg(reinterpret_cast<const float4*>(rew + off));
-          v[i] = __ldg(reinterpret_cast<const float4*>(V + off));
-          d[i] = __ldg(reinterpret_cast<const uchar4*>(done + off));
+          if (VEC == 4) {
+            const float4 r4 = __ldg(reinterpret_cast<const float4*>(rew + off));
+            const float4 v4 = __ldg(reinterpret_cast<const float4*>(V + off));
+            const uchar4 d4 = __ldg(reinterpret_cast<const uchar4*>(done + off));
+            r[i][0] = r4.x; r[i][VEC > 1 ? 1 : 0] = r4.y; r[i][VEC > 2 ? 2 : 0] = r4.z; r[i][VEC > 3 ? 3 : 0] = r4.w;
+            v[i][0] = v4.x; v[i][VEC > 1 ? 1 : 0] = v4.y; v[i][VEC > 2 ? 2 : 0] = v4.z; v[i][VEC > 3 ? 3 : 0] = v4.w;
+            d[i][0] = d4.x; d[i][VEC > 1 ? 1 : 0] = d4.y; d[i][VEC > 2 ? 2 : 0] = d4.z; d[i][VEC > 3 ? 3 : 0] = d4.w;
+          } else {
+            r[i][0] = __ldg(rew + off); v[i][0] = __ldg(V + off); d[i][0] = __ldg(done + off);
+          }
         }
+      float p[SCAN_NMOM] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};      // this chunk's CHUNK x VEC samples, fp32
 #pragma unroll
       for (int i = 0; i < CHUNK; ++i)
         if (i < cnt) {
           const size_t off = (size_t)(t1 - 1 - i) * N + n;
-          const float rr[4] = {r[i].x, r[i].y, r[i].z, r[i].w}, vv[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-          const unsigned char dd[4] = {d[i].x, d[i].y, d[i].z, d[i].w};
-          float g[4], a[4];
-          float p[SCAN_NMOM] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};      // this row's four columns, fp32
+          float g[VEC], a[VEC];
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            if (dd[c]) { carry[c] = 0.f; boot[c] = 0.f; }
+          for (int c = 0; c < VEC; ++c) {
+            if (d[i][c]) { carry[c] = 0.f; boot[c] = 0.f; }
             const float x = carry[c] + boot[c];
-            carry[c] = fmaf(gf, x, fmaf(glo, x, rr[c]));
+            carry[c] = fmaf(gf, x, fmaf(glo, x, r[i][c]));
             boot[c] = 0.f;
             g[c] = carry[c];
-            a[c] = carry[c] - vv[c];
+            a[c] = carry[c] - v[i][c];
             p[0] += a[c]; p[1] = fmaf(a[c], a[c], p[1]);
             p[2] += g[c]; p[3] = fmaf(g[c], g[c], p[3]);
-            p[4] += vv[c]; p[5] = fmaf(vv[c], vv[c], p[5]);
-            p[6] = fmaf(g[c], vv[c], p[6]);
+            p[4] += v[i][c]; p[5] = fmaf(v[i][c], v[i][c], p[5]);
+            p[6] = fmaf(g[c], v[i][c], p[6]);
           }
-#pragma unroll
-          for (int k = 0; k < SCAN_NMOM; ++k) m[k] += (double)p[k];
-          *reinterpret_cast<float4*>(G + off) = make_float4(g[0], g[1], g[2], g[3]);
-          *reinterpret_cast<float4*>(adv + off) = make_float4(a[0], a[1], a[2], a[3]);
+          if (VEC == 4) {
+            *reinterpret_cast<float4*>(G + off) = make_float4(g[0], g[VEC > 1 ? 1 : 0], g[VEC > 2 ? 2 : 0], g[VEC > 3 ? 3 : 0]);
+            *reinterpret_cast<float4*>(adv + off) = make_float4(a[0], a[VEC > 1 ? 1 : 0], a[VEC > 2 ? 2 : 0], a[VEC > 3 ? 3 : 0]);
+          } else {
+            G[off] = g[0]; adv[off] = a[0];
+          }
         }
+#pragma unroll
+      for (int k = 0; k < SCAN_NMOM; ++k) m[k] += (double)p[k];
     }
   }
   scan_finish_moments(m, ws, stats, (long long)T * N);
@@ -300,12 +318,11 @@ static int scan_launch(int T, int n, const float* rew, const unsigned char* done
     acx_scan_warp_kernel<<<grid(n, 8), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out, adv_out, ws,
                                                      stats_out);
   else if (T <= look_ahead && (n & 3) == 0 && acx_aligned16(rew) && acx_aligned16(V) && acx_aligned16(G_out) &&
-           acx_aligned16(adv_out) && (reinterpret_cast<uintptr_t>(done) & 3u) == 0) {
-    if (n / 4 >= 2 * 256 * acx_num_sms())
-      acx_scan_cols4_kernel<4, 256><<<grid(n / 4, 256), 256, 0, st>>>(T, n, rew, done, V, gamma, G_out, adv_out, ws,
-                                                                      stats_out);
-    else
-      acx_scan_cols4_kernel<10, 64><<<grid(n / 4, 64), 64, 0, st>>>(T, n, rew, done, V, gamma, G_out, adv_out, ws,
+           acx_aligned16(adv_out) && (reinterpret_cast<uintptr_t>(done) & 3u) == 0 && n / 4 >= 2 * 256 * acx_num_sms()) {
+    acx_scan_plain_kernel<4, 4, 256><<<grid(n / 4, 256), 256, 0, st>>>(T, n, rew, done, V, gamma, G_out, adv_out, ws,
+                                                                       stats_out);
+  } else if (T <= look_ahead) {
+    acx_scan_plain_kernel<1, 10, 128><<<grid(n, 128), 128, 0, st>>>(T, n, rew, done, V, gamma, G_out, adv_out, ws,
                                                                     stats_out);
   } else
     acx_scan_cols_kernel<<<grid(n, 256), 256, 0, st>>>(T, n, rew, done, V, gamma, look_ahead, G_out, adv_out, ws,

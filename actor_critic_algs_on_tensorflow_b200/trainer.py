@@ -93,9 +93,13 @@ class A2CTrainer:
         # Framer (A3C/process.py:25-43, --frames k): the networks see the last k observations of the episode
         self.frames = int(frames)
         self.ob = self.env_ob * self.frames
-        if self.frames < 1 or self.ob > 8:
-            raise L.AcxError("frames=%d: the MLP kernels take at most 8 input features (%d observation components x "
+        if self.frames < 1 or self.ob > 24:
+            raise L.AcxError("frames=%d: the MLP kernels take at most 24 input features (%d observation components x "
                              "frames)" % (self.frames, self.env_ob))
+        # more than 8 network inputs (Pendulum / CartPole from 3 frames, Acrobot from 2): the tensor-core kernels keep
+        # shared memory for the weights and take 8; the FFMA engine takes 24 and runs the whole path then
+        if self.ob > 8:
+            tensor_cores = False
         self.cont = self.n_act == 0
         self.num_ac = 1 if self.cont else self.n_act
         self.ac_scale = 2.0                       # max(|low|, high) of Pendulum (A3C/process.py:186)

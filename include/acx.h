@@ -119,7 +119,9 @@ int acx_env_step_acrobot(int n, float* state, int* elapsed, const int* action, f
  * oldest first, a fresh episode padded with copies of its first observation.  prev[frames*ob_dim][n] is the stacked
  * input one step earlier (NULL: no history, e.g. right after acx_env_reset), obs[ob_dim][n] the new observation,
  * done[n] the done flags of the transition that produced it (NULL: none ended); out[frames*ob_dim][n] must not
- * alias prev.  The MLP entry points then run with ob_dim = frames * ob_dim (<= 8). */
+ * alias prev.  The MLP entry points then run with ob_dim = frames * ob_dim: at most 24 on the FFMA entry points (three
+ * frames of Acrobot's six observations: stack_frames = 3 is the default of A3C/process.py:156-157), at most 8 on the
+ * *_tc ones, whose shared memory belongs to the weights. */
 int acx_frame_push(int n, int ob_dim, int frames, const float* prev, const float* obs, const unsigned char* done,
                    float* out, void* stream);
 

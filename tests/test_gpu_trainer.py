@@ -89,10 +89,28 @@ def test_frame_stacking_matches_oracle(env_id, env, N, T):
         np.testing.assert_array_equal(o[t + 1, :ob][:, ~cont], o[t + 1, ob:][:, ~cont])
 
 
+@pytest.mark.parametrize("env_id,env,N,T", [("Pendulum-v0", E.PENDULUM, 256, 8), ("CartPole-v0", E.CARTPOLE, 192, 12),
+                                            ("Acrobot-v1", E.ACROBOT, 128, 6)])
+def test_three_stacked_frames_match_oracle(env_id, env, N, T):
+    """stack_frames = 3, the default of the reference's process_fn (A3C/process.py:156-157): 9 / 12 / 18 network inputs,
+    beyond the 8 of the tensor-core kernels -- the trainer runs the FFMA engine (24 inputs) and matches the oracle."""
+    ms = 5 if env != E.PENDULUM else 4
+    S = a2c.A2CState(env, N, seed=41, frames=3, stagger=True, max_steps=ms)
+    tr = A2CTrainer(env_id, n_envs=N, horizon=T, seed=41, actor_params=S.actor.copy(), critic_params=S.critic.copy(),
+                    use_graph=False, max_episode_steps=ms, frames=3)
+    assert tr.ob == 3 * E.OBS_DIM[env] and not tr.tc
+    for _ in range(2):
+        tr.iteration()
+        torch.cuda.synchronize()
+        st = a2c.iteration(S, T=T, max_steps=ms)
+        _cmp_iteration(tr, st, env == E.PENDULUM)
+    assert tr.done.sum().item() > 0
+
+
 def test_frames_beyond_the_kernel_input_width_are_refused():
     from actor_critic_algs_on_tensorflow_b200 import _lib
-    with pytest.raises(_lib.AcxError, match="at most 8 input features"):
-        A2CTrainer("Pendulum-v0", n_envs=64, horizon=2, frames=3)
+    with pytest.raises(_lib.AcxError, match="at most 24 input features"):
+        A2CTrainer("Acrobot-v1", n_envs=64, horizon=2, frames=5)
 
 
 @pytest.mark.parametrize("env_id,N,T,max_steps", [("Pendulum-v0", 1024, 6, 3), ("Pendulum-v0", 200, 5, 0),
