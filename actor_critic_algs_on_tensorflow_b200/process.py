@@ -265,8 +265,9 @@ def save_checkpoint(save_path, basename, gstep, actor_tensors, critic_tensors, k
     return prefix
 
 
-def trainer_checkpoint_tensors(tr):
-    """The 22 tensors of the reference's Saver, named as in SURVEY.md Appendix A, from a trainer's flat buffers."""
+def trainer_checkpoint_tensors(tr, actor_scope="global_actor", critic_scope="global_critic"):
+    """The 22 tensors of the reference's Saver, named as in SURVEY.md Appendix A, from a trainer's flat buffers
+    (Basic_AC's variable scopes are ``Actor`` / ``Critic``, Basic_AC/policies.py:40,129)."""
     head = "mu_layer" if tr.cont else "logits"
     a = tr.actor.cpu().numpy()
     c = tr.critic.cpu().numpy()
@@ -278,33 +279,35 @@ def trainer_checkpoint_tensors(tr):
     def pick(flat, lay, name, shape):
         off, sz = lay[name]
         return flat[off:off + sz].reshape(shape).copy()
-    at = {"global_actor/Variable": np.float32(op[L.OPT_ACTOR_LR]), "global_actor/Variable_1": np.float32(op[L.OPT_GAMMA_ENT]),
-          "global_actor/Variable_2": np.float32(op[L.OPT_BETA_KL])}
+    ga, gc = actor_scope + "/", critic_scope + "/"
+    at = {ga + "Variable": np.float32(op[L.OPT_ACTOR_LR]), ga + "Variable_1": np.float32(op[L.OPT_GAMMA_ENT]),
+          ga + "Variable_2": np.float32(op[L.OPT_BETA_KL])}
     dims = [tr.ob] + list(ha) + [tr.num_ac]
     for i, (layer, w, b) in enumerate((("first_layer", "W1", "b1"), ("second_layer", "W2", "b2"),
                                        ("third_layer", "W3", "b3"), (head, "Wh", "bh"))):
-        at["global_actor/%s/kernel" % layer] = pick(a, la, w, (dims[i], dims[i + 1]))
-        at["global_actor/%s/bias" % layer] = pick(a, la, b, (dims[i + 1],))
+        at[ga + "%s/kernel" % layer] = pick(a, la, w, (dims[i], dims[i + 1]))
+        at[ga + "%s/bias" % layer] = pick(a, la, b, (dims[i + 1],))
     if tr.cont:
-        at["global_actor/log_std"] = pick(a, la, "log_std", (tr.num_ac,))
-    ct = {"global_critic/Variable": np.float32(op[L.OPT_CRITIC_LR]), "global_critic/Variable_1": np.float32(op[L.OPT_CRITIC_LR])}
+        at[ga + "log_std"] = pick(a, la, "log_std", (tr.num_ac,))
+    ct = {gc + "Variable": np.float32(op[L.OPT_CRITIC_LR]), gc + "Variable_1": np.float32(op[L.OPT_CRITIC_LR])}
     dims = [tr.ob] + list(hc) + [1]
     for i, (layer, w, b) in enumerate((("first_layer", "W1", "b1"), ("second_layer", "W2", "b2"),
                                        ("third_layer", "W3", "b3"), ("value", "Wh", "bh"))):
-        ct["global_critic/%s/kernel" % layer] = pick(c, lc, w, (dims[i], dims[i + 1]))
-        ct["global_critic/%s/bias" % layer] = pick(c, lc, b, (dims[i + 1],))
+        ct[gc + "%s/kernel" % layer] = pick(c, lc, w, (dims[i], dims[i + 1]))
+        ct[gc + "%s/bias" % layer] = pick(c, lc, b, (dims[i + 1],))
     return at, ct
 
 
-def _emit_log_rows(tr, logger, task_id, first, count, stdout_freq):
+def _emit_log_rows(tr, logger, task_id, first, count, stdout_freq, rows=None):
     """One logger row per iteration (A3C/process.py:280-281) from the trainer's device ring: a single read-back for
-    ``count`` iterations."""
+    ``count`` iterations.  ``task_id`` None: the Basic_AC row, which has no worker_id (Basic_AC/run_AC.py:277-278)."""
     if logger is None or count <= 0:
         return
-    for j, row in enumerate(tr.read_log(first, count), start=first):
-        logger(j, act_loss=row['act_loss'], worker_id=task_id, act_lr=row['act_lr'], kl_dist=row['kl_dist'],
+    extra = {} if task_id is None else {"worker_id": task_id}
+    for j, row in enumerate(rows if rows is not None else tr.read_log(first, count), start=first):
+        logger(j, act_loss=row['act_loss'], act_lr=row['act_lr'], kl_dist=row['kl_dist'],
                circ_loss=np.sqrt(max(row['crit_loss'], 0.0)), avg_rew=row['avg_rew'], ev_before=row['ev_before'],
-               ev_after=row['ev_after'], print_tog=(j % max(1, stdout_freq)) == 0, avg_ent=row['avg_ent'])
+               ev_after=row['ev_after'], print_tog=(j % max(1, stdout_freq)) == 0, avg_ent=row['avg_ent'], **extra)
         if j % 100 == 50:
             logger.flush()
 

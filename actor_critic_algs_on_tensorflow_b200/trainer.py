@@ -84,7 +84,7 @@ class A2CTrainer:
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
                  critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=True,
                  cache_activations=True, tensor_core_backward=True, frames=1, fused_rollout=True, stagger=True,
-                 diagnostics=False, log_rows=128):
+                 diagnostics=False, log_rows=128, basic=False):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
@@ -100,6 +100,10 @@ class A2CTrainer:
         # shared memory for the weights and take 8; the FFMA engine takes 24 and runs the whole path then
         if self.ob > 8:
             tensor_cores = False
+        # Basic_AC's critic: the value head reads the SECOND hidden layer, the third layer is dead weight and never gets a
+        # gradient (Basic_AC/policies.py:134-135).  Its other differences are plain arguments: clip=1.0 (:81), max_lr=1.0
+        # (Basic_AC/run_AC.py:178).  The actor is the same network and runs on the same kernels.
+        self.basic = bool(basic)
         self.cont = self.n_act == 0
         self.num_ac = 1 if self.cont else self.n_act
         self.ac_scale = 2.0                       # max(|low|, high) of Pendulum (A3C/process.py:186)
@@ -295,13 +299,14 @@ class A2CTrainer:
         s, N, T = L.cur_stream(), self.N, self.T
         if self.tc:
             L.call("acx_value_forward_tc", L.ptr(self.critic), L.ptr(self.packed_c), self.ob, T + 1, N,
-                   L.ptr(self.obs_buf), L.ptr(self.V), 0, L.ptr(self.cx2) if self.cache else None,
+                   L.ptr(self.obs_buf), L.ptr(self.V), int(self.basic), L.ptr(self.cx2) if self.cache else None,
                    L.ptr(self.cx3) if self.cache else None, L.ptr(self.cmask), s)
         elif self.cache:
             L.call("acx_value_forward_cached", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V),
-                   0, L.ptr(self.cx2), L.ptr(self.cx3), s)
+                   int(self.basic), L.ptr(self.cx2), L.ptr(self.cx3), s)
         else:
-            L.call("acx_value_forward", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V), 0, s)
+            L.call("acx_value_forward", L.ptr(self.critic), self.ob, T + 1, N, L.ptr(self.obs_buf), L.ptr(self.V),
+                   int(self.basic), s)
         L.call("acx_returns_adv_scan", T, N, L.ptr(self.rew), L.ptr(self.done), L.ptr(self.V), self.gamma,
                self.look_ahead, L.ptr(self.G), L.ptr(self.adv), L.ptr(self.stats), L.ptr(self.ws_scan),
                self.ws_scan_bytes, L.SCAN_AUTO, s)
@@ -309,30 +314,38 @@ class A2CTrainer:
         common = (L.ptr(self.obs_buf), L.ptr(self.acs), L.ptr(self.adv), L.ptr(self.stats), L.ptr(self.logps),
                   L.ptr(self.G), L.ptr(self.opt), L.ptr(ga), L.ptr(gc), L.ptr(self.stats), L.ptr(self.ws_bwd),
                   self.ws_bwd_bytes, s)
+        critic_ptr, extra = L.ptr(self.critic), 0
+        if self.basic:
+            # the Basic_AC critic first (FFMA kernel with the head on layer 2; the third layer's gradient is zero, as TF
+            # reports None for it), then the actor alone through the engine's usual entry point
+            L.call("acx_loss_backward_basic_critic", L.ptr(self.critic), self.ob, T, N, L.ptr(self.obs_buf), L.ptr(self.G),
+                   L.ptr(gc), L.ptr(self.stats), L.ptr(self.ws_bwd), self.ws_bwd_bytes, s)
+            critic_ptr, extra = None, 3
         if self.tc_bwd:
             cached = (common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3), L.ptr(self.amask),
                                      L.ptr(self.cmask)) + common[-3:])
-            head = (L.ptr(self.actor), L.ptr(self.critic), L.ptr(self.packed_bwd_a), L.ptr(self.packed_bwd_c), self.ob)
+            head = (L.ptr(self.actor), critic_ptr, L.ptr(self.packed_bwd_a), L.ptr(self.packed_bwd_c), self.ob)
             if self.cont:
                 L.call("acx_loss_backward_gauss_tc", *head, self.num_ac, self.ac_scale, T, N, *cached)
             else:
                 L.call("acx_loss_backward_cat_tc", *head, self.n_act, T, N, *cached)
             split = self.N % 4 == 0
-            return 2 + (8 if split else 4)      # value, scan, 2 x (chain, dW3 kernel, dW2 kernel, grad reduce | train, reduce)
+            per_net = 4 if split else 2         # chain, dW3 kernel, dW2 kernel, grad reduce | train, reduce
+            return 2 + extra + per_net * (1 if self.basic else 2)      # value, scan, ...
         if self.cache:
             cached = common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3)) + common[-3:]
             if self.cont:
-                L.call("acx_loss_backward_gauss_cached", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.num_ac,
+                L.call("acx_loss_backward_gauss_cached", L.ptr(self.actor), critic_ptr, self.ob, self.num_ac,
                        self.ac_scale, T, N, *cached)
             else:
-                L.call("acx_loss_backward_cat_cached", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.n_act, T, N,
+                L.call("acx_loss_backward_cat_cached", L.ptr(self.actor), critic_ptr, self.ob, self.n_act, T, N,
                        *cached)
         elif self.cont:
-            L.call("acx_loss_backward_gauss", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.num_ac,
+            L.call("acx_loss_backward_gauss", L.ptr(self.actor), critic_ptr, self.ob, self.num_ac,
                    self.ac_scale, T, N, *common)
         else:
-            L.call("acx_loss_backward_cat", L.ptr(self.actor), L.ptr(self.critic), self.ob, self.n_act, T, N, *common)
-        return 2 + 6      # value, scan, 2 x (transpose, mlp train, grad reduce)
+            L.call("acx_loss_backward_cat", L.ptr(self.actor), critic_ptr, self.ob, self.n_act, T, N, *common)
+        return 2 + extra + (3 if self.basic else 6)      # value, scan, per net (transpose, mlp train, grad reduce)
 
     def _apply(self, grad_scale):
         s, Pa, Pc = L.cur_stream(), self.Pa, self.Pc
@@ -374,9 +387,10 @@ class A2CTrainer:
         s, N, T = L.cur_stream(), self.N, self.T
         if self.tc:
             L.call("acx_value_forward_tc", L.ptr(self.critic), L.ptr(self.packed_c), self.ob, T, N, L.ptr(self.obs_buf),
-                   L.ptr(self.V_after), 0, None, None, None, s)
+                   L.ptr(self.V_after), int(self.basic), None, None, None, s)
         else:
-            L.call("acx_value_forward", L.ptr(self.critic), self.ob, T, N, L.ptr(self.obs_buf), L.ptr(self.V_after), 0, s)
+            L.call("acx_value_forward", L.ptr(self.critic), self.ob, T, N, L.ptr(self.obs_buf), L.ptr(self.V_after),
+                   int(self.basic), s)
         L.call("acx_explained_variance", T * N, L.ptr(self.G), L.ptr(self.V_after),
                self.stats.data_ptr() + 4 * L.STAT_EV_AFTER, L.ptr(self.ws_diag), self.ws_diag_bytes, s)
         return 2

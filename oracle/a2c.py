@@ -20,10 +20,11 @@ from .pathadv import linear_schedule_val, path_adv_columns, var_accounted_for
 class A2CState:
     def __init__(self, env, n_envs, seed=12321, rank=0, world=1, frames=1, dtype=np.float32,
                  actor=None, critic=None, actor_lr=0.005, critic_lr=0.001, beta=1.0, gamma_ent=0.01, stagger=False,
-                 max_steps=None):
+                 max_steps=None, basic=False):
         self.env, self.N, self.seed, self.rank, self.world = env, n_envs, seed, rank, world
         self.f = dtype
         self.cont = env == E.PENDULUM
+        self.basic = bool(basic)                       # Basic_AC critic: value head on the second layer (policies.py:134-135)
         self.frames = int(frames)                      # Framer (A3C/process.py:25-43): network input = last k observations
         self.env_ob = E.OBS_DIM[env]
         self.ob_dim = self.env_ob * self.frames
@@ -101,13 +102,13 @@ def update(S, ro, gamma=0.98, look_ahead=40, desired_kl=0.002, min_lr=1e-6, max_
     T = ro["rew"].shape[0]
     B = T * S.N
     obs_all = ro["obs"].transpose(0, 2, 1).reshape((T + 1) * S.N, S.ob_dim)
-    V = P.critic_value(S.critic, S.clay, obs_all, dtype=f).reshape(T + 1, S.N)
+    V = P.critic_value(S.critic, S.clay, obs_all, basic_head=S.basic, dtype=f).reshape(T + 1, S.N)
     G, adv = path_adv_columns(ro["rew"], ro["done"], V, gamma, look_ahead, dtype=np.float64)
     advn = P.normalize_adv(adv.reshape(-1)).astype(f)
     obs = obs_all[:B]
     acs = ro["acs"].transpose(0, 2, 1).reshape(B, -1) if S.cont else ro["acs"].reshape(B)
     lp_old = ro["logps"].reshape(B)
-    cg = P.critic_loss_grads(S.critic, S.clay, obs, G.reshape(-1).astype(f), dtype=grad_dtype)
+    cg = P.critic_loss_grads(S.critic, S.clay, obs, G.reshape(-1).astype(f), basic_head=S.basic, dtype=grad_dtype)
     ag = P.actor_loss_grads(S.actor, S.alay, obs, acs, advn, lp_old, S.beta, S.gamma_ent, S.cont,
                             S.ac_scale, clip=None, dtype=grad_dtype)
     g_c, g_a = cg["grad"].astype(np.float32), ag["grad_raw"].astype(np.float32)
@@ -121,7 +122,7 @@ def update(S, ro, gamma=0.98, look_ahead=40, desired_kl=0.002, min_lr=1e-6, max_
     kl = float(np.mean((lp_old.astype(np.float64) - lp_new.astype(np.float64)) ** 2))
     ev_before = float(var_accounted_for(target=G.reshape(-1), pred=V[:T].reshape(-1).astype(np.float64)))
     ev_after = float(var_accounted_for(target=G.reshape(-1), pred=P.critic_value(
-        S.critic, S.clay, obs, dtype=f).astype(np.float64))) if diagnostics else None
+        S.critic, S.clay, obs, basic_head=S.basic, dtype=f).astype(np.float64))) if diagnostics else None
     if allreduce is not None:
         kl = float(allreduce(np.array([kl]))[0])
     stats = dict(actor_loss=float(ag["loss"]), critic_loss=float(cg["loss"]), kl=kl, actor_lr=S.actor_lr,

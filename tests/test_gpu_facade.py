@@ -8,7 +8,7 @@ import pytest
 import torch
 
 from oracle import envs as E, policies as P
-from actor_critic_algs_on_tensorflow_b200 import envs, policies as pol, process, util as U
+from actor_critic_algs_on_tensorflow_b200 import envs, policies as pol, process, tf_bundle, util as U
 from gpu_util import GOLDEN, demo_weights
 
 pytestmark = pytest.mark.gpu
@@ -178,11 +178,14 @@ def test_process_fn_and_run_ac_smoke(tmp_path, capsys):
     files = sorted(os.listdir("ck"))
     assert "checkpoint" in files and any(f.startswith("model-CartPole-") and f.endswith(".index") for f in files)
     log = open(os.path.join("logs", "worker_0.log")).read().splitlines()
-    assert log[0] == "step avg_rew ev_before ev_after act_loss crit_loss kl_dist avg_ent" and len(log) >= 3
+    assert log[0] == "step avg_rew ev_before ev_after act_loss crit_loss kl_dist avg_ent" and len(log) == 5    # one row per iteration
     assert "Iteration 0" in capsys.readouterr().out
-    actor, critic = run_AC.main(["--env", "CartPole-v0", "--iters", "2", "--outdir", "log.txt", "--checkpoint_dir",
-                                 os.path.join("tmp", "checkpoints"), "--save_every", "1"])
+    tr = run_AC.main(["--env", "CartPole-v0", "--iters", "3", "--outdir", "log.txt", "--checkpoint_dir",
+                      os.path.join("tmp", "checkpoints"), "--save_every", "1", "--n_envs", "64", "--horizon", "100"])
     out = capsys.readouterr().out
-    assert "Discrete Action Space" in out and "Updated gamma from 0.0100 to 0.0100." in out
-    assert any(f.startswith("checkpoints-CartPole-") for f in os.listdir("tmp"))
-    assert np.isfinite(actor.net.params.cpu().numpy()).all()
+    assert "Discrete Action Space" in out and "Iteration 0" in out and "EV After" in out
+    assert any(f.startswith("checkpoints-CartPole-") and f.endswith(".index") for f in os.listdir("tmp"))
+    assert tr.basic and tr.iterations == 3 and np.isfinite(tr.params.cpu().numpy()).all()
+    t = tf_bundle.read_bundle(os.path.join("tmp", sorted(f for f in os.listdir("tmp") if f.endswith(".index"))[0][:-6]))
+    assert "Actor/logits/kernel" in t and "Critic/value/kernel" in t and t["Critic/third_layer/kernel"].shape == (128, 128)
+    assert len(open("log.txt").read().splitlines()) == 4

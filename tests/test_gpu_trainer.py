@@ -10,7 +10,7 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import a2c, envs as E, philox as R
+from oracle import a2c, envs as E, philox as R, policies as P
 from actor_critic_algs_on_tensorflow_b200.trainer import A2CTrainer
 from actor_critic_algs_on_tensorflow_b200 import process, tf_bundle
 
@@ -18,7 +18,7 @@ pytestmark = pytest.mark.gpu
 GRAD_TOL = 1e-4      # measured on B200: 1e-7 .. 3.1e-5 over the cases below
 
 
-def _cmp_iteration(tr, st, cont):
+def _cmp_iteration(tr, st, cont, clip=0.1):
     ro = st["rollout"]
     np.testing.assert_array_equal(tr.done.cpu().numpy(), ro["done"])
     np.testing.assert_allclose(tr.rew.cpu().numpy(), ro["rew"], rtol=1e-4, atol=1e-4)
@@ -31,7 +31,7 @@ def _cmp_iteration(tr, st, cont):
     np.testing.assert_allclose(tr.V.cpu().numpy(), st["V"], rtol=1e-4, atol=1e-4)
     np.testing.assert_allclose(tr.G.cpu().numpy(), st["G"], rtol=2e-4, atol=2e-4)
     ga, gc = tr.grads[:tr.Pa].cpu().numpy(), tr.grads[tr.Pa:].cpu().numpy()
-    for name, g, w in (("actor", np.clip(ga, -0.1, 0.1), st["grad_actor"]), ("critic", gc, st["grad_critic"])):
+    for name, g, w in (("actor", np.clip(ga, -clip, clip), st["grad_actor"]), ("critic", gc, st["grad_critic"])):
         err = np.abs(g - w).max() / np.abs(w).max()
         print("trainer vs oracle, %s gradient: %.2e of max" % (name, err))
         assert err <= GRAD_TOL
@@ -105,6 +105,31 @@ def test_three_stacked_frames_match_oracle(env_id, env, N, T):
         st = a2c.iteration(S, T=T, max_steps=ms)
         _cmp_iteration(tr, st, env == E.PENDULUM)
     assert tr.done.sum().item() > 0
+
+
+@pytest.mark.parametrize("tensor_cores", [False, True])
+@pytest.mark.parametrize("env_id,env,N,T", [("CartPole-v0", E.CARTPOLE, 192, 12), ("Pendulum-v0", E.PENDULUM, 256, 8)])
+def test_basic_ac_mode_matches_oracle(env_id, env, N, T, tensor_cores):
+    """basic=True (BASELINE.json configs[0], Basic_AC/run_AC.py): the critic's value head reads the second layer and its
+    third layer gets no gradient (Basic_AC/policies.py:134-135), actor clip +-1 (:81), max_lr 1 (run_AC.py:178) --
+    rollout, returns, gradients, update and lr against the oracle run with the same switches, two iterations."""
+    ms = 5 if env != E.PENDULUM else 6
+    S = a2c.A2CState(env, N, seed=51, stagger=True, max_steps=ms, basic=True)
+    tr = A2CTrainer(env_id, n_envs=N, horizon=T, seed=51, actor_params=S.actor.copy(), critic_params=S.critic.copy(),
+                    use_graph=False, max_episode_steps=ms, tensor_cores=tensor_cores, basic=True, clip=1.0, max_lr=1.0,
+                    diagnostics=True)
+    c0 = tr.critic.cpu().numpy().copy()
+    for _ in range(2):
+        tr.iteration()
+        torch.cuda.synchronize()
+        st = a2c.iteration(S, T=T, max_steps=ms, clip=1.0, max_lr=1.0, diagnostics=True)
+        _cmp_iteration(tr, st, env == E.PENDULUM, clip=1.0)
+    lay = P.critic_layout(tr.ob)
+    for name in ("W3", "b3"):                           # dead third layer: zero gradient, untouched by Adam
+        o, shp = lay[name]
+        sz = int(np.prod(shp))
+        assert not tr.grads[tr.Pa:].cpu().numpy()[o:o + sz].any()
+        np.testing.assert_array_equal(tr.critic.cpu().numpy()[o:o + sz], c0[o:o + sz])
 
 
 def test_frames_beyond_the_kernel_input_width_are_refused():
