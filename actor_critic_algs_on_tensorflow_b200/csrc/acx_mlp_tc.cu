@@ -21,9 +21,18 @@
 #include "acx_mlp.cuh"
 #include "acx_umma.cuh"
 #include "acx_env_dev.cuh"
+#include <stdlib.h>
 
 using namespace acxmlp;
 using namespace acxumma;
+
+// acx_mlp_tc2.cu: the evaluation-mode passes with two tiles in flight per SM (default); ACX_TC_ONE_TILE=1 in the
+// environment keeps them on the one-tile kernel of this file (A/B measurements)
+int acx_tc2_launch(int head, const Args& a, const float* packed, int grid, void* stream);
+static bool tc_two_tiles() {
+  static const bool on = [] { const char* e = getenv("ACX_TC_ONE_TILE"); return !(e && e[0] == '1'); }();
+  return on;
+}
 
 #ifdef ACX_FWD_PROF
 __device__ unsigned long long acx_fwd_prof[16];
@@ -704,6 +713,7 @@ extern "C" int acx_policy_logp_gauss_tc(const float* actor, const float* packed,
   a.params = actor; a.L = acx_actor_layout(ob_dim, ac_dim, 1); a.rows = rows; a.n = n; a.obs = obs;
   a.ac_scale = ac_scale; a.ac_in_f = acs; a.logp_out = logp_out; a.ent_out = ent_out; a.head_out = mu_out;
   a.logp_old = logp_old; a.kl_partial = kl_partial;
+  if (tc_two_tiles()) return acx_tc2_launch(HEAD_GAUSS, a, packed, grid, stream);
   return launch_tc<128, 64, true, HEAD_GAUSS, MODE_EVAL>(a, packed, grid, (cudaStream_t)stream);
 }
 
@@ -723,6 +733,7 @@ extern "C" int acx_policy_logp_cat_tc(const float* actor, const float* packed, i
   a.params = actor; a.L = acx_actor_layout(ob_dim, n_act, 0); a.rows = rows; a.n = n; a.obs = obs;
   a.ac_in_i = acs; a.logp_out = logp_out; a.ent_out = ent_out; a.head_out = logits_out;
   a.logp_old = logp_old; a.kl_partial = kl_partial;
+  if (tc_two_tiles()) return acx_tc2_launch(HEAD_CAT, a, packed, grid, stream);
   return launch_tc<128, 64, true, HEAD_CAT, MODE_EVAL>(a, packed, grid, (cudaStream_t)stream);
 }
 
@@ -738,6 +749,7 @@ extern "C" int acx_value_forward_tc(const float* critic, const float* packed, in
   Args a; memset(&a, 0, sizeof(a));
   a.params = critic; a.L = acx_critic_layout(ob_dim); a.rows = rows; a.n = n; a.obs = obs;
   a.v_out = v_out; a.basic_head = basic_head; a.x2_out = x2_out; a.x3_out = x3_out; a.mask_out = mask_out;
+  if (tc_two_tiles()) return acx_tc2_launch(HEAD_VALUE, a, packed, tc_grid(rows, n), stream);
   return launch_tc<256, 128, false, HEAD_VALUE, MODE_EVAL>(a, packed, tc_grid(rows, n), (cudaStream_t)stream);
 }
 

@@ -34,7 +34,7 @@ int acx_num_sms() {
 
 extern "C" int acx_params_layout(int net, int ob_dim, int num_ac, int cont, int* offsets, int* sizes) {
   ACX_REQUIRE(net == 0 || net == 1, "acx_params_layout: net must be 0 (actor) or 1 (critic), got %d", net);
-  ACX_REQUIRE(ob_dim >= 1 && ob_dim <= 8, "acx_params_layout: ob_dim %d outside [1,8]", ob_dim);
+  ACX_REQUIRE(ob_dim >= 1 && ob_dim <= 24, "acx_params_layout: ob_dim %d outside [1,24]", ob_dim);
   ACX_REQUIRE(net == 1 || (num_ac >= 1 && num_ac <= 4), "acx_params_layout: num_ac %d outside [1,4]", num_ac);
   const AcxNetLayout L = net == 0 ? acx_actor_layout(ob_dim, num_ac, cont) : acx_critic_layout(ob_dim);
   if (offsets) {
