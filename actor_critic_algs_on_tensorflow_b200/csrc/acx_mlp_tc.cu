@@ -26,11 +26,13 @@
 using namespace acxmlp;
 using namespace acxumma;
 
-// acx_mlp_tc2.cu: the evaluation-mode passes with two tiles in flight per SM (default); ACX_TC_ONE_TILE=1 in the
-// environment keeps them on the one-tile kernel of this file (A/B measurements)
+// acx_mlp_tc2.cu: the evaluation-mode passes with two tiles in flight per SM.  Parity-tested like this file's kernel,
+// but measured SLOWER on B200 (value pass 1.00 vs 0.93 ms, log-prob pass 0.68 vs 0.55 ms at 65,536 x 20: both kernels
+// are bound by the workers' instruction issue, not by tensor-pipe idle time -- profiles/r02_forward_experiments.md), so
+// it runs only when ACX_TC_TWO_TILES=1 is set in the environment.
 int acx_tc2_launch(int head, const Args& a, const float* packed, int grid, void* stream);
 static bool tc_two_tiles() {
-  static const bool on = [] { const char* e = getenv("ACX_TC_ONE_TILE"); return !(e && e[0] == '1'); }();
+  static const bool on = [] { const char* e = getenv("ACX_TC_TWO_TILES"); return e && e[0] == '1'; }();
   return on;
 }
 
