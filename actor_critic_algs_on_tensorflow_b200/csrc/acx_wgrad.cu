@@ -75,6 +75,10 @@ __device__ inline void mbar_arrive(unsigned long long* bar) {
 // float4 slot of (row r, 16-byte chunk c) inside a 128-row, 128-byte-swizzled box
 __device__ inline int sw128_f4(int r, int c) { return (r >> 3) * 64 + (r & 7) * 8 + (c ^ (r & 7)); }
 
+__device__ inline void red_add_v4(float4* p, const float4 a) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
+}
+
 __device__ inline float4 lo_of(const float4 x) {
   return make_float4(lo_trunc_tf32(x.x), lo_trunc_tf32(x.y), lo_trunc_tf32(x.z), lo_trunc_tf32(x.w));
 }
@@ -255,16 +259,15 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       float v[32];
       tmem_ld32(tl + (uint32_t)pend_c0, v);
       float4* p = reinterpret_cast<float4*>(scr_row + (pend_phase == 0 ? offW3 : offW2)) + (pend_c0 >> 2) * 128 + r;
-      float4 o[8];
-      if (!pend_first) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) o[i] = p[i * 128];
-      }
+      // the group's first flush stores, the later ones ADD with vector reductions (REDG.ADD.F32x4, round-to-nearest): the
+      // row belongs to this CTA and every address is touched by this one thread, in program order, so the sum is the same
+      // ((p + a1) + a2) ... a load-add-store gives, run to run -- without the L2 round trip of the load on the splitters'
+      // path (with a flush every 2 tiles that round trip cost 5 % of the two kernels)
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        float4 a = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-        if (!pend_first) { a.x += o[i].x; a.y += o[i].y; a.z += o[i].z; a.w += o[i].w; }
-        p[i * 128] = a;
+        const float4 a = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        if (pend_first) p[i * 128] = a;
+        else red_add_v4(p + i * 128, a);
       }
       pend_c0 += 32;
       if (pend_c0 < ncol) return false;
