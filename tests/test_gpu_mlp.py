@@ -184,5 +184,5 @@ def test_forward_rejects_bad_arguments(lib, dev):
     f = lib.load().acx_value_forward
     assert f(t.data_ptr() + 4, 3, 1, 8, t.data_ptr(), t.data_ptr(), 0, None) == -1      # misaligned params
     assert b"aligned" in lib.load().acx_last_error()
-    assert f(t.data_ptr(), 9, 1, 8, t.data_ptr(), t.data_ptr(), 0, None) == -1          # ob_dim too large
+    assert f(t.data_ptr(), 25, 1, 8, t.data_ptr(), t.data_ptr(), 0, None) == -1         # ob_dim too large (FFMA engine: 24)
     assert f(t.data_ptr(), 3, 0, 8, t.data_ptr(), t.data_ptr(), 0, None) == 0           # empty batch: no-op
