@@ -118,6 +118,17 @@ struct TcPipe {
   }
 };
 
+// bit e = (v[e] > 0): the integer image i of a float is > 0 exactly when the float is (+0 -> 0, negatives and -0 -> < 0),
+// and the sign bit of -i is set exactly when i > 0 (or i = INT_MIN = -0.0f, which neither activation produces: relu gives
+// +0, lrelu's 0.8 max(x, 0) + 0.2 x is +0 only from x = +-0 and rounds to +0) -- one negate and one funnel shift per
+// element instead of compare + select + or
+__device__ inline unsigned int pos_mask32(const float (&v)[32]) {
+  unsigned int bits = 0u;
+#pragma unroll
+  for (int e = 31; e >= 0; --e) bits = __funnelshift_l((unsigned int)(-__float_as_int(v[e])), bits, 1);
+  return bits;
+}
+
 // 32 activations of sample `s` (features j0..j0+31) -> A operand columns, hi and lo
 __device__ inline void a_store32(uint32_t tmem_lane, int j0, const float (&v)[32]) {
   // hi = the raw word (kind::tf32 ignores its low 13 mantissa bits), lo = the rounded remainder
@@ -295,8 +306,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         // the Basic_AC head sums then run while the tensor cores form layer 3
         if (A.mask_out != nullptr) {               // act'(X2)
           unsigned int bits = 0u;
-#pragma unroll
-          for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
+          bits = pos_mask32(v);
           A.mask_out[mask_tile_off(tile, H1) + (size_t)(H1 / 32 + gq * 2 + half) * MT + s] = bits;
         }
         if (A.x2_out != nullptr) {                 // tile-blocked cache; zeros beyond the batch
@@ -519,8 +529,7 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         mbar_arrive(&sm.a_ready[gq]);            // features gq*64 .. +63 of the A operand are in place
         if (A.mask_out != nullptr) {             // act'(X1) for the chain kernel (after the hand-over)
           unsigned int bits = 0u;
-#pragma unroll
-          for (int e = 0; e < 32; ++e) bits |= (v[e] > 0.f ? 1u : 0u) << e;
+          bits = pos_mask32(v);
           A.mask_out[mask_tile_off(tile_l, H1) + (size_t)(blk * 4 + gq * 2 + half) * MT + s] = bits;
         }
       }

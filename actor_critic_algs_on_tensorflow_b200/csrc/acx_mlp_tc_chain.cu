@@ -221,6 +221,14 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
           float x[8];
 #pragma unroll
           for (int u = 0; u < 8; ++u) x[u] = Sx[(k0 + u) * MT + tid];
+          if (nout == 1) {                           // same chain, weights by 16-byte loads, no per-output predication
+            const float4 w0 = *reinterpret_cast<const float4*>(&sm.Wh[k0]), w1 = *reinterpret_cast<const float4*>(&sm.Wh[k0 + 4]);
+            float p = pre[0];
+            p = fmaf(x[0], w0.x, p); p = fmaf(x[1], w0.y, p); p = fmaf(x[2], w0.z, p); p = fmaf(x[3], w0.w, p);
+            p = fmaf(x[4], w1.x, p); p = fmaf(x[5], w1.y, p); p = fmaf(x[6], w1.z, p); p = fmaf(x[7], w1.w, p);
+            pre[0] = p;
+            continue;
+          }
 #pragma unroll
           for (int u = 0; u < 8; ++u)
 #pragma unroll
@@ -313,13 +321,24 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
           float v[32];
 #pragma unroll
           for (int e = 0; e < 32; ++e) v[e] = S[(j0 + e) * MT + s];
+          if (nout == 1) {                           // one output: 16-byte weight loads, one product per feature
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            float acc = 0.f;
+            for (int e = 0; e < 32; e += 4) {
+              const float4 w = *reinterpret_cast<const float4*>(&sm.Wh[j0 + e]);
+              v[e] = __fmul_rn(w.x, dh[0]) * act_grad<LRELU>(v[e]);
+              v[e + 1] = __fmul_rn(w.y, dh[0]) * act_grad<LRELU>(v[e + 1]);
+              v[e + 2] = __fmul_rn(w.z, dh[0]) * act_grad<LRELU>(v[e + 2]);
+              v[e + 3] = __fmul_rn(w.w, dh[0]) * act_grad<LRELU>(v[e + 3]);
+            }
+          } else {
 #pragma unroll
-            for (int a = 0; a < MAX_OUT; ++a)
-              if (a < nout) acc = fmaf(sm.Wh[(j0 + e) * nout + a], dh[a], acc);
-            v[e] = acc * act_grad<LRELU>(v[e]);
+            for (int e = 0; e < 32; ++e) {
+              float acc = 0.f;
+#pragma unroll
+              for (int a = 0; a < MAX_OUT; ++a)
+                if (a < nout) acc = fmaf(sm.Wh[(j0 + e) * nout + a], dh[a], acc);
+              v[e] = acc * act_grad<LRELU>(v[e]);
+            }
           }
           a_store32_tt(tl, j0, v);
 #pragma unroll
@@ -432,25 +451,27 @@ acx_mlp_tc_chain_kernel(const Args A, const float* __restrict__ packed, float* _
         {
           // dW1[i][128h + j] += sum_m obs[i][m] dPre1[j][m], db1 likewise: thread (j, sample half), in registers
           const int j = tid & 127, hs = tid >> 7;
-          float sb = 0.f, sw[MAX_OB];
+          // two independent chains per sum (even / odd sample pairs): with one chain per input the 64 dependent FMAs of a
+          // block were latency-bound (15 % of the critic kernel's warp samples, ncu)
+          float sb[2] = {0.f, 0.f}, sw[MAX_OB][2];
 #pragma unroll
-          for (int i = 0; i < MAX_OB; ++i) sw[i] = 0.f;
+          for (int i = 0; i < MAX_OB; ++i) sw[i][0] = sw[i][1] = 0.f;
 #pragma unroll 4
           for (int m4 = 16 * hs; m4 < 16 * hs + 16; ++m4) {
             const float4 d = *reinterpret_cast<const float4*>(S + j * MS + 4 * m4);
-            sb += d.x; sb += d.y; sb += d.z; sb += d.w;
+            sb[0] += d.x; sb[1] += d.y; sb[0] += d.z; sb[1] += d.w;
 #pragma unroll
             for (int i = 0; i < MAX_OB; ++i)
               if (i < ob) {
                 const float4 o = *reinterpret_cast<const float4*>(&sm.obs[i * MT + 4 * m4]);
-                sw[i] = fmaf(o.x, d.x, sw[i]); sw[i] = fmaf(o.y, d.y, sw[i]);
-                sw[i] = fmaf(o.z, d.z, sw[i]); sw[i] = fmaf(o.w, d.w, sw[i]);
+                sw[i][0] = fmaf(o.x, d.x, sw[i][0]); sw[i][1] = fmaf(o.y, d.y, sw[i][1]);
+                sw[i][0] = fmaf(o.z, d.z, sw[i][0]); sw[i][1] = fmaf(o.w, d.w, sw[i][1]);
               }
           }
-          gb1[h] += sb;
+          gb1[h] += sb[0] + sb[1];
 #pragma unroll
           for (int i = 0; i < MAX_OB; ++i)
-            if (i < ob) gW1[h][i] += sw[i];
+            if (i < ob) gW1[h][i] += sw[i][0] + sw[i][1];
           fence_proxy_async();                      // S is next written by the async proxy (X3 prefetch)
           work_sync();
         }
