@@ -597,7 +597,8 @@ __global__ void __launch_bounds__(TC_NT, 1) acx_mlp_tc_kernel(const Args A, cons
         }
         epi_sync();              // the next step's observations (obs_x) are visible to both warpgroups
       }
-      fence_before_sync();       // this tile's tcgen05.ld are ordered before the next a_ready arrive
+      // (no tcgen05 fence here: every a_ready arrive is preceded by its own fence::before_thread_sync, and this tile's
+      // tcgen05.ld have completed -- tmem_ld32 waits for them)
       FPROF(9);
     }
 #ifdef ACX_FWD_PROF

@@ -62,10 +62,13 @@ template <class SM> struct TtPipe {      // SM: slot[TT_NSLOT][TT_SLOT_FLOATS], 
 };
 
 __device__ inline void a_store32_tt(uint32_t tmem_lane, int j0, const float (&v)[32]) {
-  float hi[32], lo[32];
+  // hi = the raw word (kind::tf32 ignores its low 13 mantissa bits), lo = the rounded remainder -- the forward kernels'
+  // split: an AND, a subtract and an integer add per value instead of two cvt.rna.tf32 (conversion-pipe instructions,
+  // 4 % of the chain kernels' warp samples) and a subtract
+  float lo[32];
 #pragma unroll
-  for (int i = 0; i < 32; ++i) split_tf32(v[i], hi[i], lo[i]);
-  tmem_st32(tmem_lane + TT_A_HI + (uint32_t)j0, hi);
+  for (int i = 0; i < 32; ++i) lo[i] = lo_trunc_tf32(v[i]);
+  tmem_st32(tmem_lane + TT_A_HI + (uint32_t)j0, v);
   tmem_st32(tmem_lane + TT_A_LO + (uint32_t)j0, lo);
 }
 
