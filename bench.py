@@ -146,6 +146,33 @@ def b_ref_baselines(seconds=3.0):
     return out
 
 
+def ref_shape_gpu(iters=60):
+    """BASELINE.json configs[0] / configs[1] on the GPU path at the REFERENCE's batch shape (about 800 / 1,200 env steps
+    per update), next to cpu_baseline.b_ref: a batch this small is launch-latency-bound on a B200 -- the numbers say what
+    the drop-in costs a user who changes nothing else, not what the hardware can do."""
+    import torch
+    from actor_critic_algs_on_tensorflow_b200.trainer import A2CTrainer
+    out = {}
+    for key, kw, steps in (("basic_ac_cartpole_8_envs_x_100_steps", dict(env_id="CartPole-v0", n_envs=8, horizon=100, basic=True,
+                                                                           clip=1.0, max_lr=1.0), 800),
+                           ("a3c_pendulum_8_envs_x_150_steps", dict(env_id="Pendulum-v0", n_envs=8, horizon=150), 1200)):
+        tr = A2CTrainer(seed=SEED, **kw)
+        for _ in range(4):
+            tr.iteration()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            tr.iteration()
+        b.record()
+        torch.cuda.synchronize()
+        sec = a.elapsed_time(b) * 1e-3 / iters
+        out[key] = {"value": steps / sec, "unit": "env-steps/s", "ms_per_update": sec * 1e3,
+                    "launches_per_update": tr.launches_per_iteration}
+        del tr
+    return out
+
+
 def run_reference(args, rank):
     """--impl reference: the numpy restatement of the reference's math on the box's host cores, on THIS arm's config
     (65,536 envs x 20 steps per iteration, full size): at 10-30 s per iteration the timed region is capped at 2 iterations
@@ -490,13 +517,15 @@ def run_ours(args, rank, local_rank, world):
                                    "the backward pass) per second; %s" % (peaks_src, bf16_peak, note),
                     "frac_of_fp32_ffma_peak": dom["achieved"] / FP32_PEAK_TFLOPS,
                     "share_of_step": dom["ms"] / step_ms,
-                    # dram__bytes_read.sum + dram__bytes_write.sum of the two kernels, one ncu --set full capture of this
-                    # workload (profiles/r01_ncu_tc_backward.md): chain 0.756 + 1.289 GB, the two wgrad kernels 2.177 + 0.197 GB
-                    "traffic": 4.419e9 if (N_ENVS, HORIZON) == (65536, 20) else None, "traffic_unit": "bytes per launch",
+                    # dram__bytes_read.sum + dram__bytes_write.sum of the group's three kernels per launch, from the ncu
+                    # --set full captures of this workload taken in round 2 (profiles/r02_ncu_step.md: chain 0.756 + 1.289 GB,
+                    # dW3 kernel 1.342 + 0.006 GB, dW2 kernel 0.687 + 0.004 GB) -- NOT measured in this run
+                    "traffic": 4.084e9 if (N_ENVS, HORIZON) == (65536, 20) else None, "traffic_unit": "bytes per launch",
+                    "traffic_source": "profiles/r02_ncu_step.md (ncu --set full, 2026-11-07; not re-measured in this run)",
                     "algorithmic_bytes": 4.09e9 if (N_ENVS, HORIZON) == (65536, 20) else None,
-                    # the same capture: sm__pipe_tc_cycles_active (the MMA instruction rate measured by
+                    # the same captures: sm__pipe_tc_cycles_active (the MMA instruction rate measured by
                     # tests/tc/run_mma_rate.py, 2,007 MAC/clk/SM, is above measured-bf16 / 2, so `frac` flatters the pipe)
-                    "tensor_pipe_active_ncu": {"chain": 0.370, "wgrad": 0.556},
+                    "tensor_pipe_active_ncu": {"chain": 0.369, "wgrad_dW3": 0.555, "wgrad_dW2": 0.562},
                     "hbm_peak_gbs": hbm_peak, "hbm_peak_source": peaks_src}
         else:
             roof = {"kernel": dom_kernel, "bound": "fp32",
@@ -508,6 +537,8 @@ def run_ours(args, rank, local_rank, world):
         total_flops = (FLOP_ACTOR_FWD * (1 + 3 + 1) + FLOP_CRITIC_FWD * (3 + (HORIZON + 1) / HORIZON)) * steps_per_it
         cb_v, cb_sec, cb_sample = (cpu_baseline() if world == 1 else (None, None, None))
         bref = b_ref_baselines(seconds=2.0) if world == 1 else None
+        if bref is not None and args.workload == "pendulum":
+            bref["gpu_same_shape"] = ref_shape_gpu()
         line = {"metric": "env-steps/sec (rollout+update)", "value": value, "unit": "env-steps/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": step_ms, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
@@ -650,7 +681,7 @@ def run_eval(args, rank, local_rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--mode", choices=["sync", "async"], default="sync")
