@@ -20,12 +20,12 @@ def num(r, k):
     return v * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6, "byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "%": 1.0}.get(u, 1.0)
 
 
-print("| kernel | grid x block | us | dram read MB | dram write MB | (read + write) / time, GB/s | dram throughput % of peak |")
+print("| kernel | grid x block | us | dram read MB | dram write MB | (read + write) / time, GB/s | of the measured 6,540 GB/s |")
 print("|---|---|---|---|---|---|---|")
 for r in rows[2:]:
     name = r[col["Kernel Name"]]
     name = name[:name.find("(")] if "(" in name else name
     t, rd, wr = num(r, "gpu__time_duration.sum"), num(r, "dram__bytes_read.sum"), num(r, "dram__bytes_write.sum")
-    print("| `%s` | %s x %s | %.1f | %.1f | %.1f | %.0f | %.1f |" % (
+    print("| `%s` | %s x %s | %.1f | %.1f | %.1f | %.0f | %.1f %% |" % (
         name.replace("void ", ""), r[col["Grid Size"]], r[col["Block Size"]], t, rd / 1e6, wr / 1e6, (rd + wr) / t / 1e3,
-        num(r, "FBSP.TriageCompute.dram__throughput.avg.pct_of_peak_sustained_elapsed")))
+        100.0 * (rd + wr) / t / 1e3 / 6540.5))
