@@ -60,3 +60,32 @@ def act_cache(lib, dev, rows, features, n):
     tiles = (n + 127) // 128
     assert total == rows * tiles * features * 128
     return torch.zeros(total, device=dev).view(rows, tiles, features, 128)
+
+
+def near_kink(actor, alay, critic, clay, obs2d, margin=2e-5):
+    """Samples with a hidden pre-activation of either network within `margin` of zero (fp64 forward).  There the
+    derivative of ReLU / leaky ReLU jumps, and which side an fp32 forward lands on is decided by rounding: the gradient
+    of such a sample is not determined at fp32 precision (a flip moves a bias gradient by ~1 / batch of a term).  The
+    gradient parity tests draw their batches without such samples, so that their bars measure arithmetic, not luck."""
+    bad = np.zeros(len(obs2d), bool)
+    for flat, lay, slope in ((actor, alay, 0.2), (critic, clay, 0.0)):
+        if flat is None:
+            continue
+        W = {k: v.astype(np.float64) for k, v in P.unpack(flat, lay).items()}
+        x = obs2d.astype(np.float64)
+        for w, b in (("W1", "b1"), ("W2", "b2"), ("W3", "b3")):
+            pre = x @ W[w] + W[b]
+            bad |= (np.abs(pre) < margin).any(axis=1)
+            x = np.where(pre > 0, pre, slope * pre)
+    return bad
+
+
+def redraw_near_kinks(actor, alay, critic, clay, obs2d, draw, margin=2e-5):
+    """obs2d with every near-kink sample (see near_kink) replaced by fresh draws: draw(k) -> [k, ob] float32."""
+    obs2d = np.array(obs2d, dtype=np.float32)
+    for _ in range(50):
+        bad = near_kink(actor, alay, critic, clay, obs2d, margin)
+        if not bad.any():
+            return obs2d
+        obs2d[bad] = draw(int(bad.sum())).astype(np.float32)
+    raise AssertionError("could not draw a batch away from the activation kinks")

@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from oracle import policies as P
-from gpu_util import demo_weights, dev_t, random_weights, rel_err, soa
+from gpu_util import demo_weights, dev_t, random_weights, redraw_near_kinks, rel_err, soa
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
@@ -48,16 +48,17 @@ def backward_gpu(lib, dev, cont, actor, critic, ob, num_ac, obs_rows, acs_rows, 
     return ga.cpu().numpy(), gc.cpu().numpy(), stats.cpu().numpy()
 
 
-def check_grads(got, want, lay, tol, want32=None):
-    """Per tensor: max-abs-diff / max-abs < tol.  The mean gradient of a large batch with random-sign
-    advantages is a heavily cancelling sum (|result| ~ |terms| / sqrt(B)); the numpy fp32 restatement of the
-    reference's own math then sits up to ~1e-3 from the fp64 value.  Where that happens (want32 given) the
-    bar is "no less accurate than twice the fp32 restatement", never looser than that."""
+def check_grads(got, want, lay, tol, want_abs=None):
+    """Per tensor: max-abs-diff / max-abs < tol.  The mean gradient of a large batch with random-sign advantages is a
+    heavily cancelling sum (|result| ~ |terms| / sqrt(B)): where the fp64 oracle's sums over |per-sample term|
+    (want_abs, ``abs_sums=True``) are given, the bar is scaled by the summation's condition number
+    kappa = max_j sum_i |t_ij| / max_j |sum_i t_ij| -- the forward error bound of any summation in working precision."""
     for k, o, s in P.items(lay):
         sz = int(np.prod(s))
         g, w = got[o:o + sz], want[o:o + sz]
-        bar = tol if want32 is None else max(tol, 2.0 * rel_err(want32[o:o + sz], w))
-        assert rel_err(g, w) < bar, "%s: rel err %.3g (bar %.3g)" % (k, rel_err(g, w), bar)
+        kappa = 1.0 if want_abs is None else max(1.0, float(np.abs(want_abs[o:o + sz]).max() / max(np.abs(w).max(), 1e-30)))
+        bar = tol * kappa
+        assert rel_err(g, w) < bar, "%s: rel err %.3g (bar %.3g, kappa %.1f)" % (k, rel_err(g, w), bar, kappa)
     used = np.zeros(lay["_size"], bool)
     for k, o, s in P.items(lay):
         used[o:o + int(np.prod(s))] = True
@@ -75,6 +76,11 @@ def test_gauss_loss_backward_matches_oracle(lib, dev, rows, n, weights):
     B = rows * n
     th = rng.uniform(-np.pi, np.pi, (rows, n))
     obs = np.stack([np.cos(th), np.sin(th), rng.uniform(-8, 8, (rows, n))], axis=-1).astype(np.float32)
+
+    def draw(k):
+        t2 = rng.uniform(-np.pi, np.pi, k)
+        return np.stack([np.cos(t2), np.sin(t2), rng.uniform(-8, 8, k)], axis=-1)
+    obs = redraw_near_kinks(actor, lay, critic, clay, obs.reshape(B, 3), draw).reshape(rows, n, 3)
     acs = rng.uniform(-2.5, 2.5, (rows, n, 1)).astype(np.float32)
     adv = rng.normal(size=(rows, n)).astype(np.float32)
     lp_old = (P.actor_logp(actor, lay, obs.reshape(B, 3), acs.reshape(B, 1), True) +
@@ -83,13 +89,10 @@ def test_gauss_loss_backward_matches_oracle(lib, dev, rows, n, weights):
     beta, gam = 0.7, 0.03
     ga, gc, stats = backward_gpu(lib, dev, True, actor, critic, 3, 1, obs, acs, adv, lp_old, targets, beta, gam)
     wa = P.actor_loss_grads(actor, lay, obs.reshape(B, 3), acs.reshape(B, 1), adv.reshape(B), lp_old.reshape(B), beta,
-                            gam, True, 2.0, clip=None, dtype=np.float64)
-    wc = P.critic_loss_grads(critic, clay, obs.reshape(B, 3), targets.reshape(B), dtype=np.float64)
-    wa32 = P.actor_loss_grads(actor, lay, obs.reshape(B, 3), acs.reshape(B, 1), adv.reshape(B), lp_old.reshape(B), beta,
-                              gam, True, 2.0, clip=None, dtype=np.float32)
-    wc32 = P.critic_loss_grads(critic, clay, obs.reshape(B, 3), targets.reshape(B), dtype=np.float32)
-    check_grads(ga, wa["grad_raw"], lay, 2 * TOL, wa32["grad_raw"])
-    check_grads(gc, wc["grad"], clay, 2 * TOL, wc32["grad"])
+                            gam, True, 2.0, clip=None, dtype=np.float64, abs_sums=True)
+    wc = P.critic_loss_grads(critic, clay, obs.reshape(B, 3), targets.reshape(B), dtype=np.float64, abs_sums=True)
+    check_grads(ga, wa["grad_raw"], lay, 2 * TOL, wa["grad_abs"])
+    check_grads(gc, wc["grad"], clay, 2 * TOL, wc["grad_abs"])
     np.testing.assert_allclose(stats[3], wa["loss"], rtol=2 * TOL, atol=1e-6)
     np.testing.assert_allclose(stats[4], wc["loss"], rtol=2 * TOL)
     np.testing.assert_allclose(stats[5], wa["kl"], rtol=2 * TOL)
@@ -125,6 +128,7 @@ def test_cat_loss_backward_matches_oracle(lib, dev, ob, n_act, rows, n):
     rng = np.random.default_rng(rows * n + ob)
     B = rows * n
     obs = rng.normal(size=(rows, n, ob)).astype(np.float32)
+    obs = redraw_near_kinks(actor, lay, critic, clay, obs.reshape(B, ob), lambda k: rng.normal(size=(k, ob))).reshape(rows, n, ob)
     acs = rng.integers(0, n_act, (rows, n)).astype(np.int32)
     adv = rng.normal(size=(rows, n)).astype(np.float32)
     lp_old = (P.actor_logp(actor, lay, obs.reshape(B, ob), acs.reshape(B), False) +
@@ -211,6 +215,7 @@ def test_basic_ac_critic_head_backward(lib, dev):
     rows, n = 3, 700
     B = rows * n
     obs = rng.normal(size=(rows, n, 4)).astype(np.float32)
+    obs = redraw_near_kinks(None, None, critic, clay, obs.reshape(B, 4), lambda k: rng.normal(size=(k, 4))).reshape(rows, n, 4)
     tg = rng.normal(size=(rows, n)).astype(np.float32)
     c = dev_t(critic, dev)
     o = dev_t(np.stack([soa(x) for x in obs]), dev)
@@ -222,18 +227,16 @@ def test_basic_ac_critic_head_backward(lib, dev):
     lib.call("acx_loss_backward_basic_critic", lib.ptr(c), 4, rows, n, lib.ptr(o), lib.ptr(t), lib.ptr(g), lib.ptr(stats),
              lib.ptr(ws), nbytes, lib.cur_stream())
     torch.cuda.synchronize()
-    want = P.critic_loss_grads(critic, clay, obs.reshape(B, 4), tg.reshape(B), basic_head=True, dtype=np.float64)
-    want32 = P.critic_loss_grads(critic, clay, obs.reshape(B, 4), tg.reshape(B), basic_head=True, dtype=np.float32)
+    want = P.critic_loss_grads(critic, clay, obs.reshape(B, 4), tg.reshape(B), basic_head=True, dtype=np.float64, abs_sums=True)
     got = g.cpu().numpy()
     for name in ("W3", "b3"):
         o3, s3 = clay[name]
         assert not got[o3:o3 + int(np.prod(s3))].any()
-    lay_nz = {k: v for k, v in clay.items() if k not in ("W3", "b3")}
-    check_grads(got, want["grad"], lay_nz | {"_size": clay["_size"]}, 2 * TOL, want32["grad"]) if False else None
     for k, off, shp in P.items(clay):
         if k in ("W3", "b3"):
             continue
         sz = int(np.prod(shp))
-        bar = max(2 * TOL, 2.0 * rel_err(want32["grad"][off:off + sz], want["grad"][off:off + sz]))
-        assert rel_err(got[off:off + sz], want["grad"][off:off + sz]) < bar, k
+        w = want["grad"][off:off + sz]
+        kappa = max(1.0, float(np.abs(want["grad_abs"][off:off + sz]).max() / np.abs(w).max()))
+        assert rel_err(got[off:off + sz], w) < 2 * TOL * kappa, (k, kappa)
     np.testing.assert_allclose(stats[4].item(), want["loss"], rtol=2 * TOL)

@@ -1,32 +1,35 @@
 """K4 with the back-propagation chain on the tensor cores (acx_loss_backward_{gauss,cat}_tc) through the C ABI:
-parity with the oracle's analytic fp64 gradients (same bar as tests/test_gpu_backward.py: 2e-5 relative per tensor, or
-twice the error of the oracle's own fp32 evaluation where the batch sum cancels heavily), agreement with the
+parity with the oracle's analytic fp64 gradients (same bar as tests/test_gpu_backward.py: 2e-5 relative per tensor,
+scaled by the batch sum's condition number where it cancels), agreement with the
 all-FFMA cached kernel to 3xTF32 accuracy, run-to-run determinism, argument checks."""
 import numpy as np
 import pytest
 import torch
 
 from oracle import policies as P
-from gpu_util import act_cache, dev_t, random_weights, rel_err, soa
+from gpu_util import act_cache, dev_t, random_weights, redraw_near_kinks, rel_err, soa
 from test_gpu_backward import make_opt
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
 
 
-def check_grads(got, want, lay, tol, want32, batch):
-    """Per tensor: max-abs-diff <= bar * max-abs + floor.  bar as in tests/test_gpu_backward.py (tol, or twice the
-    error of the oracle's own fp32 evaluation where the batch sum cancels heavily).  floor = 3e-6 / sqrt(batch): a
-    gradient element is the mean of `batch` per-sample terms of magnitude O(1), each carrying ~1e-6 relative fp32
-    rounding (tanh, exp, the lp_old - lp difference), so the mean carries ~1e-6 / sqrt(batch) absolute noise however
-    small it is itself -- which matters for the one-element tensors (bh, log_std), where max-abs IS that element."""
+def check_grads(got, want, lay, tol, want_abs, batch):
+    """Per tensor: max-abs-diff <= tol * kappa * max-abs + floor.  kappa = max_j sum_i |t_ij| / max_j |sum_i t_ij| is the
+    condition number of the batch sum (from the fp64 oracle's sums over |per-sample term|, ``abs_sums=True``): the mean
+    gradient of a batch with random-sign advantages is a cancelling sum, and tol * kappa is the forward error bound of
+    any summation in working precision.  floor = 3e-6 / sqrt(batch): a gradient element is the mean of `batch`
+    per-sample terms of magnitude O(1), each carrying ~1e-6 relative fp32 rounding (tanh, exp, the lp_old - lp
+    difference), so the mean carries ~1e-6 / sqrt(batch) absolute noise however small it is itself -- which matters for
+    the one-element tensors (bh, log_std), where max-abs IS that element."""
     floor = 3e-6 / np.sqrt(batch)
     for k, o, s in P.items(lay):
         sz = int(np.prod(s))
         g, w = got[o:o + sz].astype(np.float64), want[o:o + sz]
-        bar = max(tol, 2.0 * rel_err(want32[o:o + sz], w))
+        kappa = max(1.0, float(np.abs(want_abs[o:o + sz]).max() / max(np.abs(w).max(), 1e-30)))
         err = np.abs(g - w).max()
-        assert err <= bar * np.abs(w).max() + floor, "%s: abs err %.3g (allowed %.3g)" % (k, err, bar * np.abs(w).max() + floor)
+        assert err <= tol * kappa * np.abs(w).max() + floor, "%s: abs err %.3g (allowed %.3g, kappa %.1f)" % (
+            k, err, tol * kappa * np.abs(w).max() + floor, kappa)
     used = np.zeros(lay["_size"], bool)
     for k, o, s in P.items(lay):
         used[o:o + int(np.prod(s))] = True
@@ -43,6 +46,10 @@ class Case:
         rng = np.random.default_rng(seed + rows * 131 + n)
         self.B = B = rows * n
         self.obs = rng.normal(size=(rows, n, ob)).astype(np.float32)
+        if rows * n <= 100000:      # small batches: no sample within fp32 rounding of an activation kink (gpu_util.near_kink);
+            # the full-size batches keep theirs -- tests/test_gpu_a_fullsize.py bounds them by the condition number
+            self.obs = redraw_near_kinks(self.actor, self.lay, self.critic, self.clay, self.obs.reshape(rows * n, ob),
+                                         lambda k: rng.normal(size=(k, ob))).reshape(rows, n, ob)
         self.adv = rng.normal(size=(rows, n)).astype(np.float32)
         self.targets = (rng.normal(size=(rows, n)) * 2).astype(np.float32)
         self.beta, self.gam = beta, gam
@@ -119,8 +126,10 @@ class Case:
         B, ob = self.B, self.ob
         acs = self.acs.reshape(B, self.num_ac) if self.cont else self.acs.reshape(B)
         wa = P.actor_loss_grads(self.actor, self.lay, self.obs.reshape(B, ob), acs, self.adv.reshape(B),
-                                self.lp_old.reshape(B), self.beta, self.gam, self.cont, 2.0, clip=None, dtype=dtype)
-        wc = P.critic_loss_grads(self.critic, self.clay, self.obs.reshape(B, ob), self.targets.reshape(B), dtype=dtype)
+                                self.lp_old.reshape(B), self.beta, self.gam, self.cont, 2.0, clip=None, dtype=dtype,
+                                abs_sums=True)
+        wc = P.critic_loss_grads(self.critic, self.clay, self.obs.reshape(B, ob), self.targets.reshape(B), dtype=dtype,
+                                 abs_sums=True)
         return wa, wc
 
 
@@ -130,9 +139,8 @@ def test_gauss_tc_backward_matches_oracle(lib, dev, rows, n, split):
     k = Case(lib, dev, True, 3, 1, rows, n, 21, split=split)
     ga, gc, stats = k.run("tc")
     wa, wc = k.oracle(np.float64)
-    wa32, wc32 = k.oracle(np.float32)
-    check_grads(ga, wa["grad_raw"], k.lay, 2 * TOL, wa32["grad_raw"], k.B)
-    check_grads(gc, wc["grad"], k.clay, 2 * TOL, wc32["grad"], k.B)
+    check_grads(ga, wa["grad_raw"], k.lay, 2 * TOL, wa["grad_abs"], k.B)
+    check_grads(gc, wc["grad"], k.clay, 2 * TOL, wc["grad_abs"], k.B)
     np.testing.assert_allclose(stats[3], wa["loss"], rtol=2 * TOL, atol=1e-6)
     np.testing.assert_allclose(stats[4], wc["loss"], rtol=2 * TOL)
     np.testing.assert_allclose(stats[5], wa["kl"], rtol=2 * TOL)
@@ -146,9 +154,8 @@ def test_cat_tc_backward_matches_oracle(lib, dev, ob, n_act, rows, n, split):
     k = Case(lib, dev, False, ob, n_act, rows, n, 31, beta=1.0, gam=0.01, split=split)
     ga, gc, stats = k.run("tc")
     wa, wc = k.oracle(np.float64)
-    wa32, wc32 = k.oracle(np.float32)
-    check_grads(ga, wa["grad_raw"], k.lay, 2 * TOL, wa32["grad_raw"], k.B)
-    check_grads(gc, wc["grad"], k.clay, 2 * TOL, wc32["grad"], k.B)
+    check_grads(ga, wa["grad_raw"], k.lay, 2 * TOL, wa["grad_abs"], k.B)
+    check_grads(gc, wc["grad"], k.clay, 2 * TOL, wc["grad_abs"], k.B)
     np.testing.assert_allclose(stats[3], wa["loss"], rtol=2 * TOL, atol=1e-6)
     np.testing.assert_allclose(stats[4], wc["loss"], rtol=2 * TOL)
 
@@ -198,12 +205,10 @@ def test_tc_backward_with_the_forward_pass_sign_masks(lib, dev, rows, n):
     masked = k.run("tc", actor=False, critic_masks=True)
     np.testing.assert_array_equal(masked[1], plain[1])
     np.testing.assert_array_equal(masked[2], plain[2])
-    # against the oracle with the bar of the trainer tests (2e-3 of each tensor's max): here the cached activations come
-    # from the 3xTF32 forward, and an activation within rounding of zero may land on the other side of the ReLU kink
+    # against the oracle with the file's bar: the cached activations come from the 3xTF32 forward here, whose ~1e-6 error
+    # cannot move a sample across an activation kink -- the batch keeps 2e-5 clear of them (gpu_util.near_kink)
     _, wc = k.oracle(np.float64)
-    for name, o, sh in P.items(k.clay):
-        sz = int(np.prod(sh))
-        assert np.abs(masked[1][o:o + sz] - wc["grad"][o:o + sz]).max() <= 2e-3 * np.abs(wc["grad"][o:o + sz]).max(), name
+    check_grads(masked[1], wc["grad"], k.clay, 2 * TOL, wc["grad_abs"], k.B)
     words = k.cmask.cpu().numpy().view(np.uint32).reshape(rows, -1, 12, 128)      # [rows][tiles][8 X1 + 4 X2 words][128]
     x2 = k.cx2.cpu().numpy()                                                        # [rows][tiles][128][128]
     bits = (words[:, :, 8:, None, :] >> np.arange(32, dtype=np.uint32)[None, None, None, :, None]) & 1
