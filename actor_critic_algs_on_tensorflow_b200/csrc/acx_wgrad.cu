@@ -292,6 +292,19 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
       const int brows = phase == 0 ? H3 : 128;
       float bacc[4] = {0.f, 0.f, 0.f, 0.f};       // bias-gradient partials of rows r0 + 32 m (chunk c4 of every box)
       float4 o[OBM], o_next[OBM];
+      // phase 1, at most 4 network inputs: this thread's rows of W1 and b1 (H1 / 32 rows, the same for every box) stay in
+      // registers instead of being re-read from shared memory for every box (40 registers for the critic; the 8-input
+      // build already sits at the register cap and keeps the loads)
+      constexpr bool W1REG = OBM <= 4;
+      float w1r[W1REG ? H1 / 32 : 1][W1REG ? OBM : 1], b1r[W1REG ? H1 / 32 : 1];
+      if (W1REG && phase == 1) {
+#pragma unroll
+        for (int m = 0; m < H1 / 32; ++m) {
+          b1r[W1REG ? m : 0] = B.b1[r0 + 32 * m];
+#pragma unroll
+          for (int i = 0; i < OBM; ++i) w1r[W1REG ? m : 0][W1REG ? i : 0] = i < ob ? B.W1[i * H1 + r0 + 32 * m] : 0.f;
+        }
+      }
 #ifdef ACX_WG_PROF
       const bool sprof_ = blockIdx.x == 0 && tid == 64 + 128;
       long long sp_[5] = {0, 0, 0, 0, 0}, sl_ = clock64();
@@ -323,11 +336,11 @@ acx_wgrad_kernel(const __grid_constant__ CUtensorMap mapX2, const __grid_constan
 #pragma unroll
               for (int i = 0; i < OBM; ++i)
                 if (i < ob) {
-                  const float w = B.W1[i * H1 + k];
+                  const float w = W1REG ? w1r[W1REG ? m : 0][W1REG ? i : 0] : B.W1[i * H1 + k];
                   sacc.x = fmaf(o[i].x, w, sacc.x); sacc.y = fmaf(o[i].y, w, sacc.y);
                   sacc.z = fmaf(o[i].z, w, sacc.z); sacc.w = fmaf(o[i].w, w, sacc.w);
                 }
-              const float bk = B.b1[k];
+              const float bk = W1REG ? b1r[W1REG ? m : 0] : B.b1[k];
               float4 x;
               x.x = acxmlp::act_fn<LRELU>(__fadd_rn(sacc.x, bk)); x.y = acxmlp::act_fn<LRELU>(__fadd_rn(sacc.y, bk));
               x.z = acxmlp::act_fn<LRELU>(__fadd_rn(sacc.z, bk)); x.w = acxmlp::act_fn<LRELU>(__fadd_rn(sacc.w, bk));
