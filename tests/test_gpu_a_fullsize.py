@@ -150,14 +150,16 @@ def test_tcgen05_forward_and_backward_at_the_bench_size_match_the_fp64_oracle(li
                 assert err.max() <= BAR, (name, err.max())
             assert (v_want < k.targets.reshape(-1)).all()           # every v - target has the same sign
         else:
-            wa32, wc32, _, _, _ = chunked_oracle(k, np.float32)
+            # the numpy-fp32 restatement's own error, for the log (Pendulum size only: one more pass over 5.2 M samples
+            # would add a minute to the suite)
+            wa32, wc32 = (chunked_oracle(k, np.float32)[:2]) if k.B <= 2_000_000 else (None, None)
         # ---- K4
         failures, worst = [], 0.0
         for net, got, want, lay in (("actor", ga, wa, k.lay), ("critic", gc, wc, k.clay)):
             e = per_tensor_errors(got, want, lay)
             eabs = per_tensor_errors(sums["abs_a"] if net == "actor" else sums["abs_c"], 0 * want, lay)
             if regime == "zero-mean":
-                e32 = per_tensor_errors(wa32 if net == "actor" else wc32, want, lay)
+                e32 = per_tensor_errors(wa32 if net == "actor" else wc32, want, lay) if wa32 is not None else None
             for name in e:
                 err, scale = e[name]
                 kappa = eabs[name][0] / scale
@@ -170,7 +172,7 @@ def test_tcgen05_forward_and_backward_at_the_bench_size_match_the_fp64_oracle(li
                     ok = err <= BAR * (1.0 if strict else kappa) * scale + floor
                 else:
                     print("%s | %s | %s.%s: cuda %.2e, numpy-fp32 oracle %.2e of max |grad| = %.3e; kappa = %.0f" % (
-                        label, regime, net, name, err / scale, e32[name][0] / scale, scale, kappa))
+                        label, regime, net, name, err / scale, e32[name][0] / scale if e32 else float("nan"), scale, kappa))
                     ok = err <= BAR * kappa * scale + floor
                 if not ok:
                     failures.append((regime, net, name, err / scale))
