@@ -84,7 +84,7 @@ class A2CTrainer:
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
                  critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=True,
                  cache_activations=True, tensor_core_backward=True, frames=1, fused_rollout=True, stagger=True,
-                 diagnostics=False, log_rows=128, basic=False):
+                 diagnostics=False, log_rows=128, basic=False, overlap_nets=True):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
@@ -179,6 +179,14 @@ class A2CTrainer:
         if self.tc_bwd and N % 4 == 0:       # room for dPre3 / dPre2 / X1: weight gradients on the tensor cores too
             self.ws_bwd_bytes = L.load().acx_loss_backward_tc_workspace_bytes(self.ob, self.num_ac, int(self.cont), T, N)
         self.ws_bwd = torch.empty(self.ws_bwd_bytes, device=d, dtype=torch.uint8)
+        # the two networks' backward passes are independent: the critic's runs on a second stream (a parallel branch of
+        # the CUDA graph) with a workspace of its own.  Every kernel of the pair is persistent and fills the GPU, so the
+        # two do not run side by side -- but the one's CTAs start on the SMs the other's last wave leaves idle, and the
+        # small fixed-order reduce kernels hide behind the other network's work (step 5.15 -> 5.07 ms).  Branching the
+        # operand packs and the episode statistics off the same way measured no further gain and was dropped.
+        self.overlap_nets = bool(overlap_nets) and self.tc_bwd and N % 4 == 0 and not self.basic
+        self._side = torch.cuda.Stream(device=d) if self.overlap_nets else None
+        self.ws_bwd2 = torch.empty(self.ws_bwd_bytes, device=d, dtype=torch.uint8) if self.overlap_nets else None
         self.kl_part = torch.zeros(L.load().acx_kl_workspace_bytes() // 8, device=d, dtype=torch.float64)
         self.kl_blocks = ctypes.c_int(0)
         if self.cache:      # tile-blocked [rows][ceil(N/128)][features][128]; one row of the 2-D tensor = one time step
@@ -324,11 +332,22 @@ class A2CTrainer:
         if self.tc_bwd:
             cached = (common[:-3] + (L.ptr(self.ax2), L.ptr(self.ax3), L.ptr(self.cx2), L.ptr(self.cx3), L.ptr(self.amask),
                                      L.ptr(self.cmask)) + common[-3:])
-            head = (L.ptr(self.actor), critic_ptr, L.ptr(self.packed_bwd_a), L.ptr(self.packed_bwd_c), self.ob)
-            if self.cont:
-                L.call("acx_loss_backward_gauss_tc", *head, self.num_ac, self.ac_scale, T, N, *cached)
+            def launch(actor_p, critic_p, ws, stream):
+                head = (actor_p, critic_p, L.ptr(self.packed_bwd_a), L.ptr(self.packed_bwd_c), self.ob)
+                tail = cached[:-3] + (L.ptr(ws), self.ws_bwd_bytes, stream)
+                if self.cont:
+                    L.call("acx_loss_backward_gauss_tc", *head, self.num_ac, self.ac_scale, T, N, *tail)
+                else:
+                    L.call("acx_loss_backward_cat_tc", *head, self.n_act, T, N, *tail)
+            if self.overlap_nets:
+                cur = torch.cuda.current_stream()
+                self._side.wait_stream(cur)
+                with torch.cuda.stream(self._side):
+                    launch(None, L.ptr(self.critic), self.ws_bwd2, L.cur_stream())
+                launch(L.ptr(self.actor), None, self.ws_bwd, s)
+                cur.wait_stream(self._side)
             else:
-                L.call("acx_loss_backward_cat_tc", *head, self.n_act, T, N, *cached)
+                launch(L.ptr(self.actor), critic_ptr, self.ws_bwd, s)
             split = self.N % 4 == 0
             per_net = 4 if split else 2         # chain, dW3 kernel, dW2 kernel, grad reduce | train, reduce
             return 2 + extra + per_net * (1 if self.basic else 2)      # value, scan, ...
