@@ -18,7 +18,9 @@ is all-reduced over NCCL).  Prints ONE JSON line on rank 0 (contract in the task
             timed alone in this run.
   cpu_baseline / --impl reference
             the numpy restatement of the reference's math (oracle/a2c.py; TF 1.3 + gym cannot be
-            installed here -- BASELINE.md) on the host cores, on a bounded sample of the workload.
+            installed here -- BASELINE.md) on the host cores.  cpu_baseline of the default line: a
+            bounded sample (2,048 envs).  --impl reference: FULL-SIZE iterations (65,536 envs x 20
+            steps, the GPU arm's config), up to --steps of them within a 120 s timed region.
 """
 import argparse
 import json
@@ -175,22 +177,37 @@ def ref_shape_gpu(iters=60):
 
 def run_reference(args, rank):
     """--impl reference: the numpy restatement of the reference's math on the box's host cores, on THIS arm's config
-    (65,536 envs x 20 steps per iteration, full size): at 10-30 s per iteration the timed region is capped at 2 iterations
-    after 1 warm-up iteration on a 4,096-env sample, whatever --steps / --warmup say."""
+    (65,536 envs x 20 steps per iteration, full size, 10-15 s each on 16 cores).  Warm-up: --warmup iterations on a
+    4,096-env sample (BLAS threads, allocator; the state they leave is discarded).  Timed: --steps full-size
+    iterations, stopping early (never before 2) once the next one would carry the timed region past 120 s so that the
+    whole run stays within a few minutes: "steps" of the line is the number actually timed, "steps_requested" is
+    --steps."""
     if rank != 0:
         return
+    from oracle import a2c, envs as E
     cores = os.cpu_count()
-    k = max(1, min(args.steps, 2))
-    cpu_baseline(steps=1, n_envs=4096, warmup=0)                       # warm-up: BLAS threads, allocator
-    v, sec, sample = cpu_baseline(steps=k, n_envs=N_ENVS, warmup=0)
+    cpu_baseline(steps=max(1, args.warmup), n_envs=4096, warmup=0)
+    S = a2c.A2CState(E.ENV_IDS[ENV_ID], N_ENVS, seed=SEED)
+    budget, times = 120.0, []
+    want = max(1, args.steps)
+    while len(times) < want:
+        t0 = time.perf_counter()
+        a2c.iteration(S, T=HORIZON)
+        times.append(time.perf_counter() - t0)
+        if len(times) >= 2 and sum(times) + times[-1] > budget:
+            break
+    k, sec = len(times), sum(times) / len(times)
+    v = N_ENVS * HORIZON / sec
+    sample = "%d envs x %d steps x %d iterations: the full workload" % (N_ENVS, HORIZON, k)
     bref = b_ref_baselines()
     line = {"impl": "reference", "metric": "env-steps/sec (rollout+update)", "value": v, "unit": "env-steps/s",
-            "n_gpus": args.gpus, "steps": k, "warmup": 1, "ms_per_step": sec * 1e3,
+            "n_gpus": args.gpus, "steps": k, "warmup": args.warmup, "ms_per_step": sec * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "envs_per_gpu": N_ENVS, "horizon": HORIZON, "sample": sample,
-                       "same_config": True, "host_threads": blas_threads(), "host_cores": cores},
+            "config": {"workload": WORKLOAD, "envs_per_gpu": N_ENVS, "horizon": HORIZON, "mode": args.mode},
+            "same_config": True, "steps_requested": args.steps,
             "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "blas_threads": blas_threads(),
-                             "kind": "port", "sample": sample, "b_ref": bref},
+                             "kind": "port", "sample": sample, "warmup_sample": "4096 envs x %d steps" % HORIZON,
+                             "b_ref": bref},
             "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "numpy restatement of the reference's math (oracle/a2c.py), vectorised over the env batch: TF 1.3 and "
