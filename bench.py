@@ -140,7 +140,8 @@ def b_ref_baselines(seconds=3.0):
     from oracle import ref_loop as RL
     out = {}
     for key, env, workers, basic in (("a3c_pendulum_1_worker", "Pendulum-v0", 1, False),
-                                     ("a3c_pendulum_runner_sh_2_workers", "Pendulum-v0", 2, False),
+                                     ("a3c_pendulum_readme_2_workers", "Pendulum-v0", 2, False),
+                                     ("a3c_pendulum_runner_sh_3_workers", "Pendulum-v0", 3, False),
                                      ("basic_ac_cartpole_1_process", "CartPole-v0", 1, True)):
         v, n = RL.run_workers(env, workers, basic, seconds=seconds, seed=SEED)
         out[key] = {"value": v, "unit": "env-steps/s", "processes": workers, "env_steps_timed": n,

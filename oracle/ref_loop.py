@@ -11,7 +11,8 @@ was).  This module keeps the reference's shape instead: ONE environment, a batch
 
 TensorFlow's per-call dispatch cost (one ``sess.run`` per env step, the reference's dominant cost) is NOT modelled: the
 numbers this gives are an upper bound on the real reference.  ``run_workers`` runs k independent workers in k
-processes -- the ``runner.sh`` shape (1 ps + 2 workers; the ps does no arithmetic worth timing).
+processes -- ``A3C/runner.sh:3-4`` starts 1 ps + 3 workers, the README's example 1 ps + 2 (the ps does no arithmetic
+worth timing): both are timed.
 """
 import time
 
