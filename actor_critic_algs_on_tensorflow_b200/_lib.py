@@ -97,6 +97,9 @@ SIGNATURES = {
     "acx_kl_finalize": (_i, [_p, _i, _d, _p, _p]),
     "acx_kl_lr_update": (_i, [_p, _p, _p]),
     "acx_kl_lr_update_split": (_i, [_p, _p, _p, _f, _i, _p]),
+    "acx_xgpu_flag_offset_bytes": (_sz, [_i]),
+    "acx_xgpu_buffer_bytes": (_sz, [_i]),
+    "acx_allreduce_adam": (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _i, _p]),
 }
 
 _lib = None

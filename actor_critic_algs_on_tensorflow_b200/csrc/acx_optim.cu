@@ -7,7 +7,7 @@
 // A3C/process.py:271-278).  HBM-bound: 28 B per parameter (read g, theta, m, v; write theta, m, v).
 #include <stdarg.h>
 
-#include "acx_common.cuh"
+#include "acx_optim.cuh"
 
 // ------------------------------------------------------------------ error / info plumbing
 static thread_local char g_err[512] = "";
@@ -50,10 +50,6 @@ extern "C" int acx_params_layout(int net, int ob_dim, int num_ac, int cont, int*
 }
 
 // ------------------------------------------------------------------ kernels
-#define ACX_BETA1 0.9f
-#define ACX_BETA2 0.999f
-#define ACX_ADAM_EPS 1e-8f
-
 __global__ void acx_opt_init_kernel(float* opt, float actor_lr, float critic_lr, float beta_kl, float gamma_ent,
                                     float clip, float desired_kl, float min_lr, float max_lr, int schedule_on) {
   if (threadIdx.x == 0 && blockIdx.x == 0) {
@@ -74,20 +70,12 @@ __global__ void acx_opt_init_kernel(float* opt, float actor_lr, float critic_lr,
   }
 }
 
-__device__ inline void adam_one(float& th, float g, float& m, float& v, float alpha) {
-  // TF ApplyAdam: m += (g - m)(1 - b1); v += (g*g - v)(1 - b2); var -= (m * alpha) / (sqrt(v) + eps)
-  m = __fadd_rn(m, __fmul_rn(__fsub_rn(g, m), __fsub_rn(1.0f, ACX_BETA1)));
-  v = __fadd_rn(v, __fmul_rn(__fsub_rn(__fmul_rn(g, g), v), __fsub_rn(1.0f, ACX_BETA2)));
-  th = __fsub_rn(th, __fdiv_rn(__fmul_rn(m, alpha), __fadd_rn(__fsqrt_rn(v), ACX_ADAM_EPS)));
-}
-
 __global__ void __launch_bounds__(256) acx_adam_kernel(float* __restrict__ actor, const float* __restrict__ ga,
                                                        float* __restrict__ ma, float* __restrict__ va, int na,
                                                        float* __restrict__ critic, const float* __restrict__ gc,
                                                        float* __restrict__ mc, float* __restrict__ vc, int nc,
                                                        const float* __restrict__ opt, float scale) {
-  const float b1p = opt[ACX_OPT_BETA1_POW], b2p = opt[ACX_OPT_BETA2_POW];
-  const float corr = __fdiv_rn(__fsqrt_rn(__fsub_rn(1.0f, b2p)), __fsub_rn(1.0f, b1p));
+  const float corr = acx_adam_corr(opt);
   const float alpha_a = __fmul_rn(opt[ACX_OPT_ACTOR_LR], corr);      // lr * sqrt(1-b2^t) / (1-b1^t)
   const float alpha_c = __fmul_rn(opt[ACX_OPT_CRITIC_LR], corr);
   const float clip = opt[ACX_OPT_CLIP];
@@ -100,14 +88,11 @@ __global__ void __launch_bounds__(256) acx_adam_kernel(float* __restrict__ actor
     float4* v = reinterpret_cast<float4*>(is_a ? va : vc) + j;
     float4 g = reinterpret_cast<const float4*>(is_a ? ga : gc)[j];
     g.x *= scale; g.y *= scale; g.z *= scale; g.w *= scale;
-    if (is_a && clip > 0.f) {
-      g.x = fminf(fmaxf(g.x, -clip), clip); g.y = fminf(fmaxf(g.y, -clip), clip);
-      g.z = fminf(fmaxf(g.z, -clip), clip); g.w = fminf(fmaxf(g.w, -clip), clip);
-    }
+    if (is_a && clip > 0.f) g = acx_clip4(g, clip);
     float4 t = *th, mm = *m, vv = *v;
     const float alpha = is_a ? alpha_a : alpha_c;
-    adam_one(t.x, g.x, mm.x, vv.x, alpha); adam_one(t.y, g.y, mm.y, vv.y, alpha);
-    adam_one(t.z, g.z, mm.z, vv.z, alpha); adam_one(t.w, g.w, mm.w, vv.w, alpha);
+    acx_adam_one(t.x, g.x, mm.x, vv.x, alpha); acx_adam_one(t.y, g.y, mm.y, vv.y, alpha);
+    acx_adam_one(t.z, g.z, mm.z, vv.z, alpha); acx_adam_one(t.w, g.w, mm.w, vv.w, alpha);
     *th = t; *m = mm; *v = vv;
   }
 }
@@ -144,11 +129,9 @@ __global__ void acx_kl_lr_kernel(float* opt, float* stats, const float* kl_sum, 
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     if (flags & 1) {
       if (kl_sum != nullptr) stats[ACX_STAT_KL_POST] = __fmul_rn(*kl_sum, kl_scale);
-      const double kl = (double)stats[ACX_STAT_KL_POST], want = (double)opt[ACX_OPT_DESIRED_KL];
-      const double lr = (double)opt[ACX_OPT_ACTOR_LR];
-      stats[ACX_STAT_ACTOR_LR_USED] = (float)lr;
-      if (kl < want / 4.0) opt[ACX_OPT_ACTOR_LR] = (float)fmin((double)opt[ACX_OPT_MAX_LR], lr * 1.5);
-      else if (kl > want * 4.0) opt[ACX_OPT_ACTOR_LR] = (float)fmax((double)opt[ACX_OPT_MIN_LR], lr / 1.5);
+      const float lr = opt[ACX_OPT_ACTOR_LR];
+      stats[ACX_STAT_ACTOR_LR_USED] = lr;
+      opt[ACX_OPT_ACTOR_LR] = acx_lr_rule(lr, stats[ACX_STAT_KL_POST], opt);
     }
     if (flags & 2) {
       const int it = (int)opt[ACX_OPT_ITER];

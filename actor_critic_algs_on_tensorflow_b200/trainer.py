@@ -19,8 +19,11 @@ streams disjoint, mirroring seed+task of ``A3C/train.py:40``); parameters, Adam 
 opt block are replicated.  ``mode='sync'`` is synchronous A2C: all-reduce(sum) of the flat
 gradient, x 1/world, clip, one identical Adam step on every rank.  ONE collective per update: the
 post-update KL of update i (which only feeds the lr rule, and the lr is first consumed by update
-i+1's Adam step) rides as one extra float behind update i+1's gradient, so a step is
-graph -> all-reduce -> graph.
+i+1's Adam step) rides as one extra float behind update i+1's gradient.  ``exchange='p2p'`` (the default when the
+ranks' gradient buffers can be mapped into each other's address space -- torch symmetric memory on one NVSwitch node):
+the sum over ranks, the lr rule, the clip and the Adam step are ONE kernel reading the peers' buffers over NVLink
+(``acx_allreduce_adam``), inside the same CUDA graph as everything else: a step is one graph launch and no NCCL call.
+``exchange='nccl'``: graph -> ``all_reduce`` -> graph.
 ``mode='async'`` mirrors the reference's parameter-server semantics (per-worker clip, per-worker
 Adam moments and lr applied to shared parameters, then pull -- ``A3C/policies.py:85-98``,
 ``A3C/process.py:257-260``): every rank applies its own clipped gradient with its own moments to
@@ -28,6 +31,8 @@ the iteration-start parameters (stale by one push, as on the ps) and the paramet
 summed over ranks, i.e. every worker's push lands before the pull.
 """
 import ctypes
+import os
+import sys
 
 import numpy as np
 import torch
@@ -56,6 +61,7 @@ def glorot_flat(net, ob_dim, num_ac, cont, gen):
     return flat
 
 
+XGPU_MAX_RANKS = 8     # ACX_XGPU_MAX_RANKS of include/acx.h
 GRAD_TAIL = 4      # floats behind the flat gradient in the exchange buffer: [KL of the previous update, 3 x pad]
 
 
@@ -84,7 +90,7 @@ class A2CTrainer:
                  gamma_ent=0.01, schedule=True, rank=0, world=1, mode="sync", device=None, actor_params=None,
                  critic_params=None, use_graph=True, max_episode_steps=0, process_group=None, tensor_cores=True,
                  cache_activations=True, tensor_core_backward=True, frames=1, fused_rollout=True, stagger=True,
-                 diagnostics=False, log_rows=128, basic=False, overlap_nets=True):
+                 diagnostics=False, log_rows=128, basic=False, overlap_nets=True, exchange="auto"):
         if not torch.cuda.is_available():
             raise L.AcxError("A2CTrainer needs a CUDA device: the hot path has no CPU fallback")
         L.load()
@@ -148,6 +154,20 @@ class A2CTrainer:
         self._gradbuf = torch.zeros(P + GRAD_TAIL, device=d, dtype=f32)
         self.grads = self._gradbuf[:P]
         self.old_params = torch.empty(P, device=d, dtype=f32) if mode == "async" else None
+        # how a synchronous multi-rank update exchanges gradients: 'p2p' = acx_allreduce_adam over peer-mapped buffers
+        # (one kernel: sum over ranks + lr rule + clip + Adam), 'nccl' = all_reduce between two graphs; 'auto' takes p2p
+        # when the buffers can be mapped and says so on stderr when they cannot.  ACX_EXCHANGE overrides the argument.
+        self.exchange, self.grad_sum = "nccl", None
+        want = os.environ.get("ACX_EXCHANGE", exchange)
+        assert want in ("auto", "p2p", "nccl"), want
+        if self.world > 1 and mode == "sync" and want != "nccl":
+            try:
+                self._setup_p2p(P)
+            except Exception as e:       # noqa: BLE001 -- any failure to map peer memory means the NCCL exchange
+                if want == "p2p":
+                    raise
+                print("[acx] rank %d: peer-mapped exchange unavailable (%s: %s); using the NCCL all-reduce" %
+                      (self.rank, type(e).__name__, e), file=sys.stderr, flush=True)
 
         self.state = torch.empty((self.S, N), device=d, dtype=f32)
         self.elapsed = torch.zeros(N, device=d, dtype=torch.int32)
@@ -438,6 +458,49 @@ class A2CTrainer:
         self._gradbuf[P:P + 1].copy_(self.stats[L.STAT_KL_POST:L.STAT_KL_POST + 1])
         return n + 1 + self._lr_update(2) + self._log_push()
 
+    def _setup_p2p(self, P):
+        """Re-home the exchange buffer [gradient ‖ tail ‖ flags] into memory every rank of the group has mapped (torch
+        symmetric memory: plumbing only -- the kernel that reads the peers is acx_allreduce_adam)."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        lib = L.load()
+        if self.world > XGPU_MAX_RANKS:
+            raise L.AcxError("acx_allreduce_adam takes at most %d ranks" % XGPU_MAX_RANKS)
+        group = self.pg if self.pg is not None else dist.group.WORLD
+        nfl = lib.acx_xgpu_buffer_bytes(P + GRAD_TAIL) // 4
+        buf = symm.empty(nfl, dtype=torch.float32, device=self.dev)
+        buf.zero_()
+        torch.cuda.synchronize()
+        hdl = symm.rendezvous(buf, group)
+        ptrs = [int(x) for x in hdl.buffer_ptrs]
+        if len(ptrs) != self.world or hdl.rank != self.rank or ptrs[self.rank] != buf.data_ptr():
+            raise L.AcxError("symmetric-memory group does not match rank %d / world %d" % (self.rank, self.world))
+        self._xbuf, self._xhdl = buf, hdl
+        self._peers = (ctypes.c_void_p * self.world)(*ptrs)
+        self._gradbuf = buf[:P + GRAD_TAIL]
+        self.grads = self._gradbuf[:P]
+        self.grad_sum = torch.zeros(P + GRAD_TAIL, device=self.dev, dtype=torch.float32)
+        self._xgen = torch.zeros(128, device=self.dev, dtype=torch.int32)
+        torch.cuda.synchronize()
+        dist.barrier(group)              # every rank's flags are zero before anybody signals
+        self.exchange = "p2p"
+
+    def _seg_b_p2p(self, first):
+        """_seg_b_sync with the exchange inside: one kernel sums the ranks' [gradient ‖ previous KL] over NVLink,
+        applies the previous update's lr rule (not in the very first update), the clip and Adam."""
+        Pa, Pc, s = self.Pa, self.Pc, L.cur_stream()
+        P, scale = Pa + Pc, 1.0 / self.world
+        L.call("acx_allreduce_adam", self._peers, self.world, self.rank, Pa, Pc, GRAD_TAIL, L.ptr(self.actor),
+               L.ptr(self.m[:Pa]), L.ptr(self.v[:Pa]), L.ptr(self.critic), L.ptr(self.m[Pa:]), L.ptr(self.v[Pa:]),
+               L.ptr(self.opt), L.ptr(self.grad_sum), L.ptr(self._xgen), scale, int(not first), s)
+        n = 1
+        if not first:                    # records the lr the kernel has just used (same rule, same words)
+            n += self._lr_update(1, self.grad_sum.data_ptr() + 4 * P, scale)
+        L.call("acx_adam_tick", L.ptr(self.opt), s)
+        n += 1 + self._pack() + self._post_kl() + self._ev_after()
+        self._gradbuf[P:P + 1].copy_(self.stats[L.STAT_KL_POST:L.STAT_KL_POST + 1])
+        return n + 1 + self._lr_update(2) + self._log_push()
+
     def _seg_c_async(self):
         return self._pack() + self._post_kl() + self._ev_after() + self._lr_update() + self._log_push()
 
@@ -514,14 +577,20 @@ class A2CTrainer:
             self.noise_buf.copy_(noise, non_blocking=True)
             self.reset_u_buf.copy_(reset_u, non_blocking=True)
         first = not self.iterations_started
+        p2p = self.world > 1 and self.mode == "sync" and self.exchange == "p2p"
         if first:
             # first iteration: obs_buf[0] already holds the reset observations
             n = self._rollout(buffered) + self._episode_stats() + self._gradients()
             self.iterations_started = True
+        elif p2p:                        # the whole update, exchange included, is one graph
+            n = self._run("ab_" + tag, lambda: self._seg_a(buffered) + self._seg_b_p2p(False))
         else:
             n = self._run("a_" + tag, lambda: self._seg_a(buffered))
         if self.world == 1:
             n += self._run("b1", self._seg_b_single)
+        elif p2p:
+            if first:
+                n += self._seg_b_p2p(True)
         elif self.mode == "sync":
             sync_exchange(self._gradbuf, self.pg)
             n += self._seg_b_sync(True) if first else self._run("b", lambda: self._seg_b_sync(False))

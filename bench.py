@@ -419,7 +419,7 @@ def run_ours(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     hbm_peak, bf16_peak, peaks_src = measured_peaks()
     tr = A2CTrainer(ENV_ID, n_envs=N_ENVS, horizon=HORIZON, seed=SEED, rank=rank, world=world, mode=args.mode,
-                    use_graph=not args.no_graph, tensor_cores=not args.ffma_only)
+                    use_graph=not args.no_graph, tensor_cores=not args.ffma_only, exchange=args.exchange)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
     clean_buf = torch.zeros(64 << 20, dtype=torch.float32, device="cuda")      # 256 MiB, only ever read
 
@@ -557,6 +557,15 @@ def run_ours(args, rank, local_rank, world):
         bref = b_ref_baselines(seconds=2.0) if world == 1 else None
         if bref is not None and args.workload == "pendulum":
             bref["gpu_same_shape"] = ref_shape_gpu()
+        if world == 1:
+            parallelism = "dp1"
+        elif args.mode == "async":
+            parallelism = "dp%d (envs sharded by rank; async: NCCL all-reduce of the parameter deltas)" % world
+        elif tr.exchange == "p2p":
+            parallelism = ("dp%d (envs sharded by rank; gradient exchange + lr rule + Adam as ONE kernel over NVLink peer "
+                           "memory, acx_allreduce_adam, inside the step's CUDA graph)" % world)
+        else:
+            parallelism = "dp%d (envs sharded by rank; NCCL all-reduce of the flat gradient)" % world
         line = {"metric": "env-steps/sec (rollout+update)", "value": value, "unit": "env-steps/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": step_ms, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
@@ -566,7 +575,7 @@ def run_ours(args, rank, local_rank, world):
                            "forward_engine": "tcgen05 3xTF32" if tr.tc else "fp32 FFMA", "backward_engine": ("tcgen05 3xTF32" if getattr(tr, "tc_bwd", False) and tr.N % 4 == 0
                                                else "tcgen05 3xTF32 (dX) + fp32 FFMA (dW)" if getattr(tr, "tc_bwd", False)
                                                else "fp32 FFMA"),
-                           "parallelism": "dp%d (envs sharded by rank, NCCL all-reduce of the flat gradient)" % world},
+                           "parallelism": parallelism},
                 "e2e": {"value": world * steps_per_it * args.steps / e_sec, "unit": "env-steps/s",
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e_sec / args.steps * 1e3,
                         "h2d": "pinned host buffers; the copy of step k+1's inputs overlaps step k's kernels on a copy "
@@ -703,6 +712,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--mode", choices=["sync", "async"], default="sync")
+    ap.add_argument("--exchange", choices=["auto", "p2p", "nccl"], default="auto",
+                    help="sync multi-GPU gradient exchange: p2p = fused peer-memory kernel, nccl = all_reduce")
     ap.add_argument("--no_graph", action="store_true", help="launch kernels eagerly (for ncu launch lists)")
     ap.add_argument("--ffma_only", action="store_true", help="keep the forward passes on the FFMA engine as well")
     ap.add_argument("--workload", choices=["pendulum", "cartpole", "eval"], default="pendulum",

@@ -330,7 +330,7 @@ int acx_loss_backward_cat_cached(const float* actor, const float* critic, int ob
  * acx_tc_pack_weights_bwd() and re-filled whenever the parameters change.  The activation cache is required.
  * Gradients agree with acx_loss_backward_*_cached to 3xTF32 accuracy, not bit for bit.
  * Workspace: with at least acx_loss_backward_workspace_bytes() the weight-gradient products run as fp32 FFMA
- * inside the same kernel; with at least acx_loss_backward_tc_workspace_bytes(rows, n) (room for dPre3 and dPre2 of
+ * inside the same kernel; with at least acx_loss_backward_tc_workspace_bytes(ob_dim, num_ac, cont, rows, n) (room for dPre3 and dPre2 of
  * one network, tile-blocked like the cache) and n % 4 == 0 they run on the tensor cores too, in a second kernel
  * per network (acx_wgrad_kernel: TMA tensor loads, 128-byte swizzle, accumulators in tensor memory). */
 size_t acx_loss_backward_tc_workspace_bytes(int ob_dim, int num_ac, int cont, int rows, int n);
@@ -395,6 +395,35 @@ int acx_kl_lr_update(float* opt, float* stats, void* stream);
  * travelled as one extra float behind the flat gradient of the NEXT update's all-reduce; the lr is first consumed by
  * that update's acx_adam_apply, so applying the rule there changes nothing -- and leaves it in stats[ACX_STAT_KL_POST]. */
 int acx_kl_lr_update_split(float* opt, float* stats, const float* kl_sum, float kl_scale, int flags, void* stream);
+
+/* ---- the exchange of a synchronous multi-GPU update, fused with the optimiser step (csrc/acx_xgpu.cu) ----
+ * Replaces the workers' gradient pushes onto the ps variables and the pull (A3C/policies.py:88-98,
+ * A3C/process.py:257-260) on the GPUs of ONE node, without a collective library: every rank keeps
+ * [flat gradient (actor ‖ critic) ‖ tail ‖ flags] in an exchange buffer that all ranks have mapped into their address
+ * space (the caller maps it -- torch symmetric memory, CUDA IPC, cuMemMap; nothing is allocated here), and ONE kernel
+ * per rank (a) waits until every rank's gradient is complete, (b) adds the buffers of ranks 0 .. world-1 in that fixed
+ * order with plain loads over NVLink (bit-identical sums on every rank), (c) applies the lr rule of
+ * A3C/process.py:262-270 to tail[0] * scale when apply_lr_rule != 0 (the previous update's KL, see
+ * acx_kl_lr_update_split), (d) runs acx_adam_apply's arithmetic (x scale, clip of the actor's gradient, Adam) on its
+ * elements, and (e) returns only when every peer has read this rank's buffer, so the caller may overwrite it at once.
+ * It does NOT write the opt block: follow it with acx_kl_lr_update_split(flags = 1, kl_sum = grad_sum + n_actor +
+ * n_critic, kl_scale = scale) when apply_lr_rule != 0 (records the same lr) and with acx_adam_tick.
+ *   peer_bufs   HOST array of world device pointers: rank r's exchange buffer as mapped on this device
+ *               (peer_bufs[rank] is this rank's own); each acx_xgpu_buffer_bytes(n_actor + n_critic + n_tail) long,
+ *               flags (from acx_xgpu_flag_offset_bytes on) zeroed on every rank before the first call
+ *   grad_sum    local, n_actor + n_critic + n_tail floats: receives the summed block (nullable)
+ *   generation  local, ACX_XGPU_MAX_BLOCKS words, zero before the first call, owned by this entry point afterwards
+ * All ranks must make the same sequence of calls (it is a collective).  Graph-capturable.  A rank that never arrives:
+ * the others wait 10 s, print which rank was missing and trap (launch error), they do not hang.
+ * world <= ACX_XGPU_MAX_RANKS; counts are multiples of 4 floats and at most 1024 * ACX_XGPU_MAX_BLOCKS in total. */
+#define ACX_XGPU_MAX_RANKS 8
+#define ACX_XGPU_MAX_BLOCKS 128
+size_t acx_xgpu_flag_offset_bytes(int n_floats);
+size_t acx_xgpu_buffer_bytes(int n_floats);
+int acx_allreduce_adam(const void* const* peer_bufs, int world, int rank, int n_actor, int n_critic, int n_tail,
+                       float* actor, float* m_actor, float* v_actor, float* critic, float* m_critic, float* v_critic,
+                       const float* opt, float* grad_sum, unsigned int* generation, float scale, int apply_lr_rule,
+                       void* stream);
 
 #ifdef __cplusplus
 }

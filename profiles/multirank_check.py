@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Multi-rank semantics on hardware (one process per GPU over NCCL), both modes of trainer.A2CTrainer:
+"""Multi-rank semantics on hardware (one process per GPU), both modes of trainer.A2CTrainer; the sync checks run twice, with the
+fused peer-memory exchange (acx_allreduce_adam) and with the NCCL all-reduce:
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29531 \
         profiles/multirank_check.py > profiles/r02_multirank_check.txt
@@ -47,43 +48,45 @@ def main():
     N, T, seed = 4096, 20, 12321
     for env_id in ("Pendulum-v0", "CartPole-v0"):
         kw = dict(n_envs=N, horizon=T, seed=seed, max_episode_steps=50)
-        # ---- 2: first update, sync
-        multi = A2CTrainer(env_id, rank=rank, world=world, mode="sync", **kw)
-        single = A2CTrainer(env_id, rank=rank, world=1, **kw)               # same shard (index0 = rank * N), no exchange
-        single.index0 = rank * N
-        theta0 = multi.params.cpu().numpy().copy()
-        P_ = multi.Pa + multi.Pc
-        # single-rank gradient of this shard: rollout + gradients only
-        single._rollout(False); single._episode_stats(); single._gradients()
-        g_local = single.grads.clone()
-        multi.iteration()
-        torch.cuda.synchronize()
-        gs = gather(g_local)
-        g_sum = np.sum(np.stack(gs).astype(np.float64), axis=0)
-        got = multi._gradbuf[:P_].cpu().numpy().astype(np.float64)
-        err = np.abs(got - g_sum).max() / np.abs(g_sum).max()
-        report("%s sync: all-reduced gradient = sum of the %d single-rank gradients" % (env_id, world), err <= 2e-6,
-               "(%.1e of max)" % err)
-        gm = (g_sum / world).astype(np.float32)
-        gm[:multi.Pa] = np.clip(gm[:multi.Pa], -0.1, 0.1)
-        z = np.zeros(P_, np.float32)
-        want = np.concatenate([P.adam_step(theta0[:multi.Pa], gm[:multi.Pa], z[:multi.Pa], z[:multi.Pa], 1, 0.005)[0],
-                               P.adam_step(theta0[multi.Pa:], gm[multi.Pa:], z[multi.Pa:], z[multi.Pa:], 1, 0.001)[0]])
-        got = multi.params.cpu().numpy()
-        # first Adam step = lr * g / (|g| + eps'): elements whose averaged gradient is rounding noise may flip sign
-        frac = float(np.mean(np.abs(got - want) > 1e-6))
-        report("%s sync: update = oracle adam_step(mean gradient, clip after the reduction)" % env_id, frac < 2e-3,
-               "(%.2e of the weights differ by > 1e-6)" % frac)
-        # ---- 1: replicas identical after 10 iterations
-        for _ in range(9):
+        for exch in ("auto", "nccl"):      # 'auto' = the fused peer-memory kernel where the buffers can be mapped
+            # ---- 2: first update, sync
+            multi = A2CTrainer(env_id, rank=rank, world=world, mode="sync", exchange=exch, **kw)
+            tag = "%s sync[%s]" % (env_id, multi.exchange)
+            single = A2CTrainer(env_id, rank=rank, world=1, **kw)               # same shard (index0 = rank * N), no exchange
+            single.index0 = rank * N
+            theta0 = multi.params.cpu().numpy().copy()
+            P_ = multi.Pa + multi.Pc
+            # single-rank gradient of this shard: rollout + gradients only
+            single._rollout(False); single._episode_stats(); single._gradients()
+            g_local = single.grads.clone()
             multi.iteration()
-        torch.cuda.synchronize()
-        same = all(all(np.array_equal(x, xs[0]) for x in xs) for xs in
-                   (gather(multi.params), gather(multi.m), gather(multi.v), gather(multi.opt)))
-        st = multi.read_stats()
-        report("%s sync: params / Adam moments / opt block bit-identical on %d ranks after 10 iterations" % (env_id, world),
-               same, "(iteration %d, lr %.5f, kl %.2e)" % (st["iteration"], st["next_lr"], st["kl_dist"]))
-        del multi
+            torch.cuda.synchronize()
+            gs = gather(g_local)
+            g_sum = np.sum(np.stack(gs).astype(np.float64), axis=0)
+            got = (multi.grad_sum if multi.exchange == "p2p" else multi._gradbuf)[:P_].cpu().numpy().astype(np.float64)
+            err = np.abs(got - g_sum).max() / np.abs(g_sum).max()
+            report("%s: summed gradient = sum of the %d single-rank gradients" % (tag, world), err <= 2e-6,
+                   "(%.1e of max)" % err)
+            gm = (g_sum / world).astype(np.float32)
+            gm[:multi.Pa] = np.clip(gm[:multi.Pa], -0.1, 0.1)
+            z = np.zeros(P_, np.float32)
+            want = np.concatenate([P.adam_step(theta0[:multi.Pa], gm[:multi.Pa], z[:multi.Pa], z[:multi.Pa], 1, 0.005)[0],
+                                   P.adam_step(theta0[multi.Pa:], gm[multi.Pa:], z[multi.Pa:], z[multi.Pa:], 1, 0.001)[0]])
+            got = multi.params.cpu().numpy()
+            # first Adam step = lr * g / (|g| + eps'): elements whose averaged gradient is rounding noise may flip sign
+            frac = float(np.mean(np.abs(got - want) > 1e-6))
+            report("%s: update = oracle adam_step(mean gradient, clip after the reduction)" % tag, frac < 2e-3,
+                   "(%.2e of the weights differ by > 1e-6)" % frac)
+            # ---- 1: replicas identical after 10 iterations
+            for _ in range(9):
+                multi.iteration()
+            torch.cuda.synchronize()
+            same = all(all(np.array_equal(x, xs[0]) for x in xs) for xs in
+                       (gather(multi.params), gather(multi.m), gather(multi.v), gather(multi.opt)))
+            st = multi.read_stats()
+            report("%s: params / Adam moments / opt block bit-identical on %d ranks after 10 iterations" % (tag, world),
+                   same, "(iteration %d, lr %.5f, kl %.2e)" % (st["iteration"], st["next_lr"], st["kl_dist"]))
+            del multi, single
         # ---- 3: first update, async
         am = A2CTrainer(env_id, rank=rank, world=world, mode="async", **kw)
         am.iteration()
@@ -107,7 +110,7 @@ def main():
         lrs = [float(o[0]) for o in gather(am.opt)]
         report("%s async: shared parameters bit-identical on %d ranks after 10 iterations" % (env_id, world), same,
                "(per-rank lr %s)" % ", ".join("%.5f" % x for x in lrs))
-        del am, single
+        del am
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
