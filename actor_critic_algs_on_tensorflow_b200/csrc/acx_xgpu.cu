@@ -62,25 +62,37 @@ __device__ inline float4 ld_peer4(const float* p) {      // system-scope, never 
                : "memory");
   return v;
 }
+__device__ inline float ld_peer1(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ inline uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// polls with relaxed loads (an acquire load invalidates L1 on every poll), then ONE acquire load orders what follows
 __device__ inline void wait_flag(const uint32_t* p, uint32_t g, int my_rank, int other, int what) {
-  if ((int32_t)(ld_acquire_sys(p) - g) >= 0) return;
-  const uint64_t t0 = acx_globaltimer();
-  for (;;) {
-    for (int spin = 0; spin < 256; ++spin)
-      if ((int32_t)(ld_acquire_sys(p) - g) >= 0) return;
-    if (acx_globaltimer() - t0 > ACX_XGPU_TIMEOUT_NS) {
-      printf("acx_allreduce_adam: rank %d block %d waited %llu s for rank %d (%s, generation %u, flag %u)\n", my_rank,
-             (int)blockIdx.x, (unsigned long long)(ACX_XGPU_TIMEOUT_NS / 1000000000ull), other,
-             what ? "exit: peer has not read this rank's gradient" : "entry: peer's gradient not ready", g,
-             ld_acquire_sys(p));
-      __trap();
+  if ((int32_t)(ld_relaxed_sys(p) - g) < 0) {
+    const uint64_t t0 = acx_globaltimer();
+    for (bool seen = false; !seen;) {
+      for (int spin = 0; spin < 64 && !seen; ++spin) seen = (int32_t)(ld_relaxed_sys(p) - g) >= 0;
+      if (!seen && acx_globaltimer() - t0 > ACX_XGPU_TIMEOUT_NS) {
+        printf("acx_allreduce_adam: rank %d block %d waited %llu s for rank %d (%s, generation %u, flag %u)\n", my_rank,
+               (int)blockIdx.x, (unsigned long long)(ACX_XGPU_TIMEOUT_NS / 1000000000ull), other,
+               what ? "exit: peer has not read this rank's gradient" : "entry: peer's gradient not ready", g,
+               ld_relaxed_sys(p));
+        __trap();
+      }
     }
   }
+  (void)ld_acquire_sys(p);
 }
 
 __global__ void __launch_bounds__(XG_THREADS) acx_allreduce_adam_kernel(const XgArgs a) {
   __shared__ uint32_t g_sh;
-  __shared__ float lr_sh;
+  __shared__ float kl_sh[ACX_XGPU_MAX_RANKS];
   const int tid = threadIdx.x, b = blockIdx.x, W = a.world;
   if (tid == 0) g_sh = ++a.gen[b];
   __syncthreads();
@@ -96,31 +108,29 @@ __global__ void __launch_bounds__(XG_THREADS) acx_allreduce_adam_kernel(const Xg
   }
   __syncthreads();
 
-  // ---- reduce: fixed rank order
+  // ---- reduce: all W loads of a thread are issued before the first add (one NVLink round trip, not W), the adds run
+  // in the fixed rank order
   const int n4p = a.n4a + a.n4c, n4 = n4p + a.n4t;
   const int i = b * XG_THREADS + tid;
+  const bool rule = a.apply_lr_rule && a.n4t > 0;
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   if (i < n4) {
-    for (int r = 0; r < W; ++r) {
-      const float4 v = ld_peer4(a.peer[r] + 4 * (size_t)i);
-      s.x = __fadd_rn(s.x, v.x); s.y = __fadd_rn(s.y, v.y); s.z = __fadd_rn(s.z, v.z); s.w = __fadd_rn(s.w, v.w);
-    }
+    float4 v[ACX_XGPU_MAX_RANKS];
+#pragma unroll
+    for (int r = 0; r < ACX_XGPU_MAX_RANKS; ++r)
+      if (r < W) v[r] = ld_peer4(a.peer[r] + 4 * (size_t)i);
+    if (rule && tid < W) kl_sh[tid] = ld_peer1(a.peer[tid] + 4 * (size_t)n4p);      // tail word 0 of rank tid
+#pragma unroll
+    for (int r = 0; r < ACX_XGPU_MAX_RANKS; ++r)
+      if (r < W) {
+        s.x = __fadd_rn(s.x, v[r].x); s.y = __fadd_rn(s.y, v[r].y);
+        s.z = __fadd_rn(s.z, v[r].z); s.w = __fadd_rn(s.w, v[r].w);
+      }
     if (a.grad_sum != nullptr) reinterpret_cast<float4*>(a.grad_sum)[i] = s;
+  } else if (rule && tid < W) {
+    kl_sh[tid] = ld_peer1(a.peer[tid] + 4 * (size_t)n4p);
   }
-  // the actor's learning rate of THIS step: the rule on the rank-averaged KL of the previous update (tail word 0).
-  // Every block forms it for itself from the same words in the same order; the opt block is not written here (a
-  // block reading it after another had updated it would apply the rule twice) -- acx_kl_lr_update_split(flags = 1)
-  // on grad_sum's tail, launched right after this kernel, records the same value.
-  if (tid == 0) {
-    float lr = a.opt[ACX_OPT_ACTOR_LR];
-    if (a.apply_lr_rule && a.n4t > 0) {
-      float kl = 0.f;
-      for (int r = 0; r < W; ++r) kl = __fadd_rn(kl, ld_peer4(a.peer[r] + 4 * (size_t)n4p).x);
-      lr = acx_lr_rule(lr, __fmul_rn(kl, a.scale), a.opt);
-    }
-    lr_sh = lr;
-  }
-  __syncthreads();      // all loads of this block have returned (they fed the adds above)
+  __syncthreads();      // all loads of this block have returned (they fed the adds / the shared words above)
 
   // ---- exit, first half: peers may overwrite their block b
   if (tid < W)
@@ -128,10 +138,20 @@ __global__ void __launch_bounds__(XG_THREADS) acx_allreduce_adam_kernel(const Xg
 
   // ---- Adam on this block's elements (the arithmetic of acx_adam_kernel)
   if (i < n4p) {
+    // the actor's learning rate of THIS step: the rule on the rank-averaged KL of the previous update (tail word 0),
+    // formed by every thread from the same words in the same order.  The opt block is not written here (a block
+    // reading it after another had updated it would apply the rule twice): acx_kl_lr_update_split(flags = 1) on
+    // grad_sum's tail, launched right after this kernel, records the same value.
+    float lr_a = a.opt[ACX_OPT_ACTOR_LR];
+    if (rule) {
+      float kl = 0.f;
+      for (int r = 0; r < W; ++r) kl = __fadd_rn(kl, kl_sh[r]);
+      lr_a = acx_lr_rule(lr_a, __fmul_rn(kl, a.scale), a.opt);
+    }
     const float corr = acx_adam_corr(a.opt);
     const bool is_a = i < a.n4a;
     const int j = is_a ? i : i - a.n4a;
-    const float alpha = __fmul_rn(is_a ? lr_sh : a.opt[ACX_OPT_CRITIC_LR], corr);
+    const float alpha = __fmul_rn(is_a ? lr_a : a.opt[ACX_OPT_CRITIC_LR], corr);
     const float clip = a.opt[ACX_OPT_CLIP];
     float4* th = reinterpret_cast<float4*>(is_a ? a.actor : a.critic) + j;
     float4* m = reinterpret_cast<float4*>(is_a ? a.ma : a.mc) + j;
