@@ -161,13 +161,23 @@ class A2CTrainer:
         want = os.environ.get("ACX_EXCHANGE", exchange)
         assert want in ("auto", "p2p", "nccl"), want
         if self.world > 1 and mode == "sync" and want != "nccl":
+            err = None
             try:
                 self._setup_p2p(P)
             except Exception as e:       # noqa: BLE001 -- any failure to map peer memory means the NCCL exchange
+                err = e
+            # the ranks must agree (one that could not map its peers would sit in all_reduce while the others spin in
+            # acx_allreduce_adam); the same collective is the barrier after which every rank's flag words are zero
+            import torch.distributed as dist
+            agreed = torch.tensor([1 if self.exchange == "p2p" else 0], device=d, dtype=torch.int32)
+            dist.all_reduce(agreed, op=dist.ReduceOp.MIN, group=self.pg)
+            if int(agreed.item()) == 0:
+                why = ("%s: %s" % (type(err).__name__, err)) if err is not None else "another rank could not map the buffers"
                 if want == "p2p":
-                    raise
-                print("[acx] rank %d: peer-mapped exchange unavailable (%s: %s); using the NCCL all-reduce" %
-                      (self.rank, type(e).__name__, e), file=sys.stderr, flush=True)
+                    raise L.AcxError("exchange='p2p' unavailable on rank %d (%s)" % (self.rank, why)) from err
+                print("[acx] rank %d: peer-mapped exchange unavailable (%s); using the NCCL all-reduce" % (self.rank, why),
+                      file=sys.stderr, flush=True)
+                self.exchange = "nccl"          # a mapped exchange buffer stays where it is: NCCL reduces it as well
 
         self.state = torch.empty((self.S, N), device=d, dtype=f32)
         self.elapsed = torch.zeros(N, device=d, dtype=torch.int32)
@@ -481,8 +491,7 @@ class A2CTrainer:
         self.grads = self._gradbuf[:P]
         self.grad_sum = torch.zeros(P + GRAD_TAIL, device=self.dev, dtype=torch.float32)
         self._xgen = torch.zeros(128, device=self.dev, dtype=torch.int32)
-        torch.cuda.synchronize()
-        dist.barrier(group)              # every rank's flags are zero before anybody signals
+        torch.cuda.synchronize()         # flags zeroed; the caller's agreement all_reduce is the barrier before first use
         self.exchange = "p2p"
 
     def _seg_b_p2p(self, first):
